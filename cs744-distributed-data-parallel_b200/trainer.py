@@ -1,0 +1,168 @@
+"""One trainer for all four parts.
+
+Job setup, epoch driver, training loop and evaluation loop of the reference (``run`` /
+``train_model`` / ``test_model``: ref ``Part 2a/main.py:19-68,71-114,130-145``),
+written once and parameterised by a gradient-sync strategy and an execution back-end.
+
+Deliberate deviations from the reference, each documented in SURVEY A.3:
+
+* train mode is restored at the start of every epoch (the reference leaves the model in eval
+  mode after the first ``test_model``; set ``reproduce_eval_mode_quirk`` to get that back);
+* the window loss is accumulated on the device and read back once per 20 iterations instead of
+  keeping 20 autograd-attached tensors and syncing every iteration;
+* on CUDA the three timed regions use CUDA events and are reported as the max over ranks.
+"""
+from __future__ import annotations
+
+import time
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .backends import make_backend
+from .config import TrainConfig
+from .data import BatchLoader, GlobalShuffleSampler, SequentialSampler, ShardedSampler, get_split
+from .utils import checkpoint as ckpt
+from .utils.logger import RunLogger
+from .utils.seed import seed_everything
+from .utils.timers import CudaRegionTimer, HostRegionTimer, max_over_ranks
+
+
+def resolve_device(cfg: TrainConfig) -> torch.device:
+    want = cfg.device
+    if want == "auto":
+        want = "cuda" if torch.cuda.is_available() else "cpu"
+    if want.startswith("cuda"):
+        if not torch.cuda.is_available():
+            raise RuntimeError("--device cuda requested but no CUDA device is visible")
+        from .parallel.launch import local_device_index
+        idx = local_device_index(cfg.rank)
+        torch.cuda.set_device(idx)
+        return torch.device("cuda", idx)
+    return torch.device("cpu")
+
+
+class Trainer:
+    def __init__(self, cfg: TrainConfig, logger: Optional[RunLogger] = None,
+                 train_split=None, test_split=None) -> None:
+        self.cfg = cfg
+        torch.set_num_threads(cfg.cpu_threads)                      # ref Part 1/main.py:11
+        self.device = resolve_device(cfg)
+        seed_everything(cfg.seed)                                    # ref Part 2a/main.py:20-21
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        if self.world != cfg.world_size:
+            raise RuntimeError(f"process group has {self.world} ranks, config says {cfg.world_size}")
+        self.batch_size = cfg.per_rank_batch                         # ref Part 2a/main.py:22
+        self.logger = logger or RunLogger(cfg.part, cfg.log_every, self.rank,
+                                          json_lines=cfg.json_log, prefix_rank=cfg.log_prefix_rank)
+
+        # datasets live where the compute is: no worker processes, no per-sample python
+        on_dev = self.device if self.device.type == "cuda" else torch.device("cpu")
+        self.train_split = (train_split or get_split(True, cfg.synthetic, cfg.data_root,
+                                                     cfg.train_size if cfg.synthetic else None,
+                                                     cfg.seed)).to(on_dev)
+        self.test_split = (test_split or get_split(False, cfg.synthetic, cfg.data_root,
+                                                   cfg.test_size if cfg.synthetic else None,
+                                                   cfg.seed)).to(on_dev)
+        if cfg.sync == "none" and self.world == 1:
+            sampler = GlobalShuffleSampler(len(self.train_split))   # Part 1: shuffle=True
+        else:
+            sampler = ShardedSampler(len(self.train_split), self.world, self.rank, seed=0)
+        self.train_sampler = sampler
+        self.train_loader = BatchLoader(self.train_split, sampler, self.batch_size, True,
+                                        aug_seed=cfg.seed + self.rank)
+        self.logger.train_loader_size(len(self.train_loader))
+        self.test_loader = BatchLoader(self.test_split, SequentialSampler(len(self.test_split)),
+                                       self.batch_size, False)
+        self.logger.test_loader_size(len(self.test_loader))
+
+        self.backend = make_backend(cfg, self.device)
+        self.timer = (CudaRegionTimer() if self.device.type == "cuda" else HostRegionTimer())
+        self.start_epoch = 0
+        self.global_iteration = 0
+        if cfg.resume:
+            self.load_checkpoint(cfg.resume)
+
+    # ------------------------------------------------------------------------------------
+    def fit(self) -> Dict[str, float]:
+        result: Dict[str, float] = {}
+        for epoch in range(self.start_epoch, self.cfg.epochs):
+            t0 = time.time()
+            self.train_epoch(epoch)
+            self.backend.synchronize()
+            self.logger.epoch_time(epoch + 1, time.time() - t0)
+            loss, correct, total = self.evaluate()
+            result = {"test_loss": loss, "correct": correct, "total": total}
+        if self.cfg.checkpoint and self.rank == 0:
+            self.save_checkpoint(self.cfg.checkpoint)
+        return result
+
+    # ------------------------------------------------------------------------------------
+    def train_epoch(self, epoch: int = 0) -> List[Dict]:
+        cfg, be, timer, log = self.cfg, self.backend, self.timer, self.logger
+        if not (cfg.reproduce_eval_mode_quirk and epoch > 0):
+            be.set_train(True)
+        n_win = cfg.log_every
+        loss_acc = None
+        host_times: List[Tuple[float, float, float]] = []
+        iter_number = 1
+        for raw in self.train_loader:
+            data, target = be.prepare(raw)
+            loss = be.train_step(data, target, timer)
+            loss_acc = loss if loss_acc is None else loss_acc + loss
+            if not timer.is_async:
+                host_times.append(timer.collect())
+            if iter_number % n_win == 0:
+                times = timer.flush() if timer.is_async else host_times
+                sums = [sum(t[i] for t in times) / float(n_win) for i in range(3)]
+                if self.world > 1 and self.device.type == "cuda":
+                    sums = max_over_ranks(sums, self.device)
+                mean_loss = float(loss_acc) / float(n_win)
+                extra = None
+                if cfg.json_log and iter_number != n_win and sums[2] > 0:
+                    extra = {"images_per_s": self.batch_size * self.world / sums[2]}
+                log.window(iter_number, mean_loss, sums[0], sums[1], sums[2], extra)
+                loss_acc, host_times = None, []
+            self.global_iteration += 1
+            if cfg.max_iters is not None and iter_number >= cfg.max_iters:
+                break
+            iter_number += 1
+        if timer.is_async:
+            timer.flush()
+        return log.records
+
+    # ------------------------------------------------------------------------------------
+    def evaluate(self) -> Tuple[float, int, int]:
+        """Every rank scores the full test set on its own (ref ``Part 2a/main.py:130-145``)."""
+        be = self.backend
+        be.set_train(False)
+        be.before_eval()
+        loss_sum, correct, batches, seen = None, None, 0, 0
+        for raw in self.test_loader:
+            data, target = be.prepare(raw)
+            loss, hits = be.eval_step(data, target)
+            loss_sum = loss if loss_sum is None else loss_sum + loss
+            correct = hits if correct is None else correct + hits
+            batches += 1
+            seen += raw.size
+            if self.cfg.eval_batches is not None and batches >= self.cfg.eval_batches:
+                break
+        total = len(self.test_split) if self.cfg.eval_batches is None else seen
+        denom = len(self.test_loader) if self.cfg.eval_batches is None else batches
+        avg = float(loss_sum) / float(denom)
+        self.logger.test_result(avg, int(correct), total)
+        return avg, int(correct), total
+
+    # ------------------------------------------------------------------------------------
+    def save_checkpoint(self, path: str) -> None:
+        ckpt.save_training(path, self.backend.state_dict(), self.backend.optimizer_state_dict(),
+                           self.cfg.epochs, self.global_iteration,
+                           {"model": self.cfg.model, "sync": self.cfg.sync, "dtype": self.cfg.dtype})
+
+    def load_checkpoint(self, path: str) -> None:
+        blob = ckpt.load(path)
+        self.backend.load_state_dict(blob["model"])
+        self.backend.load_optimizer_state_dict(blob.get("optimizer"))
+        self.global_iteration = int(blob.get("iteration", 0))
