@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""Headline benchmark: VGG-11 / CIFAR-shaped synthetic data, images/sec, weak scaling.
+
+    python bench.py --gpus N --steps K --warmup W [--impl ours|reference]
+
+Metric and config are the ones BASELINE.json names: "VGG-11 CIFAR-10 images/sec + avg iter time
+at 1/2/4/8 B200 (max over ranks)", Part 3 (bucketed data parallel with backward overlap), bf16,
+per-GPU batch 256 (global batch 2048 at 8 GPUs), SGD lr .1 / momentum .9 / wd 1e-4, every step
+= zero_grad + forward + loss + backward + gradient sync + optimizer step.
+
+Two numbers per run, both timed on the device with CUDA events bracketed by barrier +
+synchronize, max over ranks:
+
+* ``value``      – the training step on device-resident inputs (kernel-only view);
+* ``e2e.value``  – the same steps through the public API (``Trainer``-level ``prepare`` +
+  ``train_step``) including, every step, the host->device copy of that step's batch from pinned
+  host memory and a device->host read of the step's loss.
+
+``--impl reference`` runs the UNMODIFIED reference (``baseline/_ref/src/Part 3``): its own
+``mdl.VGG11()``, ``DDP(model)``, ``optim.SGD`` and ``train_model()`` loop, fed by a loader that
+yields CUDA tensors (the reference loop never moves data itself, ref Part 3/main.py:88-97).
+"""
+from __future__ import annotations
+
+import argparse
+import contextlib
+import io
+import json
+import os
+import shutil
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+
+PER_GPU_BATCH = 256
+METRIC = "VGG-11 CIFAR-10 images/sec (Part 3 bucketed DP, max over ranks)"
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi, rank 0 only, during the timed region)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int = 0) -> None:
+        self.rows = []
+        self.proc = None
+        self.device_index = device_index
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.device_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 8:
+                self.rows.append(parts)
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+def dist_setup(n_gpus: int):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if n_gpus != world:
+        if world == 1 and n_gpus > 1:
+            raise SystemExit(f"--gpus {n_gpus} needs a torchrun launch with {n_gpus} ranks "
+                             f"(python -m torch.distributed.run --nproc-per-node {n_gpus} bench.py ...)")
+        n_gpus = world
+    torch.cuda.set_device(local)
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def barrier_sync(world: int) -> None:
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(ms: float, world: int) -> float:
+    if world == 1:
+        return ms
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
+
+
+def synthetic_host_batches(n: int, seed: int, kind: str):
+    """Pinned host batches. kind='u8' -> (uint8 NHWC images, labels, crop, flip) for our pipeline;
+    kind='f32' -> (normalised fp32 NCHW, labels), i.e. what the reference's DataLoader delivers."""
+    g = torch.Generator().manual_seed(1234 + seed)
+    out = []
+    for _ in range(n):
+        labels = torch.randint(0, 10, (PER_GPU_BATCH,), generator=g, dtype=torch.int64).pin_memory()
+        if kind == "u8":
+            img = torch.randint(0, 256, (PER_GPU_BATCH, 32, 32, 3), generator=g, dtype=torch.uint8).pin_memory()
+            crop = torch.randint(0, 9, (PER_GPU_BATCH, 2), generator=g, dtype=torch.int32).pin_memory()
+            flip = (torch.rand(PER_GPU_BATCH, generator=g) < 0.5).to(torch.uint8).pin_memory()
+            out.append((img, labels, crop, flip))
+        else:
+            out.append((torch.randn(PER_GPU_BATCH, 3, 32, 32, generator=g).pin_memory(), labels))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm
+# ------------------------------------------------------------------------------------------------
+def ensure_reference() -> str | None:
+    dst = os.path.join(ROOT, "baseline", "_ref", "src")
+    if os.path.exists(os.path.join(dst, "Part 3", "main.py")):
+        return dst
+    if os.path.isdir("/root/reference/src"):
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copytree("/root/reference/src", dst, dirs_exist_ok=True)
+        return dst
+    return None
+
+
+def load_reference_part3(src: str):
+    import importlib.util
+    part = os.path.join(src, "Part 3")
+    sys.path.insert(0, part)                      # main.py does `import model as mdl`
+    spec = importlib.util.spec_from_file_location("_ref_part3_main", os.path.join(part, "main.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def run_reference(args) -> dict:
+    src = ensure_reference()
+    if src is None:
+        return {"impl": "reference", "unavailable": "reference sources not found (baseline/_ref/src, /root/reference)"}
+    try:
+        import torchvision  # noqa: F401  (imported by the reference's main.py)
+    except Exception as e:
+        return {"impl": "reference", "unavailable": f"torchvision import failed: {e}"}
+    rank, world, local = dist_setup(args.gpus)
+    with contextlib.redirect_stdout(io.StringIO()):
+        ref = load_reference_part3(src)
+    torch.set_num_threads(4)
+
+    def one_run(autocast: bool, host_batches):
+        torch.manual_seed(0)
+        model = ref.mdl.VGG11().cuda()
+        if world > 1:
+            model = ref.DDP(model, device_ids=[local])
+        opt = ref.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
+        crit = torch.nn.CrossEntropyLoss().cuda()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        total = args.warmup + args.steps
+        dev_batches = None
+        if host_batches is None:
+            g = torch.Generator(device="cuda").manual_seed(7 + rank)
+            dev_batches = [(torch.randn(PER_GPU_BATCH, 3, 32, 32, device="cuda", generator=g),
+                            torch.randint(0, 10, (PER_GPU_BATCH,), device="cuda", generator=g)) for _ in range(4)]
+        sampler = ClockSampler(local) if rank == 0 else None
+
+        def loader():
+            for i in range(total):
+                if i == args.warmup:
+                    barrier_sync(world)
+                    if sampler:
+                        sampler.start()
+                    ev0.record()
+                if host_batches is not None:
+                    x, y = host_batches[i % len(host_batches)]
+                    yield x.cuda(non_blocking=True), y.cuda(non_blocking=True)
+                else:
+                    yield dev_batches[i % len(dev_batches)]
+            ev1.record()
+            torch.cuda.synchronize()
+
+        ctx = torch.autocast("cuda", dtype=torch.bfloat16) if autocast else contextlib.nullcontext()
+        model.train()
+        with contextlib.redirect_stdout(io.StringIO()), ctx:
+            ref.train_model(model, loader(), opt, crit)      # the reference's own loop, unmodified
+        barrier_sync(world)
+        clocks = sampler.stop() if sampler else None
+        ms = max_over_ranks(ev0.elapsed_time(ev1) / args.steps, world)
+        return ms, clocks
+
+    host = synthetic_host_batches(8, rank, "f32")
+    results = {}
+    for name, ac in (("fp32", False), ("bf16_autocast", True)):
+        dev_ms, clocks = one_run(ac, None)
+        e2e_ms, _ = one_run(ac, host)
+        results[name] = {"ms_per_step": dev_ms, "e2e_ms_per_step": e2e_ms, "clocks": clocks}
+    best = min(results, key=lambda k: results[k]["ms_per_step"])
+    best_e2e = min(results, key=lambda k: results[k]["e2e_ms_per_step"])
+    gb = PER_GPU_BATCH * world
+    ms = results[best]["ms_per_step"]
+    bytes_in = sum(t.numel() * t.element_size() for t in host[0])
+    out = {
+        "impl": "reference", "metric": METRIC, "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if best == "bf16_autocast" else "fp32(tf32 conv)",
+        "data": "synthetic", "clocks": results[best]["clocks"],
+        "e2e": {"value": gb / results[best_e2e]["e2e_ms_per_step"] * 1e3, "unit": "images/s",
+                "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": 0,
+                "note": "reference loop reads the loss on the host only every 20 iterations (its print)"},
+        "gpu_launches": 0,
+        "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": PER_GPU_BATCH, "seq_len": None,
+                   "parallelism": f"dp{world}", "part": "3 (torch DDP)" if world > 1 else "3 (single GPU, no DDP wrap)",
+                   "variants": {k: {"images_per_s": gb / v["ms_per_step"] * 1e3,
+                                    "e2e_images_per_s": gb / v["e2e_ms_per_step"] * 1e3} for k, v in results.items()},
+                   "l2": "working set per step (activations + weights + grads) > 126 MB L2; no explicit flush"},
+    }
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args) -> dict:
+    rank, world, local = dist_setup(args.gpus)
+    from cs744_ddp_b200.config import TrainConfig
+    from cs744_ddp_b200.engine import NativeBackend
+    from cs744_ddp_b200.data.pipeline import RawBatch
+
+    cfg = TrainConfig(num_nodes=world, rank=rank, sync="bucketed" if world > 1 else "none", dtype=args.dtype,
+                      device="cuda", backend="native", global_batch=PER_GPU_BATCH * world, synthetic=True,
+                      bucket_plan=args.bucket_plan, comm=args.comm, use_cuda_graph=not args.no_graph)
+    be = NativeBackend(cfg, torch.device("cuda", local))
+    host = synthetic_host_batches(8, rank, "u8")
+    dev = [RawBatch(*[t.cuda() for t in hb]) for hb in host[:4]]
+    prepared = [be.prepare(b) for b in dev]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    class _NoTimer:
+        def mark(self, i):
+            pass
+
+    timer = _NoTimer()
+
+    def steps(n, e2e):
+        last = None
+        for i in range(n):
+            if e2e:
+                hb = host[i % len(host)]
+                raw = RawBatch(*[t.cuda(non_blocking=True) for t in hb])
+                data, target = be.prepare(raw)
+                last = float(be.train_step(data, target, timer))          # D2H read of the loss, every step
+            else:
+                data, target = prepared[i % len(prepared)]
+                last = be.train_step(data, target, timer)
+        return last
+
+    def timed(e2e):
+        steps(args.warmup, e2e)
+        barrier_sync(world)
+        sampler = ClockSampler(local) if (rank == 0 and not e2e) else None
+        if sampler:
+            sampler.start()
+        l0 = be.launch_count()
+        ev0.record()
+        steps(args.steps, e2e)
+        ev1.record()
+        barrier_sync(world)
+        clocks = sampler.stop() if sampler else None
+        launches = be.launch_count() - l0
+        return max_over_ranks(ev0.elapsed_time(ev1) / args.steps, world), clocks, launches
+
+    ms, clocks, launches = timed(False)
+    e2e_ms, _, _ = timed(True)
+    gb = PER_GPU_BATCH * world
+    bytes_in = sum(t.numel() * t.element_size() for t in host[0])
+    return {
+        "impl": "ours", "metric": METRIC, "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "clocks": clocks,
+        "e2e": {"value": gb / e2e_ms * 1e3, "unit": "images/s", "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches,
+        "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": PER_GPU_BATCH, "seq_len": None,
+                   "parallelism": f"dp{world}", "part": "3 (bucketed P2P reduce fused with SGD)" if world > 1
+                   else "3 (single GPU)", "comm": be.comm_name(), "cuda_graph": be.uses_graph(),
+                   "bucket_plan": args.bucket_plan,
+                   "l2": "working set per step (activations + weights + grads) > 126 MB L2; no explicit flush"},
+    }
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--bucket-plan", default="per_layer", choices=["ddp", "per_layer", "single"])
+    ap.add_argument("--comm", default="auto", choices=["auto", "p2p", "nccl"])
+    ap.add_argument("--no-graph", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if not torch.cuda.is_available():
+        msg = {"impl": args.impl, "unavailable": "no CUDA device visible"}
+        print(json.dumps(msg))
+        return
+    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps(out), flush=True)
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

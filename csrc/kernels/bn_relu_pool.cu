@@ -1,0 +1,410 @@
+// BatchNorm2d (+ReLU, + optional 2x2/2 max-pool) forward and backward on NHWC tensors.
+//
+// Replaces the reference's BatchNorm2d -> ReLU(inplace) [-> MaxPool2d(2,2)] module triplets
+// (ref Part 1/model.py:16,24-25; SURVEY K-N1/K-N2/K-N3).  The per-channel batch statistics
+// (sum, sum of squares) arrive already reduced: the convolution epilogue accumulates them
+// (csrc/kernels/conv_tc.cu), so forward is ONE pass over the conv output:
+//   y -> normalise + affine + ReLU (+ pool) -> next layer's input,
+// plus the running-stat update (momentum 0.1, unbiased variance) done by block 0.
+// Backward is two passes (the two per-channel reductions BN needs, then dX); the pool routing
+// and ReLU mask are recomputed from the saved conv output instead of being stored.
+#include "../common.cuh"
+#include "../../include/ddp_b200.h"
+
+namespace ddpb {
+
+template <typename T> struct VecOf { static constexpr int N = 16 / sizeof(T); };
+
+// decode output pixel -> the (up to) four input pixel indices
+template <bool POOL>
+__device__ __forceinline__ void window(long long opix, int H, int W, long long* in) {
+  if (!POOL) { in[0] = opix; return; }
+  int OW = W >> 1, OH = H >> 1;
+  int ow = (int)(opix % OW);
+  long long r = opix / OW;
+  int oh = (int)(r % OH);
+  long long n = r / OH;
+  long long base = (n * H + 2 * oh) * W + 2 * ow;
+  in[0] = base; in[1] = base + 1; in[2] = base + W; in[3] = base + W + 1;
+}
+
+// ------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------
+template <typename T, bool POOL>
+__global__ void __launch_bounds__(256)
+bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const float* __restrict__ gamma,
+              const float* __restrict__ beta, T* __restrict__ out, float* __restrict__ save_mean,
+              float* __restrict__ save_invstd, float* __restrict__ running_mean,
+              float* __restrict__ running_var, long long* __restrict__ nbt, long long P, long long Pout,
+              int C, int H, int W, float eps, float momentum, int training) {
+  constexpr int V = VecOf<T>::N;
+  const int groups = C / V;
+  const int g = threadIdx.x % groups;
+  const int pl = threadIdx.x / groups;
+  const int ppb = blockDim.x / groups;
+  const int c0 = g * V;
+
+  float sc[V], sh[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    float mean, var;
+    if (training) {
+      mean = stats[c0 + j] / (float)P;
+      var = fmaxf(stats[C + c0 + j] / (float)P - mean * mean, 0.f);
+    } else {
+      mean = running_mean[c0 + j];
+      var = running_var[c0 + j];
+    }
+    float invstd = rsqrtf(var + eps);
+    sc[j] = gamma[c0 + j] * invstd;
+    sh[j] = beta[c0 + j] - mean * sc[j];
+    if (training && blockIdx.x == 0 && pl == 0) {
+      save_mean[c0 + j] = mean;
+      save_invstd[c0 + j] = invstd;
+      float unbiased = P > 1 ? var * ((float)P / (float)(P - 1)) : var;
+      running_mean[c0 + j] = (1.f - momentum) * running_mean[c0 + j] + momentum * mean;
+      running_var[c0 + j] = (1.f - momentum) * running_var[c0 + j] + momentum * unbiased;
+    }
+  }
+  if (training && blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
+  if (pl >= ppb) return;
+
+  for (long long op = (long long)blockIdx.x * ppb + pl; op < Pout; op += (long long)gridDim.x * ppb) {
+    long long in[4];
+    window<POOL>(op, H, W, in);
+    float best[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) best[j] = 0.f;          // ReLU floor
+#pragma unroll
+    for (int q = 0; q < (POOL ? 4 : 1); ++q) {
+      float v[V];
+      load_vec<T>(y + in[q] * C + c0, v);
+#pragma unroll
+      for (int j = 0; j < V; ++j) best[j] = fmaxf(best[j], fmaf(v[j], sc[j], sh[j]));
+    }
+    store_vec<T>(out + op * C + c0, best);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward pass 1: s1[c] = sum dz, s2[c] = sum dz * xhat      (dz = dOut routed through pool+ReLU)
+// ------------------------------------------------------------------------------------------
+template <typename T, bool POOL>
+__global__ void __launch_bounds__(256)
+bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const float* __restrict__ mean,
+                     const float* __restrict__ invstd, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float* __restrict__ sums, long long Pout, int C, int H,
+                     int W) {
+  constexpr int V = VecOf<T>::N;
+  extern __shared__ float sm[];      // [2*C]
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const int groups = C / V;
+  const int g = threadIdx.x % groups;
+  const int pl = threadIdx.x / groups;
+  const int ppb = blockDim.x / groups;
+  const int c0 = g * V;
+  float sc[V], sh[V], mu[V], is[V], a1[V], a2[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    mu[j] = mean[c0 + j]; is[j] = invstd[c0 + j];
+    sc[j] = gamma[c0 + j] * is[j];
+    sh[j] = beta[c0 + j] - mu[j] * sc[j];
+    a1[j] = 0.f; a2[j] = 0.f;
+  }
+  if (pl < ppb) {
+    for (long long op = (long long)blockIdx.x * ppb + pl; op < Pout; op += (long long)gridDim.x * ppb) {
+      long long in[4];
+      window<POOL>(op, H, W, in);
+      float d[V];
+      load_vec<T>(dout + op * C + c0, d);
+      float bz[V], by[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) { bz[j] = 0.f; by[j] = 0.f; }
+#pragma unroll
+      for (int q = 0; q < (POOL ? 4 : 1); ++q) {
+        float v[V];
+        load_vec<T>(y + in[q] * C + c0, v);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          float z = fmaf(v[j], sc[j], sh[j]);
+          if (z > bz[j]) { bz[j] = z; by[j] = v[j]; }     // strict >: first maximum wins, z<=0 never does
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        if (bz[j] > 0.f) {
+          a1[j] += d[j];
+          a2[j] += d[j] * (by[j] - mu[j]) * is[j];
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      atomicAdd(&sm[c0 + j], a1[j]);
+      atomicAdd(&sm[C + c0 + j], a2[j]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&sums[i], sm[i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// backward pass 2: dy = gamma*invstd * (dz - s1/P - xhat * s2/P); also dgamma, dbeta, conv dbias
+// ------------------------------------------------------------------------------------------
+template <typename T, bool POOL>
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, const float* __restrict__ sums, T* __restrict__ dy,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
+                    long long P, long long Pout, int C, int H, int W) {
+  constexpr int V = VecOf<T>::N;
+  extern __shared__ float sm[];      // [C]
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const int groups = C / V;
+  const int g = threadIdx.x % groups;
+  const int pl = threadIdx.x / groups;
+  const int ppb = blockDim.x / groups;
+  const int c0 = g * V;
+  float sc[V], sh[V], mu[V], is[V], k1[V], k2[V], ab[V];
+  const float invP = 1.f / (float)P;
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    mu[j] = mean[c0 + j]; is[j] = invstd[c0 + j];
+    sc[j] = gamma[c0 + j] * is[j];
+    sh[j] = beta[c0 + j] - mu[j] * sc[j];
+    float s1 = sums[c0 + j], s2 = sums[C + c0 + j];
+    k1[j] = s1 * invP; k2[j] = s2 * invP;
+    ab[j] = 0.f;
+    if (blockIdx.x == 0 && pl == 0) { dbeta[c0 + j] = s1; dgamma[c0 + j] = s2; }
+  }
+  if (pl < ppb) {
+    for (long long op = (long long)blockIdx.x * ppb + pl; op < Pout; op += (long long)gridDim.x * ppb) {
+      long long in[4];
+      window<POOL>(op, H, W, in);
+      float d[V];
+      load_vec<T>(dout + op * C + c0, d);
+      float v[POOL ? 4 : 1][V];
+      float bz[V];
+      int bq[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) { bz[j] = 0.f; bq[j] = -1; }
+#pragma unroll
+      for (int q = 0; q < (POOL ? 4 : 1); ++q) {
+        load_vec<T>(y + in[q] * C + c0, v[q]);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          float z = fmaf(v[q][j], sc[j], sh[j]);
+          if (z > bz[j]) { bz[j] = z; bq[j] = q; }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < (POOL ? 4 : 1); ++q) {
+        float o[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          float dz = (bq[j] == q) ? d[j] : 0.f;
+          float xhat = (v[q][j] - mu[j]) * is[j];
+          o[j] = sc[j] * (dz - k1[j] - xhat * k2[j]);
+          ab[j] += o[j];
+        }
+        store_vec<T>(dy + in[q] * C + c0, o);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) atomicAdd(&sm[c0 + j], ab[j]);
+  }
+  __syncthreads();
+  if (dbias)
+    for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&dbias[i], sm[i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// standalone per-channel statistics (used when the conv kernel did not produce them:
+// SIMT fallback convolutions, unit tests) and standalone 2x2 max-pool fwd/bwd (K-N3, oracle).
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+channel_stats_kernel(const T* __restrict__ y, float* __restrict__ stats, long long P, int C) {
+  constexpr int V = VecOf<T>::N;
+  extern __shared__ float sm[];
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const int groups = C / V;
+  const int g = threadIdx.x % groups, pl = threadIdx.x / groups, ppb = blockDim.x / groups, c0 = g * V;
+  float a1[V], a2[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) { a1[j] = 0.f; a2[j] = 0.f; }
+  if (pl < ppb) {
+    for (long long p = (long long)blockIdx.x * ppb + pl; p < P; p += (long long)gridDim.x * ppb) {
+      float v[V];
+      load_vec<T>(y + p * C + c0, v);
+#pragma unroll
+      for (int j = 0; j < V; ++j) { a1[j] += v[j]; a2[j] += v[j] * v[j]; }
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) { atomicAdd(&sm[c0 + j], a1[j]); atomicAdd(&sm[C + c0 + j], a2[j]); }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&stats[i], sm[i]);
+}
+
+template <typename T>
+__global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ out, long long Pout, int C, int H,
+                                   int W) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Pout * C) return;
+  int c = i % C;
+  long long in[4];
+  window<true>(i / C, H, W, in);
+  float m = to_f32(x[in[0] * C + c]);
+#pragma unroll
+  for (int q = 1; q < 4; ++q) m = fmaxf(m, to_f32(x[in[q] * C + c]));
+  out[i] = from_f32<T>(m);
+}
+
+template <typename T>
+__global__ void maxpool_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dout, T* __restrict__ dx,
+                                   long long Pout, int C, int H, int W) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Pout * C) return;
+  int c = i % C;
+  long long in[4];
+  window<true>(i / C, H, W, in);
+  float m = to_f32(x[in[0] * C + c]);
+  int bq = 0;
+#pragma unroll
+  for (int q = 1; q < 4; ++q) {
+    float v = to_f32(x[in[q] * C + c]);
+    if (v > m) { m = v; bq = q; }
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) dx[in[q] * C + c] = (q == bq) ? dout[i] : from_f32<T>(0.f);
+}
+
+static int bn_grid(long long Pout, int ppb) {
+  long long g = (Pout + ppb - 1) / ppb;
+  const long long cap = 148 * 8;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+template <typename T>
+static int bn_check(int C, int H, int W, bool pool) {
+  constexpr int V = VecOf<T>::N;
+  DDPB_REQUIRE(C % V == 0 && C / V <= 256 && 256 % (C / V) == 0, "bn: unsupported channel count %d", C);
+  DDPB_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "bn: pooling needs even H, W");
+  return DDPB_OK;
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+namespace {
+
+template <typename T, bool POOL>
+int fwd_launch(const void* y, const float* stats, const float* gamma, const float* beta, void* out,
+               float* save_mean, float* save_invstd, float* rm, float* rv, long long* nbt, int batch, int H,
+               int W, int C, int training, float eps, float momentum, cudaStream_t stream) {
+  int rc = bn_check<T>(C, H, W, POOL);
+  if (rc) return rc;
+  long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
+  int ppb = 256 / (C / VecOf<T>::N);
+  bn_fwd_kernel<T, POOL><<<bn_grid(Pout, ppb), 256, 0, stream>>>(
+      (const T*)y, stats, gamma, beta, (T*)out, save_mean, save_invstd, rm, rv, nbt, P, Pout, C, H, W, eps,
+      momentum, training);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+template <typename T, bool POOL>
+int bwd_launch(const void* dout, const void* y, const float* mean, const float* invstd, const float* gamma,
+               const float* beta, float* sums, void* dy, float* dgamma, float* dbeta, float* dbias, int batch,
+               int H, int W, int C, cudaStream_t stream) {
+  int rc = bn_check<T>(C, H, W, POOL);
+  if (rc) return rc;
+  long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
+  int ppb = 256 / (C / VecOf<T>::N);
+  int grid = bn_grid(Pout, ppb);
+  bn_bwd_reduce_kernel<T, POOL><<<grid, 256, 2 * C * sizeof(float), stream>>>(
+      (const T*)dout, (const T*)y, mean, invstd, gamma, beta, sums, Pout, C, H, W);
+  DDPB_LAUNCH_CHECK();
+  bn_bwd_apply_kernel<T, POOL><<<grid, 256, C * sizeof(float), stream>>>(
+      (const T*)dout, (const T*)y, mean, invstd, gamma, beta, sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C,
+      H, W);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+}  // namespace
+
+extern "C" int ddpb_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma, const float* beta,
+                                     void* out, float* save_mean, float* save_invstd, float* running_mean,
+                                     float* running_var, long long* num_batches_tracked, int batch, int H,
+                                     int W, int C, int pool, int training, float eps, float momentum,
+                                     int dtype, cudaStream_t stream) {
+#define ARGS y, stats, gamma, beta, out, save_mean, save_invstd, running_mean, running_var, \
+             num_batches_tracked, batch, H, W, C, training, eps, momentum, stream
+  if (dtype == DDPB_BF16) return pool ? fwd_launch<bf16, true>(ARGS) : fwd_launch<bf16, false>(ARGS);
+  return pool ? fwd_launch<float, true>(ARGS) : fwd_launch<float, false>(ARGS);
+#undef ARGS
+}
+
+// `sums` is a zeroed [2*C] scratch; dgamma/dbeta are overwritten, dbias (may be null) accumulated.
+extern "C" int ddpb_bn_relu_pool_bwd(const void* dout, const void* y, const float* save_mean,
+                                     const float* save_invstd, const float* gamma, const float* beta,
+                                     float* sums, void* dy, float* dgamma, float* dbeta, float* dbias,
+                                     int batch, int H, int W, int C, int pool, int dtype,
+                                     cudaStream_t stream) {
+#define ARGS dout, y, save_mean, save_invstd, gamma, beta, sums, dy, dgamma, dbeta, dbias, batch, H, W, C, stream
+  if (dtype == DDPB_BF16) return pool ? bwd_launch<bf16, true>(ARGS) : bwd_launch<bf16, false>(ARGS);
+  return pool ? bwd_launch<float, true>(ARGS) : bwd_launch<float, false>(ARGS);
+#undef ARGS
+}
+
+// stats[0:C] += sum over pixels, stats[C:2C] += sum of squares (stats must be zeroed by the caller)
+extern "C" int ddpb_channel_stats(const void* y, float* stats, long long pixels, int C, int dtype,
+                                  cudaStream_t stream) {
+  if (dtype == DDPB_BF16) {
+    int rc = bn_check<bf16>(C, 2, 2, false);
+    if (rc) return rc;
+    int ppb = 256 / (C / 8);
+    channel_stats_kernel<bf16><<<bn_grid(pixels, ppb), 256, 2 * C * sizeof(float), stream>>>(
+        (const bf16*)y, stats, pixels, C);
+  } else {
+    int rc = bn_check<float>(C, 2, 2, false);
+    if (rc) return rc;
+    int ppb = 256 / (C / 4);
+    channel_stats_kernel<float><<<bn_grid(pixels, ppb), 256, 2 * C * sizeof(float), stream>>>(
+        (const float*)y, stats, pixels, C);
+  }
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_maxpool2x2_fwd(const void* x, void* out, int batch, int H, int W, int C, int dtype,
+                                   cudaStream_t stream) {
+  long long Pout = (long long)batch * (H / 2) * (W / 2);
+  int blocks = ceil_div(Pout * C, 256);
+  if (dtype == DDPB_BF16)
+    maxpool_fwd_kernel<bf16><<<blocks, 256, 0, stream>>>((const bf16*)x, (bf16*)out, Pout, C, H, W);
+  else
+    maxpool_fwd_kernel<float><<<blocks, 256, 0, stream>>>((const float*)x, (float*)out, Pout, C, H, W);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_maxpool2x2_bwd(const void* x, const void* dout, void* dx, int batch, int H, int W, int C,
+                                   int dtype, cudaStream_t stream) {
+  long long Pout = (long long)batch * (H / 2) * (W / 2);
+  int blocks = ceil_div(Pout * C, 256);
+  if (dtype == DDPB_BF16)
+    maxpool_bwd_kernel<bf16><<<blocks, 256, 0, stream>>>((const bf16*)x, (const bf16*)dout, (bf16*)dx, Pout, C, H, W);
+  else
+    maxpool_bwd_kernel<float><<<blocks, 256, 0, stream>>>((const float*)x, (const float*)dout, (float*)dx, Pout, C, H, W);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}

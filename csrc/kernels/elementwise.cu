@@ -1,0 +1,165 @@
+// Memory-bound helpers: data augmentation, fused SGD, casts, layout changes.
+//
+//  * ddpb_augment         K-D1  uint8 dataset gather + crop(pad 4) + flip + /255 + normalise
+//                               (ref Part 1/main.py:82-93 transforms) -> NHWC fp32/bf16
+//  * ddpb_sgd_step        K-O3  SGD momentum + weight decay over a flat arena
+//                               (ref Part 1/main.py:114-115; torch.optim.SGD semantics)
+//  * ddpb_cast_f32_bf16 / ddpb_fill_f32 / ddpb_nchw_to_nhwc
+#include "../common.cuh"
+#include "../../include/ddp_b200.h"
+
+namespace ddpb {
+
+// ------------------------------------------------------------------------------------------
+// K-D1 augmentation. One thread per output pixel (3 channels).
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void augment_kernel(const uint8_t* __restrict__ images,   // [N,32,32,3]
+                               const int64_t* __restrict__ index,    // [B] rows of `images`, or null
+                               const int32_t* __restrict__ crop_xy,  // [B,2] in [0,8], or null
+                               const uint8_t* __restrict__ flip,     // [B], or null
+                               T* __restrict__ out,                  // [B,32,32,3]
+                               int batch, float m0, float m1, float m2, float s0, float s1, float s2) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= batch * 1024) return;
+  int b = t >> 10, h = (t >> 5) & 31, w = t & 31;
+  long long src = index ? index[b] : b;
+  int ox = crop_xy ? crop_xy[2 * b] - 4 : 0;
+  int oy = crop_xy ? crop_xy[2 * b + 1] - 4 : 0;
+  int ws = (flip && flip[b]) ? 31 - w : w;     // flip happens after the crop
+  int sh = h + oy, sw = ws + ox;
+  float v0 = 0.f, v1 = 0.f, v2 = 0.f;          // zero padding is applied BEFORE normalisation
+  if (sh >= 0 && sh < 32 && sw >= 0 && sw < 32) {
+    const uint8_t* p = images + ((src * 32 + sh) * 32 + sw) * 3;
+    v0 = p[0] / 255.f; v1 = p[1] / 255.f; v2 = p[2] / 255.f;
+  }
+  T* o = out + (size_t)t * 3;
+  o[0] = from_f32<T>((v0 - m0) / s0);
+  o[1] = from_f32<T>((v1 - m1) / s1);
+  o[2] = from_f32<T>((v2 - m2) / s2);
+}
+
+// ------------------------------------------------------------------------------------------
+// K-O3 fused SGD:  g = grad*gscale + wd*p ; buf = mom*buf + g ; p -= lr*buf
+// (momentum buffer starts at zero, which reproduces torch's "buf = g" first step exactly).
+// Optionally refreshes the bf16 compute copy in the same pass.
+// ------------------------------------------------------------------------------------------
+__global__ void sgd_kernel(float* __restrict__ param, float* __restrict__ mom,
+                           const float* __restrict__ grad, bf16* __restrict__ shadow, long long n4,
+                           float lr, float momentum, float wd, float gscale) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n4; i += stride) {
+    float4 p = reinterpret_cast<float4*>(param)[i];
+    float4 m = reinterpret_cast<float4*>(mom)[i];
+    float4 g = reinterpret_cast<const float4*>(grad)[i];
+    g.x = g.x * gscale + wd * p.x; g.y = g.y * gscale + wd * p.y;
+    g.z = g.z * gscale + wd * p.z; g.w = g.w * gscale + wd * p.w;
+    m.x = momentum * m.x + g.x; m.y = momentum * m.y + g.y;
+    m.z = momentum * m.z + g.z; m.w = momentum * m.w + g.w;
+    p.x -= lr * m.x; p.y -= lr * m.y; p.z -= lr * m.z; p.w -= lr * m.w;
+    reinterpret_cast<float4*>(param)[i] = p;
+    reinterpret_cast<float4*>(mom)[i] = m;
+    if (shadow) {
+      uint2 s;
+      s.x = pack_bf16x2(p.x, p.y); s.y = pack_bf16x2(p.z, p.w);
+      reinterpret_cast<uint2*>(shadow)[i] = s;
+    }
+  }
+}
+
+__global__ void cast_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long n4) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n4; i += stride) {
+    float4 p = reinterpret_cast<const float4*>(src)[i];
+    uint2 s;
+    s.x = pack_bf16x2(p.x, p.y); s.y = pack_bf16x2(p.z, p.w);
+    reinterpret_cast<uint2*>(dst)[i] = s;
+  }
+}
+
+__global__ void fill_kernel(float* __restrict__ dst, float v, long long n) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) dst[i] = v;
+}
+
+template <typename TI, typename TO>
+__global__ void nchw_to_nhwc_kernel(const TI* __restrict__ src, TO* __restrict__ dst, int n, int c, int hw) {
+  long long total = (long long)n * c * hw;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int ch = i % c;
+  long long r = i / c;
+  int p = r % hw;
+  int b = r / hw;
+  dst[i] = from_f32<TO>(to_f32(src[((long long)b * c + ch) * hw + p]));
+}
+
+static int grid_for(long long n, int block, int cap = 148 * 16) {
+  long long g = (n + block - 1) / block;
+  if (g < 1) g = 1;
+  return (int)(g > cap ? cap : g);
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+extern "C" int ddpb_augment(const void* images, const void* index, const void* crop_xy, const void* flip,
+                            void* out, int batch, int out_dtype, const float* mean3, const float* std3,
+                            cudaStream_t stream) {
+  DDPB_REQUIRE(batch > 0, "augment: batch must be positive");
+  int threads = 256, blocks = ceil_div((long long)batch * 1024, threads);
+  if (out_dtype == DDPB_BF16) {
+    augment_kernel<bf16><<<blocks, threads, 0, stream>>>(
+        (const uint8_t*)images, (const int64_t*)index, (const int32_t*)crop_xy, (const uint8_t*)flip,
+        (bf16*)out, batch, mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2]);
+  } else {
+    augment_kernel<float><<<blocks, threads, 0, stream>>>(
+        (const uint8_t*)images, (const int64_t*)index, (const int32_t*)crop_xy, (const uint8_t*)flip,
+        (float*)out, batch, mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2]);
+  }
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_sgd_step(float* param, float* mom, const float* grad, void* shadow_bf16, long long n,
+                             float lr, float momentum, float wd, float grad_scale, cudaStream_t stream) {
+  DDPB_REQUIRE(n % 4 == 0, "sgd: element count must be a multiple of 4 (arena slots are 64-aligned)");
+  long long n4 = n / 4;
+  sgd_kernel<<<grid_for(n4, 256), 256, 0, stream>>>(param, mom, grad, (bf16*)shadow_bf16, n4, lr, momentum,
+                                                    wd, grad_scale);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream) {
+  DDPB_REQUIRE(n % 4 == 0, "cast: element count must be a multiple of 4");
+  cast_kernel<<<grid_for(n / 4, 256), 256, 0, stream>>>(src, (bf16*)dst, n / 4);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_fill_f32(float* dst, float value, long long n, cudaStream_t stream) {
+  fill_kernel<<<grid_for(n, 256), 256, 0, stream>>>(dst, value, n);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_nchw_to_nhwc(const void* src, void* dst, int n, int c, int hw, int src_dtype,
+                                 int dst_dtype, cudaStream_t stream) {
+  long long total = (long long)n * c * hw;
+  int blocks = ceil_div(total, 256);
+  if (src_dtype == DDPB_F32 && dst_dtype == DDPB_F32)
+    nchw_to_nhwc_kernel<float, float><<<blocks, 256, 0, stream>>>((const float*)src, (float*)dst, n, c, hw);
+  else if (src_dtype == DDPB_F32 && dst_dtype == DDPB_BF16)
+    nchw_to_nhwc_kernel<float, bf16><<<blocks, 256, 0, stream>>>((const float*)src, (bf16*)dst, n, c, hw);
+  else if (src_dtype == DDPB_BF16 && dst_dtype == DDPB_BF16)
+    nchw_to_nhwc_kernel<bf16, bf16><<<blocks, 256, 0, stream>>>((const bf16*)src, (bf16*)dst, n, c, hw);
+  else
+    DDPB_REQUIRE(false, "nchw_to_nhwc: unsupported dtype pair");
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}

@@ -1,0 +1,134 @@
+// Classifier (Linear 512 -> 10) fused with softmax cross-entropy, forward and backward.
+//
+// Replaces ``self.fc1`` + ``CrossEntropyLoss()`` (ref Part 1/model.py:40,45; Part 1/main.py:39,110;
+// SURVEY K-O1/K-O2).  N = 10 is far too narrow for a tensor-core tile, and the whole problem is
+// B x 512 x 10, so this is a warp-per-sample SIMT kernel:
+//   forward : logits = a W^T + b ; loss += -log softmax[target] / B ; dlogits = (softmax - onehot)/B ;
+//             correct += (argmax == target)          (the eval loop's accuracy count, Part 1/main.py:70-71)
+//   backward: dA = dlogits W ; dW = dlogits^T A ; db = sum_b dlogits
+#include "../common.cuh"
+#include "../../include/ddp_b200.h"
+
+namespace ddpb {
+
+constexpr int NCLS = 10;
+constexpr int FEAT = 512;
+constexpr int FC_SLICE = 16;
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ bias,
+                 const int64_t* __restrict__ target, float* __restrict__ logits, float* __restrict__ dlogits,
+                 float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch) {
+  __shared__ float ws[NCLS * FEAT];
+  for (int i = threadIdx.x; i < NCLS * FEAT; i += blockDim.x) ws[i] = w[i];
+  __syncthreads();
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int b = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (b >= batch) return;
+  float acc[NCLS];
+#pragma unroll
+  for (int j = 0; j < NCLS; ++j) acc[j] = 0.f;
+  const T* a = act + (size_t)b * FEAT;
+  for (int k = lane; k < FEAT; k += 32) {
+    float av = to_f32(a[k]);
+#pragma unroll
+    for (int j = 0; j < NCLS; ++j) acc[j] = fmaf(av, ws[j * FEAT + k], acc[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < NCLS; ++j) acc[j] = warp_sum(acc[j]) + bias[j];
+  // every lane now holds all ten logits
+  float mx = acc[0];
+  int arg = 0;
+#pragma unroll
+  for (int j = 1; j < NCLS; ++j)
+    if (acc[j] > mx) { mx = acc[j]; arg = j; }
+  float se = 0.f;
+#pragma unroll
+  for (int j = 0; j < NCLS; ++j) se += expf(acc[j] - mx);
+  float lse = mx + logf(se);
+  int t = (int)target[b];
+  if (lane == 0) {
+    float lt = 0.f;
+#pragma unroll
+    for (int j = 0; j < NCLS; ++j) {
+      float p = expf(acc[j] - lse);
+      if (logits) logits[b * NCLS + j] = acc[j];
+      if (dlogits) dlogits[b * NCLS + j] = (p - (j == t ? 1.f : 0.f)) * inv_batch;
+      if (j == t) lt = acc[j];
+    }
+    atomicAdd(loss, (lse - lt) * inv_batch);
+    if (correct && arg == t) atomicAdd(correct, 1);
+  }
+}
+
+// blocks [0, batch*FEAT/256): dA ; remaining blocks: dW and db (one thread per (class, feature))
+template <typename T>
+__global__ void __launch_bounds__(256)
+fc_bwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ dlogits,
+              T* __restrict__ dact, float* __restrict__ dw, float* __restrict__ db, int batch, int blocks_da) {
+  if ((int)blockIdx.x < blocks_da) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= batch * FEAT) return;
+    int b = i / FEAT, k = i % FEAT;
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NCLS; ++j) s = fmaf(dlogits[b * NCLS + j], w[j * FEAT + k], s);
+    dact[i] = from_f32<T>(s);
+  } else {
+    // dW/db: the batch is cut into slices of FC_SLICE samples, partial sums are accumulated
+    // atomically into the (pre-zeroed) gradient arena.
+    int rel = blockIdx.x - blocks_da;
+    int per = (NCLS * FEAT + NCLS + 255) / 256;
+    int slice = rel / per;
+    int i = (rel % per) * blockDim.x + threadIdx.x;
+    int b0 = slice * FC_SLICE, b1 = min(batch, b0 + FC_SLICE);
+    if (i < NCLS * FEAT) {
+      int j = i / FEAT, k = i % FEAT;
+      float s = 0.f;
+      for (int b = b0; b < b1; ++b) s = fmaf(dlogits[b * NCLS + j], to_f32(act[(size_t)b * FEAT + k]), s);
+      atomicAdd(&dw[i], s);
+    } else if (i < NCLS * FEAT + NCLS) {
+      int j = i - NCLS * FEAT;
+      float s = 0.f;
+      for (int b = b0; b < b1; ++b) s += dlogits[b * NCLS + j];
+      atomicAdd(&db[j], s);
+    }
+  }
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+// `loss` (1 float) and `correct` (1 int, may be null) are ACCUMULATED into: zero them first.
+extern "C" int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias, const void* target_i64,
+                              float* logits, float* dlogits, float* loss, int* correct, int batch,
+                              int loss_divisor, int dtype, cudaStream_t stream) {
+  DDPB_REQUIRE(batch > 0 && loss_divisor > 0, "fc_ce_fwd: bad batch");
+  int blocks = ceil_div(batch, 8);
+  float inv = 1.f / (float)loss_divisor;
+  if (dtype == DDPB_BF16)
+    fc_ce_fwd_kernel<bf16><<<blocks, 256, 0, stream>>>((const bf16*)act, w, bias, (const int64_t*)target_i64,
+                                                      logits, dlogits, loss, correct, batch, inv);
+  else
+    fc_ce_fwd_kernel<float><<<blocks, 256, 0, stream>>>((const float*)act, w, bias, (const int64_t*)target_i64,
+                                                       logits, dlogits, loss, correct, batch, inv);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+// dw [10*512] and db [10] are ACCUMULATED into (they live in the zeroed gradient arena).
+extern "C" int ddpb_fc_bwd(const void* act, const float* w, const float* dlogits, void* dact, float* dw,
+                           float* db, int batch, int dtype, cudaStream_t stream) {
+  int blocks_da = ceil_div((long long)batch * FEAT, 256);
+  int blocks_dw = ceil_div(NCLS * FEAT + NCLS, 256) * ceil_div(batch, FC_SLICE);
+  if (dtype == DDPB_BF16)
+    fc_bwd_kernel<bf16><<<blocks_da + blocks_dw, 256, 0, stream>>>((const bf16*)act, w, dlogits, (bf16*)dact, dw,
+                                                                  db, batch, blocks_da);
+  else
+    fc_bwd_kernel<float><<<blocks_da + blocks_dw, 256, 0, stream>>>((const float*)act, w, dlogits, (float*)dact,
+                                                                   dw, db, batch, blocks_da);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}

@@ -1,0 +1,184 @@
+// conv3x3 weight gradient as a split-K implicit GEMM on tcgen05 tensor cores.
+//
+// Replaces autograd's conv weight gradient (ref Part 1/model.py:18-23 backward; SURVEY K-C3).
+//
+//   dW[co, tap, ci] = sum_p dY[p, co] * X[p + shift(tap), ci]          M = Cout, N = Cin (per tap), K = pixels
+//
+// The reduction dimension (pixels) is the SLOW dimension of both NHWC operands, so both are
+// MN-major UMMA operands: a TMA box of 64 pixels x 64 channels is 64 rows of 128 B, which with the
+// 128-byte swizzle is exactly the canonical MN-major layout (8-row K groups 1024 B apart).  The
+// shifted X tile comes from the same trick as fprop: move the box by (s-1, r-1) and let TMA
+// zero-fill what falls outside the image.
+//
+// One CTA owns: 128 output channels x 64 input channels x the three taps of one filter row
+// (3 accumulators of 64 TMEM columns that share every dY tile), over one slice of the pixels
+// (split-K).  Partial results are added to the fp32 gradient with vectorised RED
+// (red.global.add.v4.f32) straight into the gradient arena in KRSC order, i.e. the buffer the
+// peer-to-peer reduce kernels and the fused SGD read - there is no staging copy.
+#include "../common.cuh"
+#include "../../include/ddp_b200.h"
+#include "../runtime/tensormap.h"
+
+namespace ddpb {
+
+constexpr int WG_M = 128;            // output channels per CTA
+constexpr int WG_N = 64;             // input channels per CTA (per tap)
+constexpr int WG_K = 64;             // pixels per pipeline stage
+constexpr int WG_TAPS = 3;           // taps per CTA (one filter row)
+constexpr int WG_BOX = WG_K * 128;   // bytes of one 64x64 bf16 box
+constexpr int WG_STAGE = (WG_M / 64 + WG_TAPS) * WG_BOX;     // 2 dY boxes + 3 X boxes = 40 KB
+constexpr int WG_TMEM_COLS = 256;    // 3 x 64 used
+
+struct WgradParams {
+  int H, W;
+  int chunks_per_img;   // >= 1 when H*W >= 64 else 0
+  int imgs_per_chunk;   // >= 1 when H*W <= 64
+  int rows_per_chunk;
+  int total_chunks;     // ceil(B*H*W / 64)
+  int Cin, Cout;
+};
+
+void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn);   // conv_tc.cu
+
+template <int STAGES>
+__global__ void __launch_bounds__(192)
+wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+                float* __restrict__ dw, const WgradParams prm) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * WG_STAGE);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* accum_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int co_blk = blockIdx.x / (prm.Cin / WG_N), ci_blk = blockIdx.x % (prm.Cin / WG_N);
+  const int r = blockIdx.y;                      // filter row
+  const int split = blockIdx.z, nsplit = gridDim.z;
+  const int chunk_lo = (int)((long long)prm.total_chunks * split / nsplit);
+  const int chunk_hi = (int)((long long)prm.total_chunks * (split + 1) / nsplit);
+  const int k_iters = chunk_hi - chunk_lo;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmDY);
+    tma_prefetch_desc(&tmX);
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(accum_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<WG_TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (k_iters > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        for (int it = 0; it < k_iters; ++it) {
+          const int stage = it % STAGES, use = it / STAGES;
+          if (use > 0) mbar_wait(&empty_bar[stage], (use - 1) & 1);
+          const int chunk = chunk_lo + it;
+          int n0, h0;
+          if (prm.chunks_per_img > 0) { n0 = chunk / prm.chunks_per_img; h0 = (chunk % prm.chunks_per_img) * prm.rows_per_chunk; }
+          else { n0 = chunk * prm.imgs_per_chunk; h0 = 0; }
+          uint8_t* s = smem + stage * WG_STAGE;
+          mbar_expect_tx(&full_bar[stage], WG_STAGE);
+          tma_load_4d(s, &tmDY, &full_bar[stage], co_blk * WG_M, 0, h0, n0);
+          tma_load_4d(s + WG_BOX, &tmDY, &full_bar[stage], co_blk * WG_M + 64, 0, h0, n0);
+#pragma unroll
+          for (int t = 0; t < WG_TAPS; ++t)
+            tma_load_4d(s + (2 + t) * WG_BOX, &tmX, &full_bar[stage], ci_blk * WG_N, t - 1, h0 + r - 1, n0);
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        constexpr uint32_t idesc = umma_idesc_bf16(WG_M, WG_N, true, true);
+        for (int it = 0; it < k_iters; ++it) {
+          const int stage = it % STAGES, use = it / STAGES;
+          mbar_wait(&full_bar[stage], use & 1);
+          tc_fence_after();
+          const uint32_t s = smem_u32(smem + stage * WG_STAGE);
+#pragma unroll
+          for (int kk = 0; kk < WG_K / 16; ++kk) {
+            // MN-major A: two 64-channel blocks WG_BOX apart (LBO), 8-pixel groups 1024 B apart (SBO)
+            const uint64_t da = umma_desc(s + kk * 2048, WG_BOX, 1024);
+#pragma unroll
+            for (int t = 0; t < WG_TAPS; ++t) {
+              const uint64_t db = umma_desc(s + (2 + t) * WG_BOX + kk * 2048, WG_BOX, 1024);
+              umma_bf16(tmem_base + t * WG_N, da, db, idesc, (it | kk) != 0);
+            }
+          }
+          umma_commit(&empty_bar[stage]);
+        }
+        umma_commit(accum_bar);
+      }
+    } else {
+      const int q = warp & 3;
+      const int co = co_blk * WG_M + q * 32 + lane;
+      mbar_wait(accum_bar, 0);
+      tc_fence_after();
+#pragma unroll 1
+      for (int t = 0; t < WG_TAPS; ++t) {
+        float* dst = dw + ((long long)co * 9 + (r * 3 + t)) * prm.Cin + ci_blk * WG_N;
+#pragma unroll 1
+        for (int c = 0; c < WG_N; c += 32) {
+          float v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + t * WG_N + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) red_add_v4(dst + c + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<WG_TMEM_COLS>(tmem_base);
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+// dw (fp32 [Cout,3,3,Cin], KRSC) += dy^T * shifted(x).  dw is ACCUMULATED into (split-K partials
+// and the caller's zeroed gradient arena).  split_k = 0 picks a split that fills ~148 SMs.
+extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
+                                     int Cout, int split_k, cudaStream_t stream) {
+  DDPB_REQUIRE(B > 0 && H == W && (H == 32 || H == 16 || H == 8 || H == 4 || H == 2),
+               "wgrad_tc: unsupported spatial size %dx%d", H, W);
+  DDPB_REQUIRE(Cin % 64 == 0 && Cout % 128 == 0, "wgrad_tc: need Cin %% 64 == 0 and Cout %% 128 == 0 (got %d, %d)",
+               Cin, Cout);
+  int bw, bh, bn;
+  pixel_box(H, W, WG_K, &bw, &bh, &bn);
+  CUtensorMap tmDY, tmX;
+  int rc = make_tmap_nhwc_bf16(&tmDY, dy, B, H, W, Cout, 64, bw, bh, bn);
+  if (rc) return rc;
+  rc = make_tmap_nhwc_bf16(&tmX, x, B, H, W, Cin, 64, bw, bh, bn);
+  if (rc) return rc;
+  WgradParams prm;
+  prm.H = H; prm.W = W;
+  prm.chunks_per_img = H * W >= WG_K ? H * W / WG_K : 0;
+  prm.imgs_per_chunk = H * W >= WG_K ? 0 : WG_K / (H * W);
+  prm.rows_per_chunk = bh;
+  prm.total_chunks = prm.chunks_per_img > 0 ? B * prm.chunks_per_img : ceil_div(B, prm.imgs_per_chunk);
+  prm.Cin = Cin; prm.Cout = Cout;
+  int base_ctas = (Cout / WG_M) * (Cin / WG_N) * 3;
+  if (split_k <= 0) {
+    split_k = (148 + base_ctas - 1) / base_ctas;
+    if (split_k > prm.total_chunks / 4) split_k = prm.total_chunks / 4;     // keep >= 4 chunks per CTA
+    if (split_k < 1) split_k = 1;
+  }
+  if (split_k > prm.total_chunks) split_k = prm.total_chunks;
+  constexpr int STAGES = 4;
+  constexpr int smem = STAGES * WG_STAGE + (2 * STAGES + 1) * 8 + 16 + 1024;
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CUDA_CHECK(cudaFuncSetAttribute(wgrad_tc_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(base_ctas / 3, 3, split_k);
+  wgrad_tc_kernel<STAGES><<<grid, 192, smem, stream>>>(tmDY, tmX, dw, prm);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}

@@ -1,0 +1,140 @@
+/* C ABI of libddpb200.so - the sm_100a engine of the B200 data-parallel framework.
+ *
+ * Conventions
+ *   - every function returns 0 on success; on failure ddpb_last_error() describes the problem;
+ *   - activations are NHWC, conv weights KRSC (= [Cout][3][3][Cin]); `dtype` is DDPB_F32/DDPB_BF16;
+ *   - all work is enqueued on `stream`; nothing synchronises the device;
+ *   - functions documented as "accumulates" add into their output (zero it first);
+ *   - no function allocates device memory unless its comment says so.
+ * Reference citations (ref ...) are relative to /root/reference/src/.
+ */
+#ifndef DDP_B200_H_
+#define DDP_B200_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDPB_F32 0
+#define DDPB_BF16 1
+
+#define DDPB_MAX_RANKS 8
+#define DDPB_P2P_MAX_BLOCKS 64
+#define DDPB_P2P_MAX_SLOTS 64
+
+#define DDPB_P2P_ONESHOT 0
+#define DDPB_P2P_TWOSHOT 1
+#define DDPB_P2P_ROOT 2
+#define DDPB_P2P_BCAST 3
+#define DDPB_P2P_ALLGATHER 4
+
+const char* ddpb_last_error(void);
+
+/* ---- data / optimizer / layout (csrc/kernels/elementwise.cu) ------------------------------ */
+
+/* Gather `batch` images (rows `index`, or 0..batch-1 when null) of a uint8 [N,32,32,3] dataset,
+ * apply RandomCrop(32, pad 4) with offsets crop_xy[b] in [0,8] (null: none), horizontal flip
+ * (null: none), /255 and per-channel normalisation; write NHWC.  ref Part 1/main.py:82-93. */
+int ddpb_augment(const void* images_u8, const void* index_i64, const void* crop_xy_i32, const void* flip_u8,
+                 void* out, int batch, int out_dtype, const float* mean3, const float* std3, cudaStream_t stream);
+
+/* SGD with momentum and weight decay over a flat range (torch.optim.SGD semantics, dampening 0,
+ * no Nesterov; ref Part 1/main.py:114-115): g = grad*grad_scale + wd*p; m = momentum*m + g;
+ * p -= lr*m.  Refreshes the bf16 copy when shadow_bf16 is non-null.  n must be a multiple of 4. */
+int ddpb_sgd_step(float* param, float* mom, const float* grad, void* shadow_bf16, long long n, float lr,
+                  float momentum, float wd, float grad_scale, cudaStream_t stream);
+
+int ddpb_cast_f32_bf16(const float* src, void* dst_bf16, long long n, cudaStream_t stream);
+int ddpb_fill_f32(float* dst, float value, long long n, cudaStream_t stream);
+int ddpb_nchw_to_nhwc(const void* src, void* dst, int n, int c, int hw, int src_dtype, int dst_dtype,
+                      cudaStream_t stream);
+
+/* ---- BatchNorm + ReLU (+ 2x2 max-pool) (csrc/kernels/bn_relu_pool.cu) --------------------- */
+
+/* ref Part 1/model.py:16,24-25.  y: conv output [batch,H,W,C]; stats: [2C] per-channel sum and
+ * sum of squares of y (training); out: [batch,H(/2),W(/2),C].  Training mode also writes
+ * save_mean/save_invstd and updates running stats (momentum, unbiased variance) and the
+ * batch counter; eval mode normalises with the running statistics. */
+int ddpb_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma, const float* beta, void* out,
+                          float* save_mean, float* save_invstd, float* running_mean, float* running_var,
+                          long long* num_batches_tracked, int batch, int H, int W, int C, int pool, int training,
+                          float eps, float momentum, int dtype, cudaStream_t stream);
+
+/* Backward of the above.  sums: zeroed [2C] scratch.  dgamma/dbeta are written; dbias (gradient of
+ * the conv bias that precedes the BN, may be null) is accumulated. */
+int ddpb_bn_relu_pool_bwd(const void* dout, const void* y, const float* save_mean, const float* save_invstd,
+                          const float* gamma, const float* beta, float* sums, void* dy, float* dgamma,
+                          float* dbeta, float* dbias, int batch, int H, int W, int C, int pool, int dtype,
+                          cudaStream_t stream);
+
+/* stats[0:C] += sum, stats[C:2C] += sum of squares over `pixels` rows of y (accumulates). */
+int ddpb_channel_stats(const void* y, float* stats, long long pixels, int C, int dtype, cudaStream_t stream);
+
+int ddpb_maxpool2x2_fwd(const void* x, void* out, int batch, int H, int W, int C, int dtype, cudaStream_t stream);
+int ddpb_maxpool2x2_bwd(const void* x, const void* dout, void* dx, int batch, int H, int W, int C, int dtype,
+                        cudaStream_t stream);
+
+/* ---- classifier + cross-entropy (csrc/kernels/fc_ce.cu) ----------------------------------- */
+
+/* ref Part 1/model.py:40,45 and Part 1/main.py:39,70-71.  act: [batch,512]; w: fp32 [10,512].
+ * loss (1 float) accumulates sum_b CE_b / loss_divisor; correct (1 int, may be null) accumulates
+ * the number of argmax hits; logits/dlogits ([batch,10] fp32) may be null. */
+int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias, const void* target_i64, float* logits,
+                   float* dlogits, float* loss, int* correct, int batch, int loss_divisor, int dtype,
+                   cudaStream_t stream);
+
+/* dact [batch,512] is written; dw [10,512] and db [10] accumulate. */
+int ddpb_fc_bwd(const void* act, const float* w, const float* dlogits, void* dact, float* dw, float* db,
+                int batch, int dtype, cudaStream_t stream);
+
+/* ---- convolutions ------------------------------------------------------------------------- */
+
+/* SIMT fp32-accumulate kernels with fp32 weights (csrc/kernels/conv_direct.cu): the fp32 parity
+ * path, the oracle for the tensor-core kernels, and the Cin=3 first layer (dedicated kernels).
+ * ref Part 1/model.py:18-23.  stats (may be null) accumulates per-channel sum / sum of squares. */
+int ddpb_conv3x3_fwd_simt(const void* x, const float* w, const float* bias, void* y, float* stats, int B, int H,
+                          int W, int Cin, int Cout, int dtype, cudaStream_t stream);
+int ddpb_conv3x3_dgrad_simt(const void* dy, const float* w, void* dx, int B, int H, int W, int Cin, int Cout,
+                            int dtype, cudaStream_t stream);
+/* dw accumulates. */
+int ddpb_conv3x3_wgrad_simt(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                            int dtype, cudaStream_t stream);
+
+/* tcgen05 / TMEM / TMA implicit-GEMM kernels, bf16 operands, fp32 accumulation
+ * (csrc/kernels/conv_tc.cu, wgrad_tc.cu).  Cin, Cout multiples of 64 (wgrad: Cout of 128);
+ * H = W in {2,4,8,16,32}.  tile_n / split_k = 0 choose automatically. */
+int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats, int B, int H,
+                        int W, int Cin, int Cout, int tile_n, cudaStream_t stream);
+int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* dx, int B, int H, int W, int Cin, int Cout,
+                          int tile_n, cudaStream_t stream);
+/* dw (fp32 KRSC) accumulates. */
+int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                          int split_k, cudaStream_t stream);
+
+/* ---- peer-to-peer gradient engine (csrc/kernels/sync_p2p.cu, csrc/runtime/symm_mem.cpp) --- */
+
+/* One fused reduce(+SGD) / broadcast / all-gather step over elements [off, off+n) of the symmetric
+ * arenas; pointer tables have `world` entries indexed by rank.  Replaces dist.gather/scatter
+ * (ref Part 2a/main.py:117-127), dist.all_reduce + divide (ref Part 2b/main.py:116-119) and DDP's
+ * bucket all-reduce / broadcasts (ref Part 3/main.py:61), each fused with optimizer.step()
+ * (ref Part 2a/main.py:96).  flags == null disables the cross-rank barriers.  `blocks` = 0 picks. */
+int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, void* const* shadow, void* const* flags,
+                  float* mom, void* epochs, int rank, int world, int slot, long long off, long long n, float lr,
+                  float momentum, float wd, int blocks, cudaStream_t stream);
+
+/* Symmetric memory: ALLOCATES `bytes` of zeroed device memory with cudaMalloc on the current
+ * device and returns it with a 64-byte IPC handle that peers open with ddpb_symm_open. */
+int ddpb_symm_alloc(size_t bytes, void** ptr, void* handle64);
+int ddpb_symm_open(const void* handle64, void** peer_ptr);
+int ddpb_symm_close(void* peer_ptr);
+int ddpb_symm_free(void* ptr);
+/* Enable peer access from the current device to `peer_device` (same-process multi-GPU tests). */
+int ddpb_enable_peer_access(int peer_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDP_B200_H_ */

@@ -1,0 +1,233 @@
+"""Numerics of every native kernel against a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def F():
+    from cs744_ddp_b200.ops import functional
+    return functional
+
+
+@pytest.fixture(scope="module")
+def R():
+    from cs744_ddp_b200.ops import reference
+    return reference
+
+
+def _rel_err(a, b):
+    a, b = a.float(), b.float()
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+def _report(name, got, ref, tol):
+    err = _rel_err(got, ref)
+    maxabs = float((got.float() - ref.float()).abs().max())
+    print(f"[num] {name}: rel_l2={err:.3e} max_abs={maxabs:.3e} ref_max={float(ref.abs().max()):.3e}")
+    assert err < tol, f"{name}: rel l2 error {err:.3e} >= {tol}"
+
+
+# ----------------------------------------------------------------------------------------------
+def test_native_library_is_loaded(F):
+    from cs744_ddp_b200.ops import native
+    assert native.available()
+    maps = open("/proc/self/maps").read()
+    assert "libddpb200.so" in maps
+
+
+def test_augment_matches_torch_pipeline(F):
+    from cs744_ddp_b200.data import synthetic_cifar10, transform_batch
+    from cs744_ddp_b200.data.pipeline import RawBatch
+    split = synthetic_cifar10(64, seed=1).to(DEV)
+    g = torch.Generator().manual_seed(0)
+    idx = torch.randperm(64, generator=g)[:40].to(DEV)
+    crop = torch.randint(0, 9, (40, 2), generator=g, dtype=torch.int32).to(DEV)
+    flip = (torch.rand(40, generator=g) < 0.5).to(torch.uint8).to(DEV)
+    ref = transform_batch(RawBatch(split.images[idx], split.labels[idx], crop, flip), layout="nhwc")
+    out = F.augment(split.images, idx, crop, flip, torch.float32)
+    assert torch.allclose(out, ref, atol=1e-6)
+    out16 = F.augment(split.images, idx, crop, flip, torch.bfloat16)
+    assert torch.allclose(out16.float(), ref, atol=2e-2, rtol=1e-2)
+    plain = F.augment(split.images, None, None, None, torch.float32, batch=64)
+    ref2 = transform_batch(RawBatch(split.images, split.labels, None, None), layout="nhwc")
+    assert torch.allclose(plain, ref2, atol=1e-6)
+
+
+def test_sgd_matches_torch_optim(F):
+    n = 64 * 100
+    p0 = torch.randn(n, device=DEV)
+    p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.SGD([p], lr=0.1, momentum=0.9, weight_decay=1e-4)
+    mine, mom = p0.clone(), torch.zeros(n, device=DEV)
+    shadow = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    for step in range(4):
+        g = torch.randn(n, device=DEV)
+        p.grad = g.clone()
+        opt.step()
+        F.sgd_step(mine, mom, g, shadow, 0.1, 0.9, 1e-4)
+        assert torch.allclose(mine, p.data, rtol=1e-6, atol=1e-7), step
+    assert torch.equal(shadow, mine.to(torch.bfloat16))
+    assert torch.allclose(mom, opt.state[p]["momentum_buffer"], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("c,hw,pool", [(64, 32, True), (256, 8, False), (512, 2, True), (128, 16, True)])
+def test_bn_relu_pool_forward_backward(F, R, dtype, c, hw, pool):
+    torch.manual_seed(0)
+    b = 6
+    y = (torch.randn(b, hw, hw, c, device=DEV) * 1.5 + 0.3).to(dtype)
+    gamma = torch.rand(c, device=DEV) + 0.5
+    beta = torch.randn(c, device=DEV) * 0.2
+    rm, rv = torch.randn(c, device=DEV) * 0.1, torch.rand(c, device=DEV) + 0.5
+    nbt = torch.zeros(1, dtype=torch.int64, device=DEV)
+    stats = F.channel_stats(y)
+    _report("channel_stats", stats, R.channel_stats(y), 1e-5)
+    rm_n, rv_n = rm.clone(), rv.clone()
+    out, mean, invstd = F.bn_relu_pool_fwd(y, stats, gamma, beta, rm_n, rv_n, nbt, pool, True)
+    ref_out, ref_rm, ref_rv = R.bn_relu_pool_fwd(y, gamma, beta, rm, rv, pool, True)
+    tol = 1e-5 if dtype == torch.float32 else 6e-3
+    _report("bn_fwd", out, ref_out, tol)
+    _report("running_mean", rm_n, ref_rm, 1e-5)
+    _report("running_var", rv_n, ref_rv, 1e-5)
+    assert int(nbt) == 1
+    # eval mode uses the running statistics
+    out_e, _, _ = F.bn_relu_pool_fwd(y, None, gamma, beta, rm_n, rv_n, None, pool, False)
+    ref_e, _, _ = R.bn_relu_pool_fwd(y, gamma, beta, rm_n, rv_n, pool, False)
+    _report("bn_eval", out_e, ref_e, tol)
+    # backward
+    dout = torch.randn_like(out.float()).to(dtype)
+    dbias = torch.zeros(c, device=DEV)
+    dy, dgamma, dbeta = F.bn_relu_pool_bwd(dout, y, mean, invstd, gamma, beta, pool, dbias)
+    rdy, rdg, rdb = R.bn_relu_pool_bwd(dout, y, gamma, beta, pool)
+    btol = 2e-4 if dtype == torch.float32 else 1.5e-2
+    _report("bn_bwd_dy", dy, rdy, btol)
+    _report("bn_bwd_dgamma", dgamma, rdg, btol)
+    _report("bn_bwd_dbeta", dbeta, rdb, btol)
+    # conv-bias gradient = column sums of dy (mathematically ~0)
+    assert float(dbias.abs().max()) < 1e-2 * max(1.0, float(dy.float().abs().sum(dim=(0, 1, 2)).max()))
+
+
+def test_maxpool_standalone(F):
+    x = torch.randn(4, 8, 8, 64, device=DEV)
+    out = F.maxpool_fwd(x)
+    ref = torch.nn.functional.max_pool2d(x.permute(0, 3, 1, 2), 2, 2).permute(0, 2, 3, 1)
+    assert torch.equal(out, ref.contiguous())
+    dout = torch.randn_like(out)
+    xr = x.clone().requires_grad_(True)
+    torch.nn.functional.max_pool2d(xr.permute(0, 3, 1, 2), 2, 2).backward(dout.permute(0, 3, 1, 2))
+    assert torch.equal(F.maxpool_bwd(x, dout), xr.grad)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("b", [256, 10])
+def test_fc_cross_entropy(F, R, dtype, b):
+    torch.manual_seed(1)
+    act = torch.randn(b, 512, device=DEV).to(dtype)
+    w = torch.randn(10, 512, device=DEV) * 0.05
+    bias = torch.randn(10, device=DEV) * 0.1
+    tgt = torch.randint(0, 10, (b,), device=DEV)
+    logits, dlogits, loss, correct = F.fc_ce_fwd(act, w, bias, tgt)
+    rl, rloss, rdl, rda, rdw, rdb, rc = R.fc_ce(act, w, bias, tgt)
+    _report("fc_logits", logits, rl, 1e-5)
+    assert abs(float(loss) - float(rloss)) < 1e-4 * max(1.0, abs(float(rloss)))
+    _report("fc_dlogits", dlogits, rdl, 1e-4)
+    assert int(correct) == int(rc)
+    dact, dw, db = F.fc_bwd(act, w, dlogits)
+    tol = 1e-4 if dtype == torch.float32 else 6e-3
+    _report("fc_dact", dact, rda, tol)
+    _report("fc_dw", dw, rdw, 1e-4)
+    _report("fc_db", db, rdb, 1e-4)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("b,hw,cin,cout", [(4, 32, 3, 64), (3, 8, 16, 32), (5, 4, 32, 16)])
+def test_conv_simt(F, R, dtype, b, hw, cin, cout):
+    torch.manual_seed(2)
+    x = torch.randn(b, hw, hw, cin, device=DEV).to(dtype)
+    w = torch.randn(cout, 3, 3, cin, device=DEV) * 0.1
+    bias = torch.randn(cout, device=DEV) * 0.1
+    tol = 1e-5 if dtype == torch.float32 else 6e-3
+    y, stats = F.conv_fwd_simt(x, w, bias, want_stats=True)
+    _report("simt_stats", stats, R.channel_stats(y), 1e-4)
+    _report("simt_fwd", y, R.conv_fwd(x, w, bias), tol)
+    dy = torch.randn(b, hw, hw, cout, device=DEV).to(dtype)
+    _report("simt_dgrad", F.conv_dgrad_simt(dy, w), R.conv_dgrad(dy, w), tol)
+    _report("simt_wgrad", F.conv_wgrad_simt(dy, x), R.conv_wgrad(dy, x), 1e-4)
+
+
+TC_SHAPES = [  # (hw, cin, cout) of VGG-11 blocks 1..7
+    (16, 64, 128), (8, 128, 256), (8, 256, 256), (4, 256, 512), (4, 512, 512), (2, 512, 512)]
+
+
+@pytest.mark.parametrize("b", [16, 10])
+@pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
+@pytest.mark.parametrize("tile_n", [64, 128])
+def test_conv_tc_forward(F, R, b, hw, cin, cout, tile_n):
+    torch.manual_seed(3)
+    x = torch.randn(b, hw, hw, cin, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(cout, 3, 3, cin, device=DEV) * 0.05).to(torch.bfloat16)
+    bias = torch.randn(cout, device=DEV) * 0.1
+    y, stats = F.conv_fwd_tc(x, w, bias, want_stats=True, tile_n=tile_n)
+    torch.cuda.synchronize()
+    ref = R.conv_fwd(x, w, bias)
+    _report(f"tc_fwd hw{hw} {cin}->{cout} b{b} n{tile_n}", y, ref, 6e-3)
+    _report("tc_fwd_stats", stats, R.channel_stats(y), 1e-3)
+
+
+@pytest.mark.parametrize("b", [16, 10])
+@pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
+@pytest.mark.parametrize("tile_n", [64, 128])
+def test_conv_tc_dgrad(F, R, b, hw, cin, cout, tile_n):
+    torch.manual_seed(4)
+    dy = torch.randn(b, hw, hw, cout, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(cout, 3, 3, cin, device=DEV) * 0.05).to(torch.bfloat16)
+    dx = F.conv_dgrad_tc(dy, w, tile_n=tile_n)
+    torch.cuda.synchronize()
+    _report(f"tc_dgrad hw{hw} {cin}->{cout} b{b} n{tile_n}", dx, R.conv_dgrad(dy, w), 6e-3)
+
+
+@pytest.mark.parametrize("b", [16, 10])
+@pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
+@pytest.mark.parametrize("split_k", [0, 1, 3])
+def test_conv_tc_wgrad(F, R, b, hw, cin, cout, split_k):
+    torch.manual_seed(5)
+    dy = torch.randn(b, hw, hw, cout, device=DEV).to(torch.bfloat16)
+    x = torch.randn(b, hw, hw, cin, device=DEV).to(torch.bfloat16)
+    dw = F.conv_wgrad_tc(dy, x, split_k=split_k)
+    torch.cuda.synchronize()
+    _report(f"tc_wgrad hw{hw} {cin}->{cout} b{b} s{split_k}", dw, R.conv_wgrad(dy, x), 2e-3)
+
+
+@pytest.mark.parametrize("mode_name", ["oneshot", "twoshot", "root"])
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_p2p_reduce_sgd_single_gpu_emulation(F, mode_name, world):
+    """All 'ranks' live on one GPU and run one after the other with the barriers disabled: checks
+    the reduction order, slicing, SGD epilogue and the push of weights to every replica."""
+    from cs744_ddp_b200.ops import native as nv
+    mode = {"oneshot": nv.P2P_ONESHOT, "twoshot": nv.P2P_TWOSHOT, "root": nv.P2P_ROOT}[mode_name]
+    torch.manual_seed(6)
+    n, off = 4 * 1000 + 64, 64
+    total = off + n + 64
+    grads = [torch.randn(total, device=DEV) for _ in range(world)]
+    p0 = torch.randn(total, device=DEV)
+    masters = [p0.clone() for _ in range(world)]
+    shadows = [torch.zeros(total, device=DEV, dtype=torch.bfloat16) for _ in range(world)]
+    moms = [torch.zeros(total, device=DEV) for _ in range(world)]
+    for r in range(world):
+        F.p2p_sync(mode, [g.data_ptr() for g in grads], [m.data_ptr() for m in masters],
+                   [s.data_ptr() for s in shadows], None, moms[r], None, r, world, 0, off, n, 0.1, 0.9, 1e-4)
+    torch.cuda.synchronize()
+    mean_g = torch.stack(grads).sum(0) / world if mode_name != "root" else torch.stack(grads).mean(0)
+    g = mean_g + 1e-4 * p0
+    ref = p0 - 0.1 * g
+    for r in range(world):
+        assert torch.allclose(masters[r][off:off + n], ref[off:off + n], rtol=1e-5, atol=1e-6), (mode_name, r)
+        assert torch.equal(masters[r][:off], p0[:off]) and torch.equal(masters[r][off + n:], p0[off + n:])
+        assert torch.equal(shadows[r][off:off + n], masters[r][off:off + n].to(torch.bfloat16))
+    # every replica must hold bit-identical weights
+    for r in range(1, world):
+        assert torch.equal(masters[0], masters[r])

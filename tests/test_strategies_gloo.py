@@ -57,7 +57,7 @@ def _worker(rank, port, strategy, outdir, use_torch_ddp):
         if step == 0:
             first_grads = {n.replace("module.", ""): p.grad.clone() for n, p in model.named_parameters()}
         opt.step()
-        losses.append(float(loss))
+        losses.append(float(loss.detach()))
     sd = {k.replace("module.", ""): v.clone() for k, v in model.state_dict().items()}
     torch.save({"sd": sd, "losses": losses, "grads": first_grads,
                 "launch_log": getattr(strat, "launch_log", None)},
@@ -96,7 +96,7 @@ def test_averaged_gradient_is_mean_over_ranks(runs):
     for strat in ("gather_scatter", "allreduce", "bucketed"):
         for rank in range(WORLD):
             for n, g in runs[strat][rank]["grads"].items():
-                assert torch.allclose(g, oracle[n], rtol=1e-5, atol=1e-7), (strat, rank, n)
+                assert torch.allclose(g, oracle[n], rtol=1e-4, atol=1e-5), (strat, rank, n)
 
 
 def test_three_strategies_agree_bitwise_at_world_2(runs):
