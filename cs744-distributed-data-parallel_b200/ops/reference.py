@@ -1,4 +1,4 @@
-"""Plain PyTorch fp32 references of the native ops, on the engine's layouts (NHWC / KRSC).
+"""Plain PyTorch references (computed in float64, returned as fp32) of the native ops, on the engine's layouts (NHWC / KRSC).
 
 Used by the numerics tests (every CUDA kernel is compared with the same op here) and as the
 documentation of what each kernel computes.
@@ -22,22 +22,22 @@ def krsc_to_oihw(w):
 
 
 def conv_fwd(x_nhwc, w_krsc, bias):
-    y = F.conv2d(nhwc_to_nchw(x_nhwc.float()), krsc_to_oihw(w_krsc.float()), None if bias is None else bias.float(),
-                 stride=1, padding=1)
-    return nchw_to_nhwc(y)
+    y = F.conv2d(nhwc_to_nchw(x_nhwc.double()), krsc_to_oihw(w_krsc.double()),
+                 None if bias is None else bias.double(), stride=1, padding=1)
+    return nchw_to_nhwc(y).float()
 
 
 def conv_dgrad(dy_nhwc, w_krsc):
-    dx = F.conv_transpose2d(nhwc_to_nchw(dy_nhwc.float()), krsc_to_oihw(w_krsc.float()), stride=1, padding=1)
-    return nchw_to_nhwc(dx)
+    dx = F.conv_transpose2d(nhwc_to_nchw(dy_nhwc.double()), krsc_to_oihw(w_krsc.double()), stride=1, padding=1)
+    return nchw_to_nhwc(dx).float()
 
 
 def conv_wgrad(dy_nhwc, x_nhwc):
-    x = nhwc_to_nchw(x_nhwc.float())
-    dy = nhwc_to_nchw(dy_nhwc.float())
+    x = nhwc_to_nchw(x_nhwc.double())
+    dy = nhwc_to_nchw(dy_nhwc.double())
     cout, cin = dy.shape[1], x.shape[1]
     dw = torch.nn.grad.conv2d_weight(x, (cout, cin, 3, 3), dy, stride=1, padding=1)
-    return dw.permute(0, 2, 3, 1).contiguous()        # OIHW -> KRSC
+    return dw.permute(0, 2, 3, 1).contiguous().float()        # OIHW -> KRSC
 
 
 def channel_stats(y_nhwc):
@@ -74,15 +74,16 @@ def bn_relu_pool_bwd(dout_nhwc, y_nhwc, gamma, beta, pool, eps=1e-5):
 
 def fc_ce(act, w, bias, target):
     """Returns (logits, loss, dlogits, dact, dw, db, correct)."""
-    a = act.float().clone().requires_grad_(True)
-    w_ = w.float().clone().requires_grad_(True)
-    b_ = bias.float().clone().requires_grad_(True)
+    a = act.double().clone().requires_grad_(True)
+    w_ = w.double().clone().requires_grad_(True)
+    b_ = bias.double().clone().requires_grad_(True)
     logits = F.linear(a, w_, b_)
     logits.retain_grad()
     loss = F.cross_entropy(logits, target)
     loss.backward()
     correct = (logits.argmax(1) == target).sum()
-    return logits.detach(), loss.detach(), logits.grad, a.grad, w_.grad, b_.grad, correct
+    f = lambda t: t.detach().float()
+    return f(logits), f(loss), f(logits.grad), f(a.grad), f(w_.grad), f(b_.grad), correct
 
 
 def sgd(param, mom, grad, lr, momentum, wd, grad_scale=1.0):

@@ -89,10 +89,10 @@ __device__ __forceinline__ void cta_barrier_all_ranks(const P2PArgs& a, int phas
     const int r = threadIdx.x;
     st_release_sys(a.flags[r] + (size_t)idx * P2P_MAX_RANKS + a.rank, e);
     const uint32_t* mine = a.flags[a.rank] + (size_t)idx * P2P_MAX_RANKS + r;
-    unsigned long long spins = 0;
+    const unsigned long long t0 = global_timer_ns();
     // signed distance handles the (theoretical) wrap of the 32-bit epoch
     while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
-      if (++spins > (1ull << 31)) {
+      if (global_timer_ns() - t0 > 20000000000ull) {      // 20 s: a peer died or never launched
         printf("ddpb: rank %d timed out waiting for rank %d (slot %d phase %d block %d epoch %u)\n", a.rank, r,
                a.slot, phase, blockIdx.x, e);
         __trap();

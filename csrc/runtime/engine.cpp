@@ -1,0 +1,572 @@
+// The VGG training-step engine: owns every device buffer, runs forward / backward as a static
+// sequence of sm_100a kernel launches, and schedules the gradient buckets.
+//
+// What it replaces in the reference: the autograd-driven loop body
+//   zero_grad -> model(data) -> criterion -> loss.backward() -> [sync] -> optimizer.step()
+// (ref Part 2a/main.py:86-98) plus, for Part 3, torch DDP's C++ Reducer (bucket assignment, ready
+// counting, asynchronous all-reduce launch, finalize; ref Part 3/main.py:61).
+//
+// Design notes
+//  * The network is static, so the gradient-ready order is known up front: the
+//    arena that holds gradients / fp32 master weights / momentum / bf16 compute weights is laid
+//    out in THAT order and every bucket is one contiguous range.  wgrad, BN-backward and the
+//    classifier backward write their gradients straight into the arena (no pack/unpack copies).
+//  * Bucket scheduler: when the last producer of a bucket has been enqueued on the compute
+//    stream, an event is recorded; the communication stream waits on it and launches ONE fused
+//    kernel (peer-to-peer reduce + 1/W + SGD momentum/weight decay + bf16 refresh, sync_p2p.cu)
+//    that overlaps with the rest of backward.  The step ends by joining the two streams.
+//  * The whole step (both streams) is captured once per batch size into a CUDA graph and
+//    replayed, so the host cost of a step is one graph launch.
+#include <cuda_runtime.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/ddp_b200.h"
+#include "../common.cuh"
+
+namespace ddpb {
+
+static constexpr int kAlign = 64;    // arena slot alignment in elements (256 B of fp32)
+
+static long long round_up(long long x, long long m) { return (x + m - 1) / m * m; }
+
+struct Slot { long long off, numel; };
+
+struct Block {
+  int cin, cout, hw, pool;
+  Slot conv_w, conv_b, bn_w, bn_b;
+  long long stat_off;    // offset (floats) of this block's [2C] in the fwd-stats / bwd-sums scratch
+  long long ch_off;      // offset of this block's [C] in mean / invstd / running stats
+  void* y;               // conv output  [B,hw,hw,cout]
+  void* act;             // block output [B,ohw,ohw,cout]
+};
+
+struct Bucket { long long off, numel; int last_block; int mode; };   // last_block: -1 = classifier
+
+struct Graph { cudaGraphExec_t exec = nullptr; long long launches = 0; };
+
+struct Engine {
+  ddpb_engine_config cfg;
+  int esize;                       // activation element size
+  std::vector<Block> blocks;
+  Slot fc_w, fc_b;
+  long long arena_elems = 0, total_c = 0;
+  // symmetric arena
+  void* arena = nullptr; size_t arena_bytes = 0; unsigned char ipc_handle[64];
+  float *grad = nullptr, *master = nullptr, *mom = nullptr, *rmean = nullptr, *rvar = nullptr;
+  bf16* shadow = nullptr; uint32_t* flags = nullptr;
+  size_t off_grad = 0, off_master = 0, off_mom = 0, off_shadow = 0, off_rstats = 0, off_flags = 0;
+  void* peer_arena[DDPB_MAX_RANKS] = {nullptr};
+  bool peers_set = false;
+  // local buffers
+  uint32_t* epochs = nullptr;
+  float *scratch = nullptr, *mean = nullptr, *invstd = nullptr, *logits = nullptr, *dlogits = nullptr;
+  float *loss = nullptr, *eval_loss = nullptr; int *correct = nullptr; long long* nbt = nullptr;
+  size_t scratch_floats = 0;
+  void *input = nullptr, *dy_buf = nullptr, *dact = nullptr; long long* target = nullptr;
+  std::vector<Bucket> buckets;
+  cudaStream_t comm = nullptr;
+  std::vector<cudaEvent_t> bucket_ev;
+  cudaEvent_t join_ev = nullptr, fork_ev = nullptr;
+  std::map<long long, Graph> graphs;     // key = kind * 1e6 + batch
+  long long launches = 0, counting = 0;
+  bool count_only = false;
+};
+
+#define ECHECK(call)        \
+  do {                      \
+    int _rc = (call);       \
+    if (_rc) return _rc;    \
+  } while (0)
+
+static void peer_table(Engine* e, size_t off, void** out) {
+  for (int r = 0; r < e->cfg.world; ++r) {
+    void* base = (r == e->cfg.rank) ? e->arena : e->peer_arena[r];
+    out[r] = base ? (void*)((char*)base + off) : nullptr;
+  }
+}
+
+static Slot take(long long& cursor, long long numel) {
+  Slot s{cursor, numel};
+  cursor = round_up(cursor + numel, kAlign);
+  return s;
+}
+
+static int plan_layout(Engine* e) {
+  const auto& c = e->cfg;
+  e->blocks.resize(c.num_blocks);
+  long long cur = 0, stat = 0, ch = 0;
+  // gradient-ready order: classifier first (bias, weight), then blocks last -> first with the BN
+  // pair before the conv pair and weight before bias
+  e->fc_b = take(cur, 10);
+  e->fc_w = take(cur, 10 * 512);
+  for (int i = c.num_blocks - 1; i >= 0; --i) {
+    Block& b = e->blocks[i];
+    b.cin = c.cin[i]; b.cout = c.cout[i]; b.hw = c.hw[i]; b.pool = c.pool[i];
+    b.bn_w = take(cur, b.cout);
+    b.bn_b = take(cur, b.cout);
+    b.conv_w = take(cur, (long long)b.cout * 9 * b.cin);
+    b.conv_b = take(cur, b.cout);
+  }
+  for (int i = 0; i < c.num_blocks; ++i) {
+    e->blocks[i].stat_off = stat; stat += 2 * e->blocks[i].cout;
+    e->blocks[i].ch_off = ch; ch += e->blocks[i].cout;
+  }
+  e->arena_elems = cur;
+  e->total_c = ch;
+  return DDPB_OK;
+}
+
+// Buckets over the ready-ordered arena.  plan 0 = size-capped greedy (torch DDP's rule: a bucket
+// closes once it reaches its cap; first cap, then the general cap), 1 = one bucket per layer
+// (classifier separate), 2 = a single bucket.
+static void plan_buckets(Engine* e) {
+  const auto& c = e->cfg;
+  struct Item { long long off, end; int block; };
+  std::vector<Item> items;
+  auto add = [&](Slot s, int blk) { items.push_back({s.off, round_up(s.off + s.numel, kAlign), blk}); };
+  add(e->fc_b, -1); add(e->fc_w, -1);
+  for (int i = c.num_blocks - 1; i >= 0; --i) {
+    const Block& b = e->blocks[i];
+    add(b.bn_w, i); add(b.bn_b, i); add(b.conv_w, i); add(b.conv_b, i);
+  }
+  e->buckets.clear();
+  auto close = [&](long long off, long long end, int last) { e->buckets.push_back({off, end - off, last, 0}); };
+  if (c.bucket_plan == 2) {
+    close(0, e->arena_elems, 0);
+  } else if (c.bucket_plan == 1) {
+    size_t i = 0;
+    while (i < items.size()) {
+      size_t j = i;
+      while (j + 1 < items.size() && items[j + 1].block == items[i].block) ++j;
+      close(items[i].off, items[j].end, items[i].block);
+      i = j + 1;
+    }
+  } else {
+    const double mib = 1024.0 * 1024.0;
+    double limit = c.first_bucket_mb * mib, acc = 0;
+    long long start = 0;
+    for (size_t i = 0; i < items.size(); ++i) {
+      acc += (double)(items[i].end - items[i].off) * 4.0;
+      bool last_item = i + 1 == items.size();
+      // a bucket may only close at a layer boundary here: all four tensors of a layer are produced
+      // by the same group of kernels, so splitting them buys nothing
+      bool boundary = last_item || items[i + 1].block != items[i].block;
+      if ((acc >= limit && boundary) || last_item) {
+        close(start, items[i].end, items[i].block);
+        start = items[i].end; acc = 0; limit = c.bucket_cap_mb * mib;
+      }
+    }
+  }
+  for (auto& b : e->buckets)
+    b.mode = (c.world > 1 && b.numel * 4 >= 256 * 1024) ? DDPB_P2P_TWOSHOT : DDPB_P2P_ONESHOT;
+}
+
+static int alloc_all(Engine* e) {
+  const auto& c = e->cfg;
+  const long long B = c.max_batch;
+  e->esize = c.dtype == DDPB_BF16 ? 2 : 4;
+  // ---- symmetric arena ----
+  size_t cur = 0;
+  auto carve = [&](size_t bytes) { size_t o = cur; cur = (size_t)round_up((long long)(cur + bytes), 1024); return o; };
+  e->off_grad = carve(e->arena_elems * 4);
+  e->off_master = carve(e->arena_elems * 4);
+  e->off_mom = carve(e->arena_elems * 4);
+  e->off_shadow = carve(e->arena_elems * 2);
+  e->off_rstats = carve(e->total_c * 2 * 4);
+  e->off_flags = carve((size_t)DDPB_P2P_MAX_SLOTS * 2 * DDPB_P2P_MAX_BLOCKS * DDPB_MAX_RANKS * 4);
+  e->arena_bytes = cur;
+  ECHECK(ddpb_symm_alloc(e->arena_bytes, &e->arena, e->ipc_handle));
+  char* a = (char*)e->arena;
+  e->grad = (float*)(a + e->off_grad); e->master = (float*)(a + e->off_master);
+  e->mom = (float*)(a + e->off_mom); e->shadow = (bf16*)(a + e->off_shadow);
+  e->rmean = (float*)(a + e->off_rstats); e->rvar = e->rmean + e->total_c;
+  e->flags = (uint32_t*)(a + e->off_flags);
+  // ---- local ----
+  size_t nep = (size_t)DDPB_P2P_MAX_SLOTS * 2 * DDPB_P2P_MAX_BLOCKS * 4;
+  DDPB_CUDA_CHECK(cudaMalloc(&e->epochs, nep));
+  DDPB_CUDA_CHECK(cudaMemset(e->epochs, 0, nep));
+  // scratch: [fwd stats 2*sumC][bwd sums 2*sumC][loss][pad]
+  e->scratch_floats = (size_t)e->total_c * 4 + 64;
+  DDPB_CUDA_CHECK(cudaMalloc(&e->scratch, e->scratch_floats * 4));
+  e->loss = e->scratch + e->total_c * 4;
+  DDPB_CUDA_CHECK(cudaMalloc(&e->mean, e->total_c * 4));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->invstd, e->total_c * 4));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->nbt, sizeof(long long) * (c.num_blocks + 1)));
+  DDPB_CUDA_CHECK(cudaMemset(e->nbt, 0, sizeof(long long) * (c.num_blocks + 1)));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->logits, B * 10 * 4));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->dlogits, B * 10 * 4));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->eval_loss, 64));
+  e->correct = (int*)(e->eval_loss + 1);
+  DDPB_CUDA_CHECK(cudaMemset(e->eval_loss, 0, 64));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->input, B * 32 * 32 * 3 * e->esize));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->target, B * 8));
+  long long max_y = 0, max_act = 512;
+  for (auto& b : e->blocks) {
+    long long y = (long long)b.hw * b.hw * b.cout;
+    long long o = b.pool ? y / 4 : y;
+    max_y = std::max(max_y, y); max_act = std::max(max_act, o);
+    DDPB_CUDA_CHECK(cudaMalloc(&b.y, B * y * e->esize));
+    DDPB_CUDA_CHECK(cudaMalloc(&b.act, B * o * e->esize));
+  }
+  DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf, B * max_y * e->esize));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->dact, B * max_act * e->esize));
+  // BN defaults: gamma 1, running_var 1 (weights are loaded by the caller afterwards)
+  DDPB_CUDA_CHECK(cudaMemset(e->mean, 0, e->total_c * 4));
+  DDPB_CUDA_CHECK(cudaMemset(e->invstd, 0, e->total_c * 4));
+  DDPB_CUDA_CHECK(cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking));
+  e->bucket_ev.resize(e->buckets.size());
+  for (auto& ev : e->bucket_ev) DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->join_ev, cudaEventDisableTiming));
+  DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->fork_ev, cudaEventDisableTiming));
+  return DDPB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward / backward sequences
+// ---------------------------------------------------------------------------------------------
+static bool use_tc(const Engine* e, const Block& b) {
+  return e->cfg.dtype == DDPB_BF16 && e->cfg.use_tc && b.cin % 64 == 0 && b.cout % 128 == 0;
+}
+
+#define LAUNCH(e, call)   \
+  do {                    \
+    ECHECK(call);         \
+    (e)->counting += 1;   \
+  } while (0)
+
+static int forward(Engine* e, int B, int training, cudaStream_t s) {
+  const int dt = e->cfg.dtype;
+  float* fstats = e->scratch;
+  if (training) {
+    DDPB_CUDA_CHECK(cudaMemsetAsync(e->scratch, 0, e->scratch_floats * 4, s));
+  }
+  const void* x = e->input;
+  for (size_t i = 0; i < e->blocks.size(); ++i) {
+    Block& b = e->blocks[i];
+    float* st = training ? fstats + b.stat_off : nullptr;
+    const float* bias = e->master + b.conv_b.off;
+    if (use_tc(e, b))
+      LAUNCH(e, ddpb_conv3x3_fwd_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+    else {
+      LAUNCH(e, ddpb_conv3x3_fwd_simt(x, e->master + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, dt, s));
+      if (st && !(b.cin == 3 && b.cout == 64)) e->counting += 1;       // separate channel_stats launch
+    }
+    LAUNCH(e, ddpb_bn_relu_pool_fwd(b.y, st, e->master + b.bn_w.off, e->master + b.bn_b.off, b.act,
+                                    e->mean + b.ch_off, e->invstd + b.ch_off, e->rmean + b.ch_off,
+                                    e->rvar + b.ch_off, e->nbt + i, B, b.hw, b.hw, b.cout, b.pool, training, 1e-5f,
+                                    0.1f, dt, s));
+    x = b.act;
+  }
+  return DDPB_OK;
+}
+
+static int loss_fwd(Engine* e, int B, int training, cudaStream_t s) {
+  const Block& last = e->blocks.back();
+  LAUNCH(e, ddpb_fc_ce_fwd(last.act, e->master + e->fc_w.off, e->master + e->fc_b.off, e->target, e->logits,
+                           training ? e->dlogits : nullptr, training ? e->loss : e->eval_loss,
+                           training ? nullptr : e->correct, B, B, e->cfg.dtype, s));
+  return DDPB_OK;
+}
+
+static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
+  const auto& c = e->cfg;
+  const Bucket& b = e->buckets[bi];
+  if (c.world == 1 || !e->peers_set) {
+    // single process (or NCCL fallback driven from Python): plain fused SGD on the bucket
+    if (c.external_sync) return DDPB_OK;
+    LAUNCH(e, ddpb_sgd_step(e->master + b.off, e->mom + b.off, e->grad + b.off,
+                            c.dtype == DDPB_BF16 ? (void*)(e->shadow + b.off) : nullptr, b.numel, c.lr, c.momentum,
+                            c.wd, 1.f, s));
+    return DDPB_OK;
+  }
+  void *g[DDPB_MAX_RANKS], *m[DDPB_MAX_RANKS], *sh[DDPB_MAX_RANKS], *f[DDPB_MAX_RANKS];
+  peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
+  peer_table(e, e->off_shadow, sh); peer_table(e, e->off_flags, f);
+  LAUNCH(e, ddpb_p2p_sync(b.mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
+                          c.momentum, c.wd, 0, s));
+  return DDPB_OK;
+}
+
+// After the producers of block `blk` (-1 = classifier) are enqueued on `s`: launch every bucket
+// whose last producer this was.  Overlapped strategies hand the bucket to the comm stream.
+static int buckets_ready(Engine* e, int blk, cudaStream_t s) {
+  const auto& c = e->cfg;
+  if (c.strategy != 3) return DDPB_OK;        // only the bucketed strategy syncs during backward
+  for (size_t i = 0; i < e->buckets.size(); ++i) {
+    if (e->buckets[i].last_block != blk) continue;
+    if (c.world > 1 && e->peers_set) {
+      DDPB_CUDA_CHECK(cudaEventRecord(e->bucket_ev[i], s));
+      DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, e->bucket_ev[i], 0));
+      ECHECK(launch_bucket(e, (int)i, e->comm));
+    } else {
+      ECHECK(launch_bucket(e, (int)i, s));
+    }
+  }
+  return DDPB_OK;
+}
+
+static int backward(Engine* e, int B, cudaStream_t s) {
+  const auto& c = e->cfg;
+  const int dt = c.dtype;
+  float* bsums = e->scratch + e->total_c * 2;
+  DDPB_CUDA_CHECK(cudaMemsetAsync(e->grad, 0, e->arena_elems * 4, s));
+  const Block& last = e->blocks.back();
+  LAUNCH(e, ddpb_fc_bwd(last.act, e->master + e->fc_w.off, e->dlogits, e->dact, e->grad + e->fc_w.off,
+                        e->grad + e->fc_b.off, B, dt, s));
+  ECHECK(buckets_ready(e, -1, s));
+  for (int i = (int)e->blocks.size() - 1; i >= 0; --i) {
+    Block& b = e->blocks[i];
+    const void* x_in = i == 0 ? e->input : e->blocks[i - 1].act;
+    LAUNCH(e, ddpb_bn_relu_pool_bwd(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off, e->master + b.bn_w.off,
+                                    e->master + b.bn_b.off, bsums + b.stat_off, e->dy_buf, e->grad + b.bn_w.off,
+                                    e->grad + b.bn_b.off, e->grad + b.conv_b.off, B, b.hw, b.hw, b.cout, b.pool,
+                                    dt, s));
+    e->counting += 1;     // the BN backward is two launches (reduce + apply)
+    if (use_tc(e, b)) {
+      LAUNCH(e, ddpb_conv3x3_wgrad_tc(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+      ECHECK(buckets_ready(e, i, s));
+      if (i > 0)
+        LAUNCH(e, ddpb_conv3x3_dgrad_tc(e->dy_buf, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+    } else {
+      LAUNCH(e, ddpb_conv3x3_wgrad_simt(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, s));
+      ECHECK(buckets_ready(e, i, s));
+      if (i > 0)
+        LAUNCH(e, ddpb_conv3x3_dgrad_simt(e->dy_buf, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
+    }
+  }
+  // ---- end of backward: the non-overlapped strategies synchronise here, like the reference ----
+  const bool p2p = c.world > 1 && e->peers_set;
+  if (c.strategy == 3) {
+    if (p2p) {   // join: the step is complete when every bucket kernel has finished
+      DDPB_CUDA_CHECK(cudaEventRecord(e->join_ev, e->comm));
+      DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->join_ev, 0));
+    }
+  } else if (!c.external_sync) {
+    if (p2p) {
+      void *g[DDPB_MAX_RANKS], *m[DDPB_MAX_RANKS], *sh[DDPB_MAX_RANKS], *f[DDPB_MAX_RANKS];
+      peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
+      peer_table(e, e->off_shadow, sh); peer_table(e, e->off_flags, f);
+      int mode = c.strategy == 1 ? DDPB_P2P_ROOT : DDPB_P2P_TWOSHOT;
+      LAUNCH(e, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1, 0,
+                              e->arena_elems, c.lr, c.momentum, c.wd, 0, s));
+    } else {
+      LAUNCH(e, ddpb_sgd_step(e->master, e->mom, e->grad, dt == DDPB_BF16 ? (void*)e->shadow : nullptr,
+                              e->arena_elems, c.lr, c.momentum, c.wd, 1.f, s));
+    }
+  }
+  return DDPB_OK;
+}
+
+enum { KIND_FWD = 1, KIND_BWD = 2, KIND_STEP = 3 };
+
+static int run_kind(Engine* e, int kind, int B, cudaStream_t s) {
+  if (kind & KIND_FWD) { ECHECK(forward(e, B, 1, s)); ECHECK(loss_fwd(e, B, 1, s)); }
+  if (kind & KIND_BWD) ECHECK(backward(e, B, s));
+  return DDPB_OK;
+}
+
+static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
+  if (!e->cfg.use_graph) {
+    e->counting = 0;
+    ECHECK(run_kind(e, kind, B, s));
+    e->launches += e->counting;
+    return DDPB_OK;
+  }
+  long long key = (long long)kind * 1000000 + B;
+  auto it = e->graphs.find(key);
+  if (it == e->graphs.end()) {
+    // one eager run first: it performs the one-time cudaFuncSetAttribute calls (not capturable)
+    e->counting = 0;
+    ECHECK(run_kind(e, kind, B, s));
+    e->launches += e->counting;
+    DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
+    DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm));
+    // NOTE: that eager run was a real step; the caller asked for exactly one, so capture only and
+    // launch the graph from the NEXT call on.
+    Graph g;
+    cudaGraph_t graph;
+    e->counting = 0;
+    DDPB_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    int rc = run_kind(e, kind, B, s);
+    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    if (rc) return rc;
+    DDPB_CUDA_CHECK(ce);
+    g.launches = e->counting;
+    DDPB_CUDA_CHECK(cudaGraphInstantiate(&g.exec, graph, 0));
+    cudaGraphDestroy(graph);
+    e->graphs[key] = g;
+    return DDPB_OK;
+  }
+  DDPB_CUDA_CHECK(cudaGraphLaunch(it->second.exec, s));
+  e->launches += it->second.launches;
+  return DDPB_OK;
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) {
+  DDPB_REQUIRE(cfg && handle, "engine_create: null argument");
+  DDPB_REQUIRE(cfg->num_blocks > 0 && cfg->num_blocks <= DDPB_MAX_BLOCKS, "engine_create: bad block count");
+  DDPB_REQUIRE(cfg->world >= 1 && cfg->world <= DDPB_MAX_RANKS, "engine_create: world size %d unsupported", cfg->world);
+  Engine* e = new Engine();
+  e->cfg = *cfg;
+  int rc = plan_layout(e);
+  if (!rc) { plan_buckets(e); rc = alloc_all(e); }
+  if (rc) { delete e; return rc; }
+  DDPB_REQUIRE((int)e->buckets.size() < DDPB_P2P_MAX_SLOTS - 1, "engine_create: too many buckets");
+  *handle = e;
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_engine_destroy(void* handle) {
+  Engine* e = (Engine*)handle;
+  if (!e) return DDPB_OK;
+  cudaDeviceSynchronize();
+  for (auto& kv : e->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  for (int r = 0; r < e->cfg.world; ++r)
+    if (r != e->cfg.rank && e->peer_arena[r]) cudaIpcCloseMemHandle(e->peer_arena[r]);
+  for (auto& b : e->blocks) { cudaFree(b.y); cudaFree(b.act); }
+  void* frees[] = {e->epochs, e->scratch, e->mean, e->invstd, e->nbt, e->logits, e->dlogits, e->eval_loss,
+                   e->input, e->target, e->dy_buf, e->dact, e->arena};
+  for (void* p : frees) if (p) cudaFree(p);
+  for (auto& ev : e->bucket_ev) cudaEventDestroy(ev);
+  if (e->join_ev) cudaEventDestroy(e->join_ev);
+  if (e->fork_ev) cudaEventDestroy(e->fork_ev);
+  if (e->comm) cudaStreamDestroy(e->comm);
+  delete e;
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_engine_info(void* handle, ddpb_engine_info_t* out) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(e && out, "engine_info: null argument");
+  memset(out, 0, sizeof(*out));
+  out->arena = e->arena; out->arena_bytes = e->arena_bytes;
+  memcpy(out->ipc_handle, e->ipc_handle, 64);
+  out->arena_elems = e->arena_elems; out->total_channels = e->total_c;
+  out->grad = e->grad; out->master = e->master; out->mom = e->mom; out->shadow = e->shadow;
+  out->running_mean = e->rmean; out->running_var = e->rvar; out->num_batches_tracked = e->nbt;
+  out->input = e->input; out->target = e->target; out->loss = e->loss; out->eval_loss = e->eval_loss;
+  out->correct = e->correct; out->logits = e->logits;
+  out->num_buckets = (int)e->buckets.size();
+  for (size_t i = 0; i < e->buckets.size() && i < DDPB_P2P_MAX_SLOTS; ++i) {
+    out->bucket_off[i] = e->buckets[i].off; out->bucket_numel[i] = e->buckets[i].numel;
+    out->bucket_mode[i] = e->buckets[i].mode; out->bucket_last_block[i] = e->buckets[i].last_block;
+  }
+  out->fc_w_off = e->fc_w.off; out->fc_b_off = e->fc_b.off;
+  for (size_t i = 0; i < e->blocks.size(); ++i) {
+    const Block& b = e->blocks[i];
+    out->conv_w_off[i] = b.conv_w.off; out->conv_b_off[i] = b.conv_b.off;
+    out->bn_w_off[i] = b.bn_w.off; out->bn_b_off[i] = b.bn_b.off; out->ch_off[i] = b.ch_off;
+    out->y[i] = b.y; out->act[i] = b.act;
+  }
+  out->launches = e->launches;
+  return DDPB_OK;
+}
+
+// peer_arena[r] = this rank's mapping of rank r's arena (ddpb_symm_open), entry `rank` ignored.
+extern "C" int ddpb_engine_set_peers(void* handle, void* const* peer_arena) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(e && peer_arena, "engine_set_peers: null argument");
+  for (int r = 0; r < e->cfg.world; ++r) e->peer_arena[r] = r == e->cfg.rank ? e->arena : peer_arena[r];
+  e->peers_set = true;
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_engine_set_lr(void* handle, float lr) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(e, "engine_set_lr: null");
+  if (lr != e->cfg.lr) {       // baked into captured graphs: drop them
+    e->cfg.lr = lr;
+    for (auto& kv : e->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    e->graphs.clear();
+  }
+  return DDPB_OK;
+}
+
+// Refresh the bf16 compute copy from the fp32 master weights (after loading a checkpoint).
+extern "C" int ddpb_engine_refresh_shadow(void* handle, cudaStream_t s) {
+  Engine* e = (Engine*)handle;
+  return ddpb_cast_f32_bf16(e->master, e->shadow, e->arena_elems, s);
+}
+
+extern "C" int ddpb_engine_forward(void* handle, int batch, cudaStream_t s) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_forward: batch %d out of range", batch);
+  return run_graphed(e, KIND_FWD, batch, s);
+}
+extern "C" int ddpb_engine_backward(void* handle, int batch, cudaStream_t s) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_backward: batch %d out of range", batch);
+  return run_graphed(e, KIND_BWD, batch, s);
+}
+extern "C" int ddpb_engine_train_step(void* handle, int batch, cudaStream_t s) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_train_step: batch %d out of range", batch);
+  return run_graphed(e, KIND_STEP, batch, s);
+}
+
+// Eval forward: BN uses running statistics; eval_loss += mean CE of the batch; correct += hits.
+extern "C" int ddpb_engine_eval_step(void* handle, int batch, cudaStream_t s) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_eval_step: batch %d out of range", batch);
+  e->counting = 0;
+  ECHECK(forward(e, batch, 0, s));
+  ECHECK(loss_fwd(e, batch, 0, s));
+  e->launches += e->counting;
+  return DDPB_OK;
+}
+
+extern "C" int ddpb_engine_eval_reset(void* handle, cudaStream_t s) {
+  Engine* e = (Engine*)handle;
+  DDPB_CUDA_CHECK(cudaMemsetAsync(e->eval_loss, 0, 64, s));
+  return DDPB_OK;
+}
+
+// Collective over the symmetric arena outside the training step: what = 0 broadcast master weights,
+// 1 broadcast BN running statistics (rank 0 -> all; DDP's init / buffer sync), 2 all-gather the
+// momentum shards of the two-shot buckets (before a checkpoint).
+extern "C" int ddpb_engine_collective(void* handle, int what, cudaStream_t s) {
+  Engine* e = (Engine*)handle;
+  const auto& c = e->cfg;
+  if (c.world == 1 || !e->peers_set) return DDPB_OK;
+  void *buf[DDPB_MAX_RANKS], *f[DDPB_MAX_RANKS];
+  peer_table(e, e->off_flags, f);
+  const int slot = DDPB_P2P_MAX_SLOTS - 2;
+  if (what == 0) {
+    peer_table(e, e->off_master, buf);
+    ECHECK(ddpb_p2p_sync(DDPB_P2P_BCAST, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot, 0,
+                         e->arena_elems, 0, 0, 0, 0, s));
+    return ddpb_engine_refresh_shadow(handle, s);
+  }
+  if (what == 1) {
+    peer_table(e, e->off_rstats, buf);
+    return ddpb_p2p_sync(DDPB_P2P_BCAST, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot, 0,
+                         round_up(e->total_c * 2, 4), 0, 0, 0, 0, s);
+  }
+  if (what == 2) {
+    peer_table(e, e->off_mom, buf);
+    if (c.strategy == 3) {
+      for (size_t i = 0; i < e->buckets.size(); ++i)
+        if (e->buckets[i].mode == DDPB_P2P_TWOSHOT)
+          ECHECK(ddpb_p2p_sync(DDPB_P2P_ALLGATHER, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world,
+                               slot, e->buckets[i].off, e->buckets[i].numel, 0, 0, 0, 0, s));
+      return DDPB_OK;
+    }
+    if (c.strategy == 2)
+      return ddpb_p2p_sync(DDPB_P2P_ALLGATHER, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot,
+                           0, e->arena_elems, 0, 0, 0, 0, s);
+    if (c.strategy == 1)   // root owns all momentum: broadcast it
+      return ddpb_p2p_sync(DDPB_P2P_BCAST, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot, 0,
+                           e->arena_elems, 0, 0, 0, 0, s);
+    return DDPB_OK;
+  }
+  DDPB_REQUIRE(false, "engine_collective: unknown op %d", what);
+}

@@ -134,6 +134,62 @@ int ddpb_symm_free(void* ptr);
 /* Enable peer access from the current device to `peer_device` (same-process multi-GPU tests). */
 int ddpb_enable_peer_access(int peer_device);
 
+/* ---- training-step engine (csrc/runtime/engine.cpp) ---------------------------------------- */
+
+#define DDPB_MAX_BLOCKS 24
+
+/* Strategy: 0 none (ref Part 1), 1 gather_scatter (Part 2a), 2 allreduce (Part 2b), 3 bucketed (Part 3). */
+typedef struct ddpb_engine_config {
+  int dtype;            /* DDPB_F32 / DDPB_BF16 activations + conv operands */
+  int max_batch;        /* per-rank batch the buffers are sized for */
+  int world, rank;
+  int strategy;
+  int num_blocks;       /* conv+BN+ReLU(+pool) blocks */
+  int cin[DDPB_MAX_BLOCKS], cout[DDPB_MAX_BLOCKS], hw[DDPB_MAX_BLOCKS], pool[DDPB_MAX_BLOCKS];
+  float lr, momentum, wd;
+  int bucket_plan;      /* 0 size-capped (DDP rule), 1 per layer, 2 single */
+  float first_bucket_mb, bucket_cap_mb;
+  int use_graph;        /* capture each step kind into a CUDA graph */
+  int use_tc;           /* tcgen05 kernels for bf16 layers with Cin%64==0, Cout%128==0 */
+  int external_sync;    /* 1: the engine neither syncs nor steps; the caller reduces `grad` and calls
+                           ddpb_sgd_step (NCCL baseline path) */
+} ddpb_engine_config;
+
+typedef struct ddpb_engine_info_t {
+  void* arena; size_t arena_bytes; unsigned char ipc_handle[64];
+  long long arena_elems, total_channels;
+  float *grad, *master, *mom; void* shadow;
+  float *running_mean, *running_var; long long* num_batches_tracked;
+  void* input; long long* target; float *loss, *eval_loss; int* correct; float* logits;
+  int num_buckets;
+  long long bucket_off[DDPB_P2P_MAX_SLOTS], bucket_numel[DDPB_P2P_MAX_SLOTS];
+  int bucket_mode[DDPB_P2P_MAX_SLOTS], bucket_last_block[DDPB_P2P_MAX_SLOTS];
+  long long fc_w_off, fc_b_off;
+  long long conv_w_off[DDPB_MAX_BLOCKS], conv_b_off[DDPB_MAX_BLOCKS], bn_w_off[DDPB_MAX_BLOCKS],
+      bn_b_off[DDPB_MAX_BLOCKS], ch_off[DDPB_MAX_BLOCKS];
+  void *y[DDPB_MAX_BLOCKS], *act[DDPB_MAX_BLOCKS];
+  long long launches;   /* kernels launched by the engine so far (graph replays included) */
+} ddpb_engine_info_t;
+
+/* ALLOCATES all device buffers (cudaMalloc), including the symmetric arena. */
+int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle);
+int ddpb_engine_destroy(void* handle);
+int ddpb_engine_info(void* handle, ddpb_engine_info_t* out);
+int ddpb_engine_set_peers(void* handle, void* const* peer_arena);
+int ddpb_engine_set_lr(void* handle, float lr);
+int ddpb_engine_refresh_shadow(void* handle, cudaStream_t stream);
+/* One iteration on the batch already staged in info.input / info.target.  forward = conv stack +
+ * classifier + loss (info.loss); backward = all gradients + gradient sync + optimizer step
+ * (ref Part 2a/main.py:88-96); train_step = both. */
+int ddpb_engine_forward(void* handle, int batch, cudaStream_t stream);
+int ddpb_engine_backward(void* handle, int batch, cudaStream_t stream);
+int ddpb_engine_train_step(void* handle, int batch, cudaStream_t stream);
+/* ref Part 1/main.py:61-76: eval-mode forward; accumulates info.eval_loss / info.correct. */
+int ddpb_engine_eval_step(void* handle, int batch, cudaStream_t stream);
+int ddpb_engine_eval_reset(void* handle, cudaStream_t stream);
+/* what: 0 broadcast weights from rank 0, 1 broadcast BN running stats, 2 gather momentum shards. */
+int ddpb_engine_collective(void* handle, int what, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

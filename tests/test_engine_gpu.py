@@ -1,0 +1,206 @@
+"""The native step engine against the torch back-end (the reference's computation) on one GPU."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = torch.device("cuda", 0)
+
+
+class _T:            # region timer stub (forces the split forward/backward path)
+    is_async = True
+
+    def mark(self, i):
+        pass
+
+
+class _Fused:        # no ``is_async``: the engine runs the whole step as one graph
+    def mark(self, i):
+        pass
+
+
+def _cfg(**kw):
+    from cs744_ddp_b200.config import TrainConfig
+    base = dict(synthetic=True, global_batch=16, device="cuda", log_every=4)
+    base.update(kw)
+    return TrainConfig(**base)
+
+
+def _batches(n, b, seed=0):
+    from cs744_ddp_b200.data import synthetic_cifar10
+    from cs744_ddp_b200.data.pipeline import RawBatch
+    split = synthetic_cifar10(n * b, seed=seed)
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for i in range(n):
+        crop = torch.randint(0, 9, (b, 2), generator=g, dtype=torch.int32)
+        flip = (torch.rand(b, generator=g) < 0.5).to(torch.uint8)
+        out.append(RawBatch(split.images[i * b:(i + 1) * b], split.labels[i * b:(i + 1) * b], crop, flip))
+    return out
+
+
+@pytest.fixture(scope="module")
+def no_tf32():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def _pair(dtype, graph, b=16):
+    from cs744_ddp_b200.backends import TorchBackend
+    from cs744_ddp_b200.engine import NativeBackend
+    torch.manual_seed(0)
+    tb = TorchBackend(_cfg(backend="torch", dtype="fp32", global_batch=b), DEV)
+    nb = NativeBackend(_cfg(backend="native", dtype=dtype, use_cuda_graph=graph, global_batch=b), DEV,
+                       init_state=tb.state_dict())
+    return tb, nb
+
+
+def _rel(a, b):
+    return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_fp32_engine_matches_torch_training(no_tf32, graph):
+    tb, nb = _pair("fp32", graph)
+    tb.set_train(True)
+    for step, raw in enumerate(_batches(4, 16)):
+        lt = tb.train_step(*tb.prepare(raw), _T())
+        ln = nb.train_step(*nb.prepare(raw), _T())
+        print(f"[eng] fp32 graph={graph} step {step}: torch {float(lt):.6f} native {float(ln):.6f}")
+        assert abs(float(lt) - float(ln)) < 2e-3 * max(1.0, abs(float(lt))), step
+    sd_t, sd_n = tb.state_dict(), nb.state_dict()
+    assert list(sd_t.keys()) == list(sd_n.keys())
+    for k in sd_t:
+        if "num_batches" in k:
+            assert int(sd_t[k]) == int(sd_n[k]) == 4
+            continue
+        err = _rel(sd_n[k], sd_t[k])
+        # conv biases sit in front of a BN: their gradient is numerical noise
+        tol = 5e-2 if (k.endswith(".bias") and sd_t[k].numel() > 10 and "layers" in k) else 5e-3
+        assert err < tol, (k, err)
+
+
+def test_fp32_gradients_match_autograd(no_tf32):
+    tb, nb = _pair("fp32", False)
+    raw = _batches(1, 16, seed=3)[0]
+    data, target = tb.prepare(raw)
+    tb.optimizer.zero_grad()
+    loss = tb.criterion(tb.model(data), target)
+    loss.backward()
+    ref = {n: p.grad.clone() for n, p in tb.model.named_parameters()}
+    # run only forward + backward on the engine (lr 0 keeps the weights, gradients stay in the arena)
+    nb.cfg.lr = 0.0
+    from cs744_ddp_b200.ops.native import check, stream_handle
+    check(nb._lib.ddpb_engine_set_lr(nb._handle, __import__("ctypes").c_float(0.0)))
+    nb.train_step(*nb.prepare(raw), _T())
+    got = nb.grads()
+    for name, g in ref.items():
+        if name.endswith(".bias") and "layers" in name and g.abs().max() < 1e-5:
+            continue                                   # conv bias before BN: pure noise
+        err = _rel(got[name], g)
+        print(f"[eng] grad {name}: rel {err:.2e}")
+        assert err < 2e-3, (name, err)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_bf16_tensor_core_engine_tracks_fp32(no_tf32, graph):
+    tb, nb = _pair("bf16", graph, b=32)
+    tb.set_train(True)
+    lt_hist, ln_hist = [], []
+    for step, raw in enumerate(_batches(6, 32, seed=1)):
+        lt_hist.append(float(tb.train_step(*tb.prepare(raw), _T())))
+        ln_hist.append(float(nb.train_step(*nb.prepare(raw), _Fused() if graph else _T())))
+    print("[eng] bf16 losses torch ", ["%.4f" % v for v in lt_hist])
+    print("[eng] bf16 losses native", ["%.4f" % v for v in ln_hist])
+    assert abs(lt_hist[0] - ln_hist[0]) < 3e-2 * max(1.0, lt_hist[0])
+    for a, b in zip(lt_hist, ln_hist):
+        assert abs(a - b) < 0.25 * max(1.0, a)
+    w_t = tb.state_dict()["layers.8.weight"]
+    w_n = nb.state_dict()["layers.8.weight"]
+    assert _rel(w_n, w_t) < 5e-2
+
+
+def test_bf16_first_step_gradients_close_to_fp32(no_tf32):
+    tb, nb = _pair("bf16", False, b=32)
+    raw = _batches(1, 32, seed=5)[0]
+    data, target = tb.prepare(raw)
+    tb.criterion(tb.model(data), target).backward()
+    import ctypes
+    from cs744_ddp_b200.ops.native import check
+    check(nb._lib.ddpb_engine_set_lr(nb._handle, ctypes.c_float(0.0)))
+    nb.train_step(*nb.prepare(raw), _T())
+    got = nb.grads()
+    for name, p in tb.model.named_parameters():
+        if "weight" not in name:
+            continue
+        g = p.grad
+        cos = float(torch.nn.functional.cosine_similarity(got[name].flatten(), g.flatten(), dim=0))
+        print(f"[eng] bf16 grad {name}: cos {cos:.5f} rel {_rel(got[name], g):.3e}")
+        assert cos > 0.98, (name, cos)
+
+
+def test_eval_matches_torch(no_tf32):
+    tb, nb = _pair("fp32", False)
+    tb.set_train(False)
+    nb.set_train(False)
+    raw = _batches(1, 16, seed=7)[0]
+    raw.crop_xy = None
+    raw.flip = None
+    lt, ct = tb.eval_step(*tb.prepare(raw))
+    ln, cn = nb.eval_step(*nb.prepare(raw))
+    assert abs(float(lt) - float(ln)) < 1e-3 * max(1.0, float(lt))
+    assert int(ct) == int(cn)
+
+
+def test_state_dict_is_the_reference_format(ref_model_module, tmp_path):
+    from cs744_ddp_b200.engine import NativeBackend
+    from cs744_ddp_b200.utils import checkpoint as ckpt
+    torch.manual_seed(0)
+    nb = NativeBackend(_cfg(backend="native", dtype="bf16"), DEV)
+    nb.train_step(*nb.prepare(_batches(1, 16)[0]), _T())
+    path = str(tmp_path / "m.pt")
+    ckpt.save_model(path, nb.state_dict())
+    ref = ref_model_module.VGG11()
+    ref.load_state_dict(torch.load(path), strict=True)            # loads into the reference model
+    for k, v in ref.state_dict().items():
+        assert v.dtype == nb.state_dict()[k].dtype
+    # and back: a fresh engine initialised from that file continues identically
+    osd = nb.optimizer_state_dict()
+    nb2 = NativeBackend(_cfg(backend="native", dtype="bf16"), DEV, init_state=ckpt.load(path)["model"])
+    nb2.load_optimizer_state_dict(osd)
+    raw = _batches(1, 16, seed=9)[0]
+    l1 = float(nb.train_step(*nb.prepare(raw), _T()))
+    l2 = float(nb2.train_step(*nb2.prepare(raw), _T()))
+    assert abs(l1 - l2) < 1e-4 * max(1.0, abs(l1))      # atomics make the last bits run-dependent
+    for k, v in nb.state_dict().items():
+        if v.dtype.is_floating_point and v.numel() > 1 and not (k.endswith(".bias") and "layers" in k):
+            assert _rel(nb2.state_dict()[k], v) < 1e-3, k
+
+
+def test_trainer_end_to_end_native():
+    import re
+    from cs744_ddp_b200.trainer import Trainer
+    from cs744_ddp_b200.utils.logger import RunLogger
+    lines = []
+    cfg = _cfg(backend="native", dtype="bf16", train_size=16 * 9, test_size=40, max_iters=8)
+    t = Trainer(cfg, RunLogger("1", 4, sink=lines.append))
+    res = t.fit()
+    assert res["total"] == 40
+    assert re.match(r"Training loss after 4 epochs is [-\d.e]+$", lines[0])
+    assert re.match(r"Forward Pass time in iter 8 is [-\d.e]+$", lines[2])
+    assert t.backend.launch_count() > 0
+    assert "libddpb200.so" in open("/proc/self/maps").read()
+
+
+def test_bucket_plans_cover_arena():
+    from cs744_ddp_b200.engine import NativeBackend
+    for plan, n in (("ddp", 3), ("per_layer", 9), ("single", 1)):
+        nb = NativeBackend(_cfg(backend="native", dtype="bf16", bucket_plan=plan, sync="bucketed"), DEV)
+        b = nb.buckets()
+        assert len(b) == n, (plan, b)
+        assert b[0][0] == 0 and all(x[0] + x[1] == y[0] for x, y in zip(b, b[1:]))
+        assert b[-1][0] + b[-1][1] == int(nb.info.arena_elems)
+        del nb

@@ -1,0 +1,54 @@
+#!/bin/bash
+# One GPU-box call.  Each risky group runs in its own process so a trapped kernel cannot take the
+# other groups down.  Usage: tools/gpu_ci.sh [stage ...]; stages: kernels engine bench kbench ref ncu
+set -u
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+OUT=gpurun_out
+STAGES="${*:-kernels engine bench}"
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > $OUT/gpu.csv 2>&1
+: > $OUT/summary.log
+run() { # name, timeout, cmd...
+  local name=$1 t=$2; shift 2
+  echo "=== $name" | tee -a $OUT/summary.log
+  timeout $t "$@" > $OUT/$name.log 2>&1
+  echo "exit=$? ($name)" | tee -a $OUT/summary.log
+  tail -n ${TAILN:-6} $OUT/$name.log | tee -a $OUT/summary.log
+}
+for st in $STAGES; do
+case $st in
+kernels)
+  run t_basic 600 python -m pytest tests/test_kernels_gpu.py -q -s -k "not conv_tc" -p no:cacheprovider
+  run t_tc 900 python -m pytest tests/test_kernels_gpu.py -q -s -k "conv_tc" -p no:cacheprovider ;;
+engine)
+  TAILN=25 run t_engine 900 python -m pytest tests/test_engine_gpu.py -q -s -p no:cacheprovider ;;
+multigpu)
+  TAILN=25 run t_multigpu 900 python -m pytest tests/test_multigpu.py -q -s -p no:cacheprovider ;;
+smoke)
+  run smoke 300 python __graft_entry__.py --smoke ;;
+bench)
+  run bench_ours 600 python bench.py --steps 50 --warmup 10
+  run bench_ours_nograph 600 python bench.py --steps 50 --warmup 10 --no-graph ;;
+bench2)
+  run bench2_p2p 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 50 --warmup 10
+  run bench2_nccl 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29534 bench.py --gpus 2 --steps 50 --warmup 10 --comm nccl
+  run bench2_ref 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29535 bench.py --gpus 2 --steps 40 --warmup 10 --impl reference ;;
+kbench)
+  TAILN=80 run kernel_bench 600 python tools/kernel_bench.py ;;
+ref)
+  run bench_ref 900 python bench.py --impl reference --steps 40 --warmup 10 ;;
+ncu)
+  # launch list of two training steps (only after the same command exited 0 without ncu)
+  python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncu_plain.log 2>&1 &&
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 200 --csv \
+      --log-file $OUT/launches.csv python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncu_run.log 2>&1
+  echo "ncu exit=$?" | tee -a $OUT/summary.log ;;
+ncufull)
+  python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncu_plain.log 2>&1 &&
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"${NCU_KERNEL:-conv3x3_tc}" -s ${NCU_SKIP:-30} -c 3 \
+      -o $OUT/prof_${NCU_TAG:-conv} -f python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncufull_run.log 2>&1
+  echo "ncufull exit=$?" | tee -a $OUT/summary.log ;;
+esac
+done
+grep -h "\[num\]\|\[eng\]" $OUT/t_*.log 2>/dev/null | sort | uniq > $OUT/numerics.log
+echo done
