@@ -18,6 +18,7 @@ bf16 compute copy).
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes
 from typing import Any, Dict, List, Optional, Tuple
 
@@ -65,7 +66,7 @@ class EngineInfo(ctypes.Structure):
         ("bn_w_off", ctypes.c_longlong * MAX_BLOCKS), ("bn_b_off", ctypes.c_longlong * MAX_BLOCKS),
         ("ch_off", ctypes.c_longlong * MAX_BLOCKS),
         ("y", ctypes.c_void_p * MAX_BLOCKS), ("act", ctypes.c_void_p * MAX_BLOCKS),
-        ("launches", ctypes.c_longlong),
+        ("launches", ctypes.c_longlong), ("graph_active", ctypes.c_int),
     ]
 
 
@@ -89,6 +90,9 @@ class NativeBackend:
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.max_batch = int(max_batch or max(cfg.per_rank_batch, 1))
         self.training = True
+        # The engine runs on its own stream: the legacy default stream cannot be captured into a
+        # CUDA graph.  ``on_stream()`` orders it after/before the caller's current stream.
+        self.stream = torch.cuda.Stream(device)
         self._lib = lib()
         self._handle = ctypes.c_void_p()
         self._comm = "none"
@@ -192,14 +196,29 @@ class NativeBackend:
         dist.barrier()
         return True
 
+    @contextlib.contextmanager
+    def on_stream(self):
+        """Run the enclosed work on the engine stream, ordered after everything already queued on
+        the caller's stream and before whatever the caller queues next.  Free when the caller
+        already made the engine stream current (the trainer and bench.py do)."""
+        cur = torch.cuda.current_stream(self.device)
+        if cur.cuda_stream == self.stream.cuda_stream:
+            yield
+            return
+        self.stream.wait_stream(cur)
+        with torch.cuda.stream(self.stream):
+            yield
+        cur.wait_stream(self.stream)
+
     # ---- data --------------------------------------------------------------------------------------
     def prepare(self, batch: RawBatch) -> Tuple[torch.Tensor, torch.Tensor]:
-        b = batch.to(self.device)
-        n = b.size
+        n = batch.size
         if n > self.max_batch:
             raise nv.NativeError(f"batch {n} exceeds the engine's max batch {self.max_batch}")
-        F.augment(b.images, None, b.crop_xy, b.flip, self.dtype, out=self.input, batch=n)
-        self.target[:n].copy_(b.labels, non_blocking=True)
+        with self.on_stream():
+            b = batch.to(self.device)
+            F.augment(b.images, None, b.crop_xy, b.flip, self.dtype, out=self.input, batch=n)
+            self.target[:n].copy_(b.labels, non_blocking=True)
         return self.input[:n], self.target[:n]
 
     def _stage(self, data: torch.Tensor, target: torch.Tensor) -> int:
@@ -217,18 +236,21 @@ class NativeBackend:
         self.training = bool(flag)
 
     def train_step(self, data: torch.Tensor, target: torch.Tensor, timer) -> torch.Tensor:
-        n = self._stage(data, target)
-        s = stream_handle()
         split = hasattr(timer, "is_async")            # region timers want the forward/backward seam
         timer.mark(0)
         if split or self._external_sync:
-            check(self._lib.ddpb_engine_forward(self._handle, n, s), "engine_forward")
+            with self.on_stream():
+                n = self._stage(data, target)
+                check(self._lib.ddpb_engine_forward(self._handle, n, stream_handle()), "engine_forward")
             timer.mark(1)
-            check(self._lib.ddpb_engine_backward(self._handle, n, s), "engine_backward")
-            if self._external_sync:
-                self._nccl_sync_and_step()
+            with self.on_stream():
+                check(self._lib.ddpb_engine_backward(self._handle, n, stream_handle()), "engine_backward")
+                if self._external_sync:
+                    self._nccl_sync_and_step()
         else:
-            check(self._lib.ddpb_engine_train_step(self._handle, n, s), "engine_train_step")
+            with self.on_stream():
+                n = self._stage(data, target)
+                check(self._lib.ddpb_engine_train_step(self._handle, n, stream_handle()), "engine_train_step")
             timer.mark(1)
         timer.mark(2)
         return self.loss[0]
@@ -263,11 +285,12 @@ class NativeBackend:
             self.sync_buffers()
 
     def eval_step(self, data: torch.Tensor, target: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-        n = self._stage(data, target)
-        s = stream_handle()
-        check(self._lib.ddpb_engine_eval_reset(self._handle, s), "eval_reset")
-        check(self._lib.ddpb_engine_eval_step(self._handle, n, s), "engine_eval_step")
-        return self.eval_loss[0].clone(), self.correct[0].clone()
+        with self.on_stream():
+            n = self._stage(data, target)
+            s = stream_handle()
+            check(self._lib.ddpb_engine_eval_reset(self._handle, s), "eval_reset")
+            check(self._lib.ddpb_engine_eval_step(self._handle, n, s), "engine_eval_step")
+            return self.eval_loss[0].clone(), self.correct[0].clone()
 
     # ---- collectives -----------------------------------------------------------------------------------
     def sync_buffers(self) -> None:
@@ -407,7 +430,8 @@ class NativeBackend:
         return self._comm
 
     def uses_graph(self) -> bool:
-        return bool(self.cfg.use_cuda_graph)
+        self._refresh_info()
+        return bool(self.info.graph_active)
 
     def synchronize(self) -> None:
         torch.cuda.synchronize(self.device)

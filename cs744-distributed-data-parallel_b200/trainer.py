@@ -14,6 +14,7 @@ Deliberate deviations from the reference, each documented in SURVEY A.3:
 """
 from __future__ import annotations
 
+import contextlib
 import time
 from typing import Dict, List, Optional, Tuple
 
@@ -100,7 +101,21 @@ class Trainer:
         return result
 
     # ------------------------------------------------------------------------------------
+    def _stream_ctx(self):
+        """The native engine runs on its own (capturable) stream; make it current for the loop so
+        that data staging, the step and the timers' events all share one stream."""
+        stream = getattr(self.backend, "stream", None)
+        return torch.cuda.stream(stream) if stream is not None else contextlib.nullcontext()
+
     def train_epoch(self, epoch: int = 0) -> List[Dict]:
+        with self._stream_ctx():
+            return self._train_epoch(epoch)
+
+    def evaluate(self) -> Tuple[float, int, int]:
+        with self._stream_ctx():
+            return self._evaluate()
+
+    def _train_epoch(self, epoch: int = 0) -> List[Dict]:
         cfg, be, timer, log = self.cfg, self.backend, self.timer, self.logger
         if not (cfg.reproduce_eval_mode_quirk and epoch > 0):
             be.set_train(True)
@@ -134,7 +149,7 @@ class Trainer:
         return log.records
 
     # ------------------------------------------------------------------------------------
-    def evaluate(self) -> Tuple[float, int, int]:
+    def _evaluate(self) -> Tuple[float, int, int]:
         """Every rank scores the full test set on its own (ref ``Part 2a/main.py:130-145``)."""
         be = self.backend
         be.set_train(False)

@@ -23,6 +23,7 @@ void set_last_error(const char* fmt, ...);
     if (_e != cudaSuccess) {                                                               \
       ::ddpb::set_last_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,                 \
                              cudaGetErrorString(_e));                                      \
+      (void)cudaGetLastError(); /* do not leave a non-sticky error behind for the next call */ \
       return DDPB_ERR_CUDA;                                                                \
     }                                                                                      \
   } while (0)

@@ -28,6 +28,24 @@ __device__ __forceinline__ void window(long long opix, int H, int W, long long* 
   in[0] = base; in[1] = base + 1; in[2] = base + W; in[3] = base + W + 1;
 }
 
+// Sum per-thread channel partials over the block's pixel lanes and add the result to gout[0..C).
+// Plain shared-memory stores + a strided read instead of shared float atomics (those compile to
+// compare-and-swap loops and serialise badly when 32 lanes hit one channel).
+// sm: [ppb * C] floats.  All threads of the block must call this.
+template <int V>
+__device__ __forceinline__ void block_reduce_channels(float* sm, const float* a, int c0, int pl, int ppb, int C,
+                                                      float* __restrict__ gout) {
+#pragma unroll
+  for (int j = 0; j < V; ++j) sm[pl * C + c0 + j] = a[j];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int q = 0; q < ppb; ++q) s += sm[q * C + c];
+    if (gout) atomicAdd(&gout[c], s);
+  }
+  __syncthreads();
+}
+
 // ------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------
@@ -97,9 +115,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
                      const float* __restrict__ beta, float* __restrict__ sums, long long Pout, int C, int H,
                      int W) {
   constexpr int V = VecOf<T>::N;
-  extern __shared__ float sm[];      // [2*C]
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
+  extern __shared__ float sm[];      // [ppb*C]
   const int groups = C / V;
   const int g = threadIdx.x % groups;
   const int pl = threadIdx.x / groups;
@@ -140,14 +156,9 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
         }
       }
     }
-#pragma unroll
-    for (int j = 0; j < V; ++j) {
-      atomicAdd(&sm[c0 + j], a1[j]);
-      atomicAdd(&sm[C + c0 + j], a2[j]);
-    }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&sums[i], sm[i]);
+  block_reduce_channels<V>(sm, a1, c0, pl, ppb, C, sums);
+  block_reduce_channels<V>(sm, a2, c0, pl, ppb, C, sums + C);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -161,9 +172,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
                     float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
                     long long P, long long Pout, int C, int H, int W) {
   constexpr int V = VecOf<T>::N;
-  extern __shared__ float sm[];      // [C]
-  for (int i = threadIdx.x; i < C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
+  extern __shared__ float sm[];      // [ppb*C]
   const int groups = C / V;
   const int g = threadIdx.x % groups;
   const int pl = threadIdx.x / groups;
@@ -214,12 +223,8 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
         store_vec<T>(dy + in[q] * C + c0, o);
       }
     }
-#pragma unroll
-    for (int j = 0; j < V; ++j) atomicAdd(&sm[c0 + j], ab[j]);
   }
-  __syncthreads();
-  if (dbias)
-    for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&dbias[i], sm[i]);
+  if (dbias) block_reduce_channels<V>(sm, ab, c0, pl, ppb, C, dbias);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -230,9 +235,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 channel_stats_kernel(const T* __restrict__ y, float* __restrict__ stats, long long P, int C) {
   constexpr int V = VecOf<T>::N;
-  extern __shared__ float sm[];
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
+  extern __shared__ float sm[];      // [ppb*C]
   const int groups = C / V;
   const int g = threadIdx.x % groups, pl = threadIdx.x / groups, ppb = blockDim.x / groups, c0 = g * V;
   float a1[V], a2[V];
@@ -245,11 +248,9 @@ channel_stats_kernel(const T* __restrict__ y, float* __restrict__ stats, long lo
 #pragma unroll
       for (int j = 0; j < V; ++j) { a1[j] += v[j]; a2[j] += v[j] * v[j]; }
     }
-#pragma unroll
-    for (int j = 0; j < V; ++j) { atomicAdd(&sm[c0 + j], a1[j]); atomicAdd(&sm[C + c0 + j], a2[j]); }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&stats[i], sm[i]);
+  block_reduce_channels<V>(sm, a1, c0, pl, ppb, C, stats);
+  block_reduce_channels<V>(sm, a2, c0, pl, ppb, C, stats + C);
 }
 
 template <typename T>
@@ -285,9 +286,17 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ x, const T* __restrict_
   for (int q = 0; q < 4; ++q) dx[in[q] * C + c] = (q == bq) ? dout[i] : from_f32<T>(0.f);
 }
 
-static int bn_grid(long long Pout, int ppb) {
+// Persistent grid: at most one wave of resident blocks (148 SMs x blocks that fit per SM); the
+// kernels stride over pixels, so a tail wave of partially filled SMs never happens.
+template <typename K>
+static int bn_grid(K kernel, long long Pout, int ppb, int smem_bytes) {
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, smem_bytes) != cudaSuccess || occ < 1) {
+    (void)cudaGetLastError();
+    occ = 2;
+  }
   long long g = (Pout + ppb - 1) / ppb;
-  const long long cap = 148 * 8;
+  const long long cap = 148LL * occ;
   return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
@@ -313,7 +322,7 @@ int fwd_launch(const void* y, const float* stats, const float* gamma, const floa
   if (rc) return rc;
   long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
   int ppb = 256 / (C / VecOf<T>::N);
-  bn_fwd_kernel<T, POOL><<<bn_grid(Pout, ppb), 256, 0, stream>>>(
+  bn_fwd_kernel<T, POOL><<<bn_grid(bn_fwd_kernel<T, POOL>, Pout, ppb, 0), 256, 0, stream>>>(
       (const T*)y, stats, gamma, beta, (T*)out, save_mean, save_invstd, rm, rv, nbt, P, Pout, C, H, W, eps,
       momentum, training);
   DDPB_LAUNCH_CHECK();
@@ -328,11 +337,11 @@ int bwd_launch(const void* dout, const void* y, const float* mean, const float* 
   if (rc) return rc;
   long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
   int ppb = 256 / (C / VecOf<T>::N);
-  int grid = bn_grid(Pout, ppb);
-  bn_bwd_reduce_kernel<T, POOL><<<grid, 256, 2 * C * sizeof(float), stream>>>(
+  const int smem = 256 * VecOf<T>::N * sizeof(float);      // [ppb][C] partials
+  bn_bwd_reduce_kernel<T, POOL><<<bn_grid(bn_bwd_reduce_kernel<T, POOL>, Pout, ppb, smem), 256, smem, stream>>>(
       (const T*)dout, (const T*)y, mean, invstd, gamma, beta, sums, Pout, C, H, W);
   DDPB_LAUNCH_CHECK();
-  bn_bwd_apply_kernel<T, POOL><<<grid, 256, C * sizeof(float), stream>>>(
+  bn_bwd_apply_kernel<T, POOL><<<bn_grid(bn_bwd_apply_kernel<T, POOL>, Pout, ppb, smem), 256, smem, stream>>>(
       (const T*)dout, (const T*)y, mean, invstd, gamma, beta, sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C,
       H, W);
   DDPB_LAUNCH_CHECK();
@@ -372,13 +381,13 @@ extern "C" int ddpb_channel_stats(const void* y, float* stats, long long pixels,
     int rc = bn_check<bf16>(C, 2, 2, false);
     if (rc) return rc;
     int ppb = 256 / (C / 8);
-    channel_stats_kernel<bf16><<<bn_grid(pixels, ppb), 256, 2 * C * sizeof(float), stream>>>(
+    channel_stats_kernel<bf16><<<bn_grid(channel_stats_kernel<bf16>, pixels, ppb, 256 * 8 * 4), 256, 256 * 8 * 4, stream>>>(
         (const bf16*)y, stats, pixels, C);
   } else {
     int rc = bn_check<float>(C, 2, 2, false);
     if (rc) return rc;
     int ppb = 256 / (C / 4);
-    channel_stats_kernel<float><<<bn_grid(pixels, ppb), 256, 2 * C * sizeof(float), stream>>>(
+    channel_stats_kernel<float><<<bn_grid(channel_stats_kernel<float>, pixels, ppb, 256 * 4 * 4), 256, 256 * 4 * 4, stream>>>(
         (const float*)y, stats, pixels, C);
   }
   DDPB_LAUNCH_CHECK();

@@ -389,16 +389,35 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
     // NOTE: that eager run was a real step; the caller asked for exactly one, so capture only and
     // launch the graph from the NEXT call on.
     Graph g;
-    cudaGraph_t graph;
+    cudaGraph_t graph = nullptr;
     e->counting = 0;
-    DDPB_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    cudaError_t ce = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+    if (ce != cudaSuccess) {
+      // e.g. the legacy default stream cannot be captured: keep running eagerly, remember why
+      (void)cudaGetLastError();
+      set_last_error("CUDA graph capture unavailable (%s); running eagerly", cudaGetErrorString(ce));
+      e->cfg.use_graph = 0;
+      return DDPB_OK;
+    }
     int rc = run_kind(e, kind, B, s);
-    cudaError_t ce = cudaStreamEndCapture(s, &graph);
-    if (rc) return rc;
-    DDPB_CUDA_CHECK(ce);
+    ce = cudaStreamEndCapture(s, &graph);
+    if (rc || ce != cudaSuccess || !graph) {
+      (void)cudaGetLastError();
+      if (graph) cudaGraphDestroy(graph);
+      e->cfg.use_graph = 0;
+      if (rc) return rc;
+      set_last_error("CUDA graph capture failed (%s); running eagerly", cudaGetErrorString(ce));
+      return DDPB_OK;
+    }
     g.launches = e->counting;
-    DDPB_CUDA_CHECK(cudaGraphInstantiate(&g.exec, graph, 0));
+    ce = cudaGraphInstantiate(&g.exec, graph, 0);
     cudaGraphDestroy(graph);
+    if (ce != cudaSuccess) {
+      (void)cudaGetLastError();
+      e->cfg.use_graph = 0;
+      set_last_error("cudaGraphInstantiate failed (%s); running eagerly", cudaGetErrorString(ce));
+      return DDPB_OK;
+    }
     e->graphs[key] = g;
     return DDPB_OK;
   }
@@ -468,6 +487,7 @@ extern "C" int ddpb_engine_info(void* handle, ddpb_engine_info_t* out) {
     out->y[i] = b.y; out->act[i] = b.act;
   }
   out->launches = e->launches;
+  out->graph_active = e->cfg.use_graph && !e->graphs.empty();
   return DDPB_OK;
 }
 

@@ -169,6 +169,7 @@ typedef struct ddpb_engine_info_t {
       bn_b_off[DDPB_MAX_BLOCKS], ch_off[DDPB_MAX_BLOCKS];
   void *y[DDPB_MAX_BLOCKS], *act[DDPB_MAX_BLOCKS];
   long long launches;   /* kernels launched by the engine so far (graph replays included) */
+  int graph_active;     /* 1 when steps are being replayed from captured CUDA graphs */
 } ddpb_engine_info_t;
 
 /* ALLOCATES all device buffers (cudaMalloc), including the symmetric arena. */
