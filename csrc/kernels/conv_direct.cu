@@ -238,6 +238,194 @@ first_layer_wgrad(const T* __restrict__ dy, const T* __restrict__ x, float* __re
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// first layer on 32x32 images (the CIFAR case), tuned: a tile is 4 image rows (128 pixels); the
+// 6 input rows it needs are staged once in shared memory as fp32 with a zero halo, so no thread
+// touches global memory for x again and the conv's padding needs no branches.
+// ------------------------------------------------------------------------------------------
+constexpr int FL_W = 32, FL_ROWS = 4, FL_TILE = FL_W * FL_ROWS;     // 128 pixels
+constexpr int FL_XR = FL_ROWS + 2, FL_XW = FL_W + 2;                // staged rows x (cols + halo)
+
+template <typename T>
+__device__ __forceinline__ void fl_stage_x(const T* __restrict__ x, float (*xs)[FL_XW][3], long long tile, int H) {
+  // tile -> image n, first row h0; xs[r][c][ci] = x[n, h0-1+r, c-1, ci] or 0 outside the image
+  const int tiles_per_img = H / FL_ROWS;
+  const long long n = tile / tiles_per_img;
+  const int h0 = (int)(tile % tiles_per_img) * FL_ROWS;
+  for (int i = threadIdx.x; i < FL_XR * FL_XW; i += blockDim.x) {
+    const int r = i / FL_XW, c = i % FL_XW;
+    const int ih = h0 - 1 + r, iw = c - 1;
+    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+    if (ih >= 0 && ih < H && iw >= 0 && iw < FL_W) {
+      const T* p = x + ((n * H + ih) * FL_W + iw) * 3;
+      v0 = to_f32(p[0]); v1 = to_f32(p[1]); v2 = to_f32(p[2]);
+    }
+    xs[r][c][0] = v0; xs[r][c][1] = v1; xs[r][c][2] = v2;
+  }
+}
+
+// forward: thread = 2 vertically adjacent pixels x 16 output channels (32 accumulators);
+// warps share the channel quarter, so weight reads are broadcast LDS.128.
+template <typename T>
+__global__ void __launch_bounds__(256, 1)      // 32 acc + 32 stat registers per thread: no spills at 1 CTA/SM
+first_layer_fwd_32(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                   T* __restrict__ y, float* __restrict__ stats, int B, int H) {
+  constexpr int CO = 64, K = 27, CG = 16;
+  __shared__ __align__(16) float wt[K][CO];
+  __shared__ float sb[CO];
+  __shared__ float xs[2][FL_XR][FL_XW][3];
+  __shared__ float sred[8][2 * CG];
+  for (int i = threadIdx.x; i < K * CO; i += blockDim.x) wt[i % K][i / K] = w[i];
+  if (threadIdx.x < CO) sb[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
+  const int pp = threadIdx.x & 63, cq = threadIdx.x >> 6, c0 = cq * CG;
+  const int wcol = pp & 31, rp = pp >> 5;               // pixel pair: rows 2*rp and 2*rp+1, column wcol
+  const long long tiles = (long long)B * (H / FL_ROWS);
+  float s1[CG], s2[CG];
+#pragma unroll
+  for (int j = 0; j < CG; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
+  int buf = 0;
+  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, buf ^= 1) {
+    fl_stage_x<T>(x, xs[buf], tile, H);
+    __syncthreads();           // also orders the previous iteration's reads of the other buffer
+    float acc[2][CG];
+#pragma unroll
+    for (int j = 0; j < CG; ++j) { acc[0][j] = sb[c0 + j]; acc[1][j] = acc[0][j]; }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {            // input rows 2*rp + r feed output row 0 (r<3) and 1 (r>0)
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) {
+          const float xv = xs[buf][2 * rp + r][wcol + s][ci];
+          if (r < 3) {
+            const float4* wr = reinterpret_cast<const float4*>(&wt[(r * 3 + s) * 3 + ci][c0]);
+#pragma unroll
+            for (int q = 0; q < CG / 4; ++q) {
+              const float4 wv = wr[q];
+              acc[0][4 * q + 0] = fmaf(xv, wv.x, acc[0][4 * q + 0]);
+              acc[0][4 * q + 1] = fmaf(xv, wv.y, acc[0][4 * q + 1]);
+              acc[0][4 * q + 2] = fmaf(xv, wv.z, acc[0][4 * q + 2]);
+              acc[0][4 * q + 3] = fmaf(xv, wv.w, acc[0][4 * q + 3]);
+            }
+          }
+          if (r > 0) {
+            const float4* wr = reinterpret_cast<const float4*>(&wt[((r - 1) * 3 + s) * 3 + ci][c0]);
+#pragma unroll
+            for (int q = 0; q < CG / 4; ++q) {
+              const float4 wv = wr[q];
+              acc[1][4 * q + 0] = fmaf(xv, wv.x, acc[1][4 * q + 0]);
+              acc[1][4 * q + 1] = fmaf(xv, wv.y, acc[1][4 * q + 1]);
+              acc[1][4 * q + 2] = fmaf(xv, wv.z, acc[1][4 * q + 2]);
+              acc[1][4 * q + 3] = fmaf(xv, wv.w, acc[1][4 * q + 3]);
+            }
+          }
+        }
+      }
+    }
+    constexpr int V = 16 / sizeof(T);
+#pragma unroll
+    for (int o = 0; o < 2; ++o) {
+      const long long p = tile * FL_TILE + (2 * rp + o) * FL_W + wcol;
+      T* yp = y + p * CO + c0;
+#pragma unroll
+      for (int q = 0; q < CG / V; ++q) {
+        float tmp[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          tmp[j] = to_f32(from_f32<T>(acc[o][q * V + j]));      // statistics of the stored values
+          s1[q * V + j] += tmp[j];
+          s2[q * V + j] += tmp[j] * tmp[j];
+        }
+        store_vec<T>(yp + q * V, tmp);
+      }
+    }
+  }
+  if (stats) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int j = 0; j < CG; ++j) {
+      const float a = warp_sum(s1[j]), b = warp_sum(s2[j]);
+      if (lane == 0) { sred[warp][j] = a; sred[warp][CG + j] = b; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2 * CO) {          // channel c lives in warps 2*(c/16) and 2*(c/16)+1
+      const int c = threadIdx.x % CO, which = threadIdx.x / CO;
+      const int q = c / CG, j = c % CG;
+      atomicAdd(&stats[which * CO + c], sred[2 * q][which * CG + j] + sred[2 * q + 1][which * CG + j]);
+    }
+  }
+}
+
+// wgrad: dW[64][27] += dY^T * im2col(X).  Per tile: dY [128][64] and the 6 input rows are staged in
+// shared memory; thread = 8 output channels x 7 taps (56 accumulators) over 1 of 8 pixel streams.
+template <typename T>
+__global__ void __launch_bounds__(256)
+first_layer_wgrad_32(const T* __restrict__ dy, const T* __restrict__ x, float* __restrict__ dw, int B, int H) {
+  constexpr int CO = 64, K = 27, KP = 28;
+  __shared__ __align__(16) float sdy[FL_TILE][CO];      // 32 KB
+  __shared__ float xs[FL_XR][FL_XW][3];
+  const int lane = threadIdx.x & 31, stream = threadIdx.x >> 5;     // one warp per pixel stream
+  const int cg = lane & 7, tg = lane >> 3;                          // 8 channel groups x 4 tap groups
+  // offsets (relative to the pixel's top-left patch corner) of this thread's 7 patch elements
+  int koff[7];
+#pragma unroll
+  for (int b = 0; b < 7; ++b) {
+    const int k = tg * 7 + b;
+    const int kk = k < K ? k : 0;                       // k = 27 is padding: its column is never copied out
+    const int tap = kk / 3, ci = kk % 3, r = tap / 3, s = tap % 3;
+    koff[b] = (r * FL_XW + s) * 3 + ci;
+  }
+  float acc[8][7];
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 7; ++b) acc[a][b] = 0.f;
+  const long long tiles = (long long)B * (H / FL_ROWS);
+  constexpr int V = 16 / sizeof(T);
+  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    __syncthreads();
+    fl_stage_x<T>(x, xs, tile, H);
+    for (int i = threadIdx.x; i < FL_TILE * CO / V; i += blockDim.x) {
+      float tmp[V];
+      load_vec<T>(dy + tile * FL_TILE * CO + (long long)i * V, tmp);
+#pragma unroll
+      for (int j = 0; j < V; ++j) (&sdy[0][0])[i * V + j] = tmp[j];
+    }
+    __syncthreads();
+    const float* xflat = &xs[0][0][0];
+#pragma unroll 2
+    for (int i = 0; i < FL_TILE / 8; ++i) {
+      const int pl = stream * (FL_TILE / 8) + i;            // pixel inside the tile
+      const int base = ((pl / FL_W) * FL_XW + (pl % FL_W)) * 3;
+      const float4 d0 = *reinterpret_cast<const float4*>(&sdy[pl][cg * 8]);
+      const float4 d1 = *reinterpret_cast<const float4*>(&sdy[pl][cg * 8 + 4]);
+      const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+      for (int b = 0; b < 7; ++b) {
+        const float xv = xflat[base + koff[b]];
+#pragma unroll
+        for (int a = 0; a < 8; ++a) acc[a][b] = fmaf(d[a], xv, acc[a][b]);
+      }
+    }
+  }
+  // combine the 8 pixel streams (deterministic order), then one atomic per output element
+  __syncthreads();
+  float* sacc = &sdy[0][0];                              // reuse: [64][28]
+  for (int s = 0; s < 8; ++s) {
+    if (stream == s) {
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 7; ++b) {
+          float* dst = &sacc[(cg * 8 + a) * KP + tg * 7 + b];
+          *dst = (s == 0 ? 0.f : *dst) + acc[a][b];
+        }
+    }
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < CO * K; i += blockDim.x) atomicAdd(&dw[i], sacc[(i / K) * KP + (i % K)]);
+}
+
 }  // namespace ddpb
 
 using namespace ddpb;
@@ -248,6 +436,16 @@ extern "C" int ddpb_conv3x3_fwd_simt(const void* x, const float* w, const float*
                                      int B, int H, int W, int Cin, int Cout, int dtype,
                                      cudaStream_t stream) {
   long long total = (long long)B * H * W * Cout;
+  if (Cin == 3 && Cout == 64 && W == FL_W && H % FL_ROWS == 0) {
+    long long tiles = (long long)B * (H / FL_ROWS);
+    int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
+    if (dtype == DDPB_BF16)
+      first_layer_fwd_32<bf16><<<grid, 256, 0, stream>>>((const bf16*)x, w, bias, (bf16*)y, stats, B, H);
+    else
+      first_layer_fwd_32<float><<<grid, 256, 0, stream>>>((const float*)x, w, bias, (float*)y, stats, B, H);
+    DDPB_LAUNCH_CHECK();
+    return DDPB_OK;
+  }
   if (Cin == 3 && Cout == 64) {
     int grid = ceil_div((long long)B * H * W, 64);
     if (grid > 148 * 8) grid = 148 * 8;
@@ -283,6 +481,16 @@ extern "C" int ddpb_conv3x3_dgrad_simt(const void* dy, const float* w, void* dx,
 // dw (fp32 [Cout,3,3,Cin]) is ACCUMULATED into: zero it first.
 extern "C" int ddpb_conv3x3_wgrad_simt(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
                                        int Cout, int dtype, cudaStream_t stream) {
+  if (Cin == 3 && Cout == 64 && W == FL_W && H % FL_ROWS == 0) {
+    long long tiles = (long long)B * (H / FL_ROWS);
+    int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
+    if (dtype == DDPB_BF16)
+      first_layer_wgrad_32<bf16><<<grid, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, B, H);
+    else
+      first_layer_wgrad_32<float><<<grid, 256, 0, stream>>>((const float*)dy, (const float*)x, dw, B, H);
+    DDPB_LAUNCH_CHECK();
+    return DDPB_OK;
+  }
   if (Cin == 3 && Cout == 64) {
     int grid = ceil_div((long long)B * H * W, 64);
     if (grid > 148 * 2) grid = 148 * 2;

@@ -327,17 +327,19 @@ static int backward(Engine* e, int B, cudaStream_t s) {
                                     e->grad + b.bn_b.off, e->grad + b.conv_b.off, B, b.hw, b.hw, b.cout, b.pool,
                                     dt, s));
     e->counting += 1;     // the BN backward is two launches (reduce + apply)
+    // dgrad BEFORE wgrad: (1) it is on the critical path of the next layer; (2) the bucket's fused
+    // reduce+SGD overwrites this layer's weights as soon as wgrad is done, so every reader of the
+    // old weights (dgrad) has to be ordered before the bucket's ready event.
     if (use_tc(e, b)) {
-      LAUNCH(e, ddpb_conv3x3_wgrad_tc(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, s));
-      ECHECK(buckets_ready(e, i, s));
       if (i > 0)
         LAUNCH(e, ddpb_conv3x3_dgrad_tc(e->dy_buf, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+      LAUNCH(e, ddpb_conv3x3_wgrad_tc(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, s));
     } else {
-      LAUNCH(e, ddpb_conv3x3_wgrad_simt(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, s));
-      ECHECK(buckets_ready(e, i, s));
       if (i > 0)
         LAUNCH(e, ddpb_conv3x3_dgrad_simt(e->dy_buf, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
+      LAUNCH(e, ddpb_conv3x3_wgrad_simt(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, s));
     }
+    ECHECK(buckets_ready(e, i, s));
   }
   // ---- end of backward: the non-overlapped strategies synchronise here, like the reference ----
   const bool p2p = c.world > 1 && e->peers_set;

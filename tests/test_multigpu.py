@@ -40,7 +40,7 @@ def _worker(rank, port, sync, comm, dtype, outdir, plan):
     dist.init_process_group("nccl", rank=rank, world_size=WORLD, device_id=torch.device("cuda", rank))
     torch.manual_seed(0)
     cfg = TrainConfig(num_nodes=WORLD, rank=rank, sync=sync, comm=comm, dtype=dtype, device="cuda",
-                      backend="native", global_batch=B * WORLD, synthetic=True, bucket_plan=plan)
+                      backend="native", global_batch=B * WORLD, synthetic=True, bucket_plan=plan, lr=0.01)
     be = NativeBackend(cfg, torch.device("cuda", rank))
     split = synthetic_cifar10(STEPS * B, seed=10 + rank)
     losses = []
