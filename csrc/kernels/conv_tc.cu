@@ -43,8 +43,8 @@ struct ConvTcParams {
 template <int BN, int STAGES, bool DGRAD>
 __global__ void __launch_bounds__(192)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  bf16* __restrict__ out, const float* __restrict__ bias, float* __restrict__ stats,
-                  const ConvTcParams prm) {
+                  const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias,
+                  float* __restrict__ stats, const ConvTcParams prm) {
   constexpr int B_BYTES = BN * KCHUNK * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
@@ -54,7 +54,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* accum_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
-  float* red = reinterpret_cast<float*>(tmem_slot + 2);   // [2*BN] per-CTA stats partials (fprop)
+  float* bias_s = reinterpret_cast<float*>(tmem_slot + 2);   // [BN] bias of this tile's channels (fprop)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tile = blockIdx.x, n_tile = blockIdx.y;
@@ -68,12 +68,13 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     mbar_init(accum_bar, 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<BN>(tmem_slot);
-  if (!DGRAD) for (int i = threadIdx.x; i < 2 * BN; i += blockDim.x) red[i] = 0.f;
+  if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? bias[n_tile * BN + i] : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -130,63 +131,76 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
+    // 1. TMEM -> registers -> (+bias) -> bf16 -> shared memory, in the 128B-swizzled layout a TMA
+    //    store expects (the pipeline stages are free once the accumulator barrier has fired).
+    // 2. one thread stores the tile with TMA (coalesced, clipped at the tensor edge, asynchronous).
+    // 3. fprop: per-channel sum / sum-of-squares of the ROUNDED tile, read back from shared memory
+    //    (8-byte column-group loads; no shuffles, no shared-memory atomics).
     const int q = warp & 3;                    // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;             // pixel row inside the tile
-    const long long p = (long long)m_tile * TILE_M + row;
-    const bool valid = p < prm.total_pixels;
+    const int t = threadIdx.x - 64;            // 0..127 among the epilogue threads
+    uint8_t* tile = smem;                      // [BN/64][128 rows][128 B]
+    float* red = reinterpret_cast<float*>(smem + 32768);      // [parts][2*BN]
     mbar_wait(accum_bar, 0);
     tc_fence_after();
-    bf16* orow = out + p * prm.n_out + n_tile * BN;
 #pragma unroll 1
     for (int c = 0; c < BN; c += 32) {
       float v[32];
       tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c, v);
       tmem_ld_wait();
-      if (!DGRAD && bias) {
+      if (!DGRAD) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] += __ldg(&bias[n_tile * BN + c + j]);
+        for (int j = 0; j < 32; ++j) v[j] += bias_s[c + j];
       }
-      uint32_t pk[16];
+      uint8_t* rbase = tile + (c >> 6) * (TILE_M * 128) + row * 128;
+      const int j0 = (c & 63) >> 3;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-      if (valid) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          reinterpret_cast<uint4*>(orow + c)[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+      for (int j = 0; j < 4; ++j) {
+        uint4 pk = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                              pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        *reinterpret_cast<uint4*>(rbase + (((j0 + j) ^ (row & 7)) << 4)) = pk;
       }
-      if (!DGRAD && stats) {
-        // BatchNorm statistics of the ROUNDED outputs; column sums over the warp's 32 rows via a
-        // halving butterfly (31 shuffles per 32 columns): lane l ends with column l's total.
-        float a[32], b[32];
+    }
+    fence_async_proxy();                                       // generic-proxy writes -> visible to TMA
+    asm volatile("bar.sync 1, 128;" ::: "memory");             // the four epilogue warps only
+    if (t == 0) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          float2 f = unpack_bf16x2(pk[j]);
-          a[2 * j] = valid ? f.x : 0.f; a[2 * j + 1] = valid ? f.y : 0.f;
-          b[2 * j] = a[2 * j] * a[2 * j]; b[2 * j + 1] = a[2 * j + 1] * a[2 * j + 1];
-        }
-#pragma unroll
-        for (int step = 16, n = 32; step >= 1; step >>= 1, n >>= 1) {
-          const bool upper = (lane & step) != 0;
-#pragma unroll
-          for (int i = 0; i < n / 2; ++i) {
-            float sa_ = upper ? a[i] : a[i + n / 2], ka = upper ? a[i + n / 2] : a[i];
-            float sb_ = upper ? b[i] : b[i + n / 2], kb = upper ? b[i + n / 2] : b[i];
-            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa_, step);
-            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb_, step);
-          }
-        }
-        atomicAdd(&red[c + lane], a[0]);
-        atomicAdd(&red[BN + c + lane], b[0]);
-      }
+      for (int hblk = 0; hblk < BN / 64; ++hblk)
+        tma_store_2d(&tmC, tile + hblk * (TILE_M * 128), n_tile * BN + hblk * 64, m_tile * TILE_M);
+      tma_store_commit();
     }
     if (!DGRAD && stats) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");     // the four epilogue warps only
-      const int t = threadIdx.x - 64;
-      for (int i = t; i < BN; i += 128) {
-        atomicAdd(&stats[n_tile * BN + i], red[i]);
-        atomicAdd(&stats[prm.n_out + n_tile * BN + i], red[BN + i]);
+      constexpr int GROUPS = BN / 4, PARTS = 128 / GROUPS, ROWS = TILE_M / PARTS;
+      const int g = t % GROUPS, part = t / GROUPS;
+      const long long left = prm.total_pixels - (long long)m_tile * TILE_M;
+      const int valid_rows = left < TILE_M ? (int)left : TILE_M;
+      const uint8_t* cbase = tile + ((4 * g) >> 6) * (TILE_M * 128);
+      const int jc = ((4 * g) & 63) >> 3, inner = ((4 * g) & 7) * 2;
+      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+      const int r_end = min(valid_rows, (part + 1) * ROWS);
+#pragma unroll 4
+      for (int r = part * ROWS; r < r_end; ++r) {
+        const uint2 u = *reinterpret_cast<const uint2*>(cbase + r * 128 + ((jc ^ (r & 7)) << 4) + inner);
+        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
+        s1[0] += a.x; s1[1] += a.y; s1[2] += b.x; s1[3] += b.y;
+        s2[0] = fmaf(a.x, a.x, s2[0]); s2[1] = fmaf(a.y, a.y, s2[1]);
+        s2[2] = fmaf(b.x, b.x, s2[2]); s2[3] = fmaf(b.y, b.y, s2[3]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        red[part * 2 * BN + 4 * g + j] = s1[j];
+        red[part * 2 * BN + BN + 4 * g + j] = s2[j];
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int i = t; i < 2 * BN; i += 128) {
+        float acc = 0.f;
+#pragma unroll
+        for (int pz = 0; pz < PARTS; ++pz) acc += red[pz * 2 * BN + i];
+        const int col = i < BN ? i : i - BN;
+        atomicAdd(&stats[(i < BN ? 0 : prm.n_out) + n_tile * BN + col], acc);
       }
     }
+    if (t == 0) tma_store_wait_read();        // shared memory must stay valid until TMA has read it
   }
   tc_fence_before();
   __syncthreads();
@@ -194,7 +208,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 }
 
 template <int BN, int STAGES>
-constexpr int conv_tc_smem() { return STAGES * (A_BYTES + BN * KCHUNK * 2) + (2 * STAGES + 1) * 8 + 16 + 2 * BN * 4 + 1024; }
+constexpr int conv_tc_smem() { return STAGES * (A_BYTES + BN * KCHUNK * 2) + (2 * STAGES + 1) * 8 + 16 + BN * 4 + 1024; }
 
 // pixel box (w, h, n) holding `pixels` (128 or 64) consecutive NHWC pixels of an HxW image
 void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn) {
@@ -209,8 +223,11 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   const int Nc = DGRAD ? Cin : Cout;     // output channels
   int bw, bh, bn;
   pixel_box(H, W, TILE_M, &bw, &bh, &bn);
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmC;
   int rc = make_tmap_nhwc_bf16(&tmA, in, B, H, W, Kc, KCHUNK, bw, bh, bn);
+  if (rc) return rc;
+  // output matrix [pixels][Nc]; the epilogue stores 64-column x 128-row boxes (clipped at the edge)
+  rc = make_tmap_2d_bf16(&tmC, out, (long long)B * H * W, Nc, 64, TILE_M);
   if (rc) return rc;
   // weight matrix [Cout rows][9*Cin cols]; fprop box = 64 cols x BN rows, dgrad box = 64 cols x 64 rows
   rc = make_tmap_2d_bf16(&tmB, w, Cout, 9LL * Cin, KCHUNK, DGRAD ? 64 : BN);
@@ -233,9 +250,14 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  kern<<<grid, 192, smem, stream>>>(tmA, tmB, out, bias, stats, prm);
+  kern<<<grid, 192, smem, stream>>>(tmA, tmB, tmC, bias, stats, prm);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
+}
+
+static long long cta_count(int B, int H, int W, int n_channels, int tile_n) {
+  long long m_tiles = H * W >= TILE_M ? (long long)B * (H * W / TILE_M) : ceil_div(B, TILE_M / (H * W));
+  return m_tiles * (n_channels / tile_n);
 }
 
 static int check_shapes(int B, int H, int W, int Cin, int Cout) {
@@ -260,8 +282,12 @@ extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const floa
   DDPB_REQUIRE(Cout % tile_n == 0, "conv_tc fwd: Cout %d not a multiple of tile %d", Cout, tile_n);
   if (tile_n == 128)
     return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
-  if (tile_n == 64)
+  if (tile_n == 64) {
+    // fewer CTAs than SMs: one CTA per SM with a deep pipeline (more bytes in flight per CTA)
+    if (cta_count(B, H, W, Cout, 64) <= 148)
+      return launch<64, 8, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
     return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
+  }
   DDPB_REQUIRE(false, "conv_tc fwd: tile_n must be 64 or 128");
 }
 
@@ -274,7 +300,10 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
   DDPB_REQUIRE(Cin % tile_n == 0, "conv_tc dgrad: Cin %d not a multiple of tile %d", Cin, tile_n);
   if (tile_n == 128)
     return launch<128, 3, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-  if (tile_n == 64)
+  if (tile_n == 64) {
+    if (cta_count(B, H, W, Cin, 64) <= 148)
+      return launch<64, 8, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
     return launch<64, 4, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+  }
   DDPB_REQUIRE(false, "conv_tc dgrad: tile_n must be 64 or 128");
 }

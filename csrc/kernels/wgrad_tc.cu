@@ -165,9 +165,16 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
   prm.Cin = Cin; prm.Cout = Cout;
   int base_ctas = (Cout / WG_M) * (Cin / WG_N) * 3;
   if (split_k <= 0) {
-    split_k = (148 + base_ctas - 1) / base_ctas;
-    if (split_k > prm.total_chunks / 4) split_k = prm.total_chunks / 4;     // keep >= 4 chunks per CTA
-    if (split_k < 1) split_k = 1;
+    // one CTA per SM: pick the split that minimises (waves) x (k-iterations per CTA + fixed cost);
+    // 150 CTAs on 148 SMs would cost a whole second wave
+    long long best_cost = -1;
+    const int max_split = prm.total_chunks < 64 ? prm.total_chunks : 64;
+    for (int s = 1; s <= max_split; ++s) {
+      long long waves = ((long long)base_ctas * s + 147) / 148;
+      long long iters = (prm.total_chunks + s - 1) / s;
+      long long cost = waves * (iters + 3);
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; split_k = s; }
+    }
   }
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
   constexpr int STAGES = 4;

@@ -45,7 +45,7 @@ ncu)
   echo "ncu exit=$?" | tee -a $OUT/summary.log ;;
 ncufull)
   python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncu_plain.log 2>&1 &&
-  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"${NCU_KERNEL:-conv3x3_tc}" -s ${NCU_SKIP:-30} -c 3 \
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"${NCU_KERNEL:-conv3x3_tc}" -s ${NCU_SKIP:-30} -c ${NCU_COUNT:-3} \
       -o $OUT/prof_${NCU_TAG:-conv} -f python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncufull_run.log 2>&1
   echo "ncufull exit=$?" | tee -a $OUT/summary.log ;;
 esac
