@@ -8,6 +8,8 @@
 // plus the running-stat update (momentum 0.1, unbiased variance) done by block 0.
 // Backward is two passes (the two per-channel reductions BN needs, then dX); the pool routing
 // and ReLU mask are recomputed from the saved conv output instead of being stored.
+#include <mutex>
+
 #include "../common.cuh"
 #include "../../include/ddp_b200.h"
 
@@ -372,6 +374,68 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* dout, const void* y, const floa
   if (dtype == DDPB_BF16) return pool ? bwd_launch<bf16, true>(ARGS) : bwd_launch<bf16, false>(ARGS);
   return pool ? bwd_launch<float, true>(ARGS) : bwd_launch<float, false>(ARGS);
 #undef ARGS
+}
+
+// ------------------------------------------------------------------------------------------
+// BN backward for callers that have no workspace to give.
+//
+// ddpb_bn_relu_pool_bwd needs 2*C floats of zeroed scratch for its two per-channel reductions
+// and expects the caller to own that buffer.  Some callers cannot: a host program that handed the
+// whole GPU to its own memory pool at start-up and forbids further cudaMalloc calls, or a plug-in
+// slot whose signature carries only the op's inputs and outputs and no workspace argument.  For
+// them the scratch lives inside the library image, as a fixed device array:
+//
+//  * capacity: DDPB_BN_NOALLOC_MAX_C channels (2 * 2048 floats = 16 KB).  Every GPU that loads the
+//    library carries these 16 KB until the process exits, whether or not this entry point is used;
+//  * the array is one per device and shared by all calls: it still holds the previous call's sums,
+//    so each call clears the 2*C floats it is about to use (a memset enqueued on `stream`) before
+//    the kernels run.  Two calls whose work overlaps on the GPU (different streams, or different
+//    host threads) would clear and accumulate into the same floats and corrupt each other:
+//    serialise them;
+//  * the first call on a device looks up that device's address of the array (the host-side name
+//    of a __device__ variable is not a device pointer) and caches it; that look-up is a host-side
+//    runtime query, so make the first call on each device before any stream capture begins.
+//
+// No cudaMalloc / cudaFree and no allocating library routine runs here.  Results are the same as
+// ddpb_bn_relu_pool_bwd's up to the order of the floating-point atomic additions.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_bn_bwd_static_sums[2 * DDPB_BN_NOALLOC_MAX_C];
+
+namespace {
+std::mutex g_static_sums_mutex;
+float* g_static_sums_addr[64] = {nullptr};     // per device ordinal
+
+// Device address of g_bn_bwd_static_sums on the CURRENT device (looked up once per device).
+int static_sums_for_current_device(float** out) {
+  int dev = -1;
+  DDPB_CUDA_CHECK(cudaGetDevice(&dev));
+  DDPB_REQUIRE(dev >= 0 && dev < 64, "bn_bwd_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_sums_mutex);
+  if (!g_static_sums_addr[dev]) {
+    float* p = nullptr;
+    DDPB_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_bn_bwd_static_sums));
+    DDPB_REQUIRE(p != nullptr, "bn_bwd_noalloc: cudaGetSymbolAddress returned a null pointer");
+    g_static_sums_addr[dev] = p;
+  }
+  *out = g_static_sums_addr[dev];
+  return DDPB_OK;
+}
+}  // namespace
+
+extern "C" int ddpb_bn_relu_pool_bwd_noalloc(const void* dout, const void* y, const float* save_mean,
+                                             const float* save_invstd, const float* gamma, const float* beta,
+                                             void* dy, float* dgamma, float* dbeta, float* dbias, int batch,
+                                             int H, int W, int C, int pool, int dtype, cudaStream_t stream) {
+  DDPB_REQUIRE(C > 0 && C <= DDPB_BN_NOALLOC_MAX_C,
+               "bn_bwd_noalloc: C = %d exceeds the built-in scratch capacity of %d channels; use "
+               "ddpb_bn_relu_pool_bwd with a caller-owned [2*C] buffer instead",
+               C, DDPB_BN_NOALLOC_MAX_C);
+  float* sums = nullptr;
+  int rc = static_sums_for_current_device(&sums);
+  if (rc) return rc;
+  DDPB_CUDA_CHECK(cudaMemsetAsync(sums, 0, sizeof(float) * 2 * (size_t)C, stream));
+  return ddpb_bn_relu_pool_bwd(dout, y, save_mean, save_invstd, gamma, beta, sums, dy, dgamma, dbeta, dbias, batch,
+                               H, W, C, pool, dtype, stream);
 }
 
 // stats[0:C] += sum over pixels, stats[C:2C] += sum of squares (stats must be zeroed by the caller)

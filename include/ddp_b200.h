@@ -70,6 +70,20 @@ int ddpb_bn_relu_pool_bwd(const void* dout, const void* y, const float* save_mea
                           float* dbeta, float* dbias, int batch, int H, int W, int C, int pool, int dtype,
                           cudaStream_t stream);
 
+/* Same computation as ddpb_bn_relu_pool_bwd for callers that cannot supply the [2*C] scratch: a
+ * host that pre-committed all device memory to its own pool, or a plug-in interface that passes only
+ * inputs and outputs.  The scratch is a fixed 16 KB device array inside the library (resident on
+ * every GPU that loads it), so this call performs no allocation of any kind.  Limits: C <=
+ * DDPB_BN_NOALLOC_MAX_C (larger C is rejected with an error); all calls on a device share the
+ * array, so calls that overlap on the GPU race - serialise them; the first call on each device
+ * resolves the array's device address on the host and should happen before any stream capture.
+ * This entry point has no counterpart in the reference. */
+#define DDPB_BN_NOALLOC_MAX_C 2048
+int ddpb_bn_relu_pool_bwd_noalloc(const void* dout, const void* y, const float* save_mean,
+                                  const float* save_invstd, const float* gamma, const float* beta, void* dy,
+                                  float* dgamma, float* dbeta, float* dbias, int batch, int H, int W, int C,
+                                  int pool, int dtype, cudaStream_t stream);
+
 /* stats[0:C] += sum, stats[C:2C] += sum of squares over `pixels` rows of y (accumulates). */
 int ddpb_channel_stats(const void* y, float* stats, long long pixels, int C, int dtype, cudaStream_t stream);
 

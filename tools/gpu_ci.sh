@@ -26,6 +26,10 @@ multigpu)
   TAILN=25 run t_multigpu 900 python -m pytest tests/test_multigpu.py -q -s -p no:cacheprovider ;;
 smoke)
   run smoke 300 python __graft_entry__.py --smoke ;;
+zz)
+  run t_zz_alone 300 python -m pytest tests/test_zz_no_alloc.py -q -p no:cacheprovider ;;
+full)
+  TAILN=15 run t_full 1500 python -m pytest tests -x -q -m gpu -p no:cacheprovider ;;
 bench)
   run bench_ours 600 python bench.py --steps 50 --warmup 10
   run bench_ours_nograph 600 python bench.py --steps 50 --warmup 10 --no-graph ;;
