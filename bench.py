@@ -306,6 +306,14 @@ def run_ours(args) -> dict:
     with torch.cuda.stream(be.stream):          # the engine's own (graph-capturable) stream
         ms, clocks, launches = timed(False)
         e2e_ms, _, _ = timed(True)
+        # device timeline of one (eager) step: how much of the gradient sync is exposed after backward
+        barrier_sync(world)
+        tl = [be.profile_step(*prepared[0]) for _ in range(3)][-1]
+        barrier_sync(world)
+    timeline = {"forward_ms": round(tl["forward_ms"], 4), "backward_compute_end_ms": round(tl["backward_compute_end_ms"], 4),
+                "eager_step_ms": round(tl["step_ms"], 4), "exposed_comm_ms": round(tl["exposed_comm_ms"], 4),
+                "exposed_comm_frac": round(tl["exposed_comm_frac"], 4),
+                "buckets_ready_done_ms": [[round(b["ready_ms"], 3), round(b["done_ms"], 3)] for b in tl["buckets"]]}
     gb = PER_GPU_BATCH * world
     bytes_in = sum(t.numel() * t.element_size() for t in host[0])
     return {
@@ -318,7 +326,7 @@ def run_ours(args) -> dict:
         "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": PER_GPU_BATCH, "seq_len": None,
                    "parallelism": f"dp{world}", "part": "3 (bucketed P2P reduce fused with SGD)" if world > 1
                    else "3 (single GPU)", "comm": be.comm_name(), "cuda_graph": be.uses_graph(),
-                   "bucket_plan": args.bucket_plan,
+                   "bucket_plan": args.bucket_plan, "timeline": timeline,
                    "l2": "working set per step (activations + weights + grads) > 126 MB L2; no explicit flush"},
     }
 

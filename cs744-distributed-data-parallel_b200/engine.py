@@ -422,6 +422,24 @@ class NativeBackend:
         return [(int(i.bucket_off[b]), int(i.bucket_numel[b]), int(i.bucket_mode[b]), int(i.bucket_last_block[b]))
                 for b in range(int(i.num_buckets))]
 
+    def profile_step(self, data: torch.Tensor, target: torch.Tensor) -> Dict[str, Any]:
+        """One instrumented (eager) training step: device timeline of forward, backward and every
+        bucket's fused reduce.  ``exposed_comm_ms`` is what the gradient sync adds after the last
+        backward kernel finished; the per-bucket rows show how far ahead of that each reduce ended."""
+        nb = int(self.info.num_buckets)
+        buf = (ctypes.c_float * (3 + 2 * nb))()
+        n = ctypes.c_int(0)
+        with self.on_stream():
+            b = self._stage(data, target)
+            check(self._lib.ddpb_engine_profile_step(self._handle, b, stream_handle(), buf, len(buf),
+                                                     ctypes.byref(n)), "engine_profile_step")
+        fwd, bwd, end = buf[0], buf[1], buf[2]
+        rows = [{"bucket": i, "bytes": int(self.info.bucket_numel[i]) * 4, "ready_ms": buf[3 + 2 * i],
+                 "done_ms": buf[4 + 2 * i]} for i in range(nb) if buf[3 + 2 * i] >= 0]
+        return {"forward_ms": fwd, "backward_compute_end_ms": bwd, "step_ms": end,
+                "exposed_comm_ms": end - bwd, "exposed_comm_frac": (end - bwd) / end if end > 0 else 0.0,
+                "buckets": rows}
+
     def launch_count(self) -> int:
         self._refresh_info()
         return int(self.info.launches)

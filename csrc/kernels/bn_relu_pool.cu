@@ -17,17 +17,37 @@ namespace ddpb {
 
 template <typename T> struct VecOf { static constexpr int N = 16 / sizeof(T); };
 
-// decode output pixel -> the (up to) four input pixel indices
+// decode output pixel -> the (up to) four input pixel indices.  32-bit arithmetic on purpose: the
+// 64-bit divisions this replaced cost more instructions than the rest of the loop body.  H and W
+// are powers of two for every layer of the VGG family (shift path); other sizes take the divide.
+struct PoolGeom {
+  int H, W, ow_shift, oh_shift;     // shifts are -1 when OW / OH are not powers of two
+};
+
+__host__ __device__ inline int log2_exact(int v) {
+  int s = 0;
+  while ((1 << s) < v) ++s;
+  return (1 << s) == v ? s : -1;
+}
+
 template <bool POOL>
-__device__ __forceinline__ void window(long long opix, int H, int W, long long* in) {
+__device__ __forceinline__ void window(int opix, const PoolGeom& gm, int* in) {
   if (!POOL) { in[0] = opix; return; }
-  int OW = W >> 1, OH = H >> 1;
-  int ow = (int)(opix % OW);
-  long long r = opix / OW;
-  int oh = (int)(r % OH);
-  long long n = r / OH;
-  long long base = (n * H + 2 * oh) * W + 2 * ow;
-  in[0] = base; in[1] = base + 1; in[2] = base + W; in[3] = base + W + 1;
+  int ow, oh, n;
+  if (gm.ow_shift >= 0 && gm.oh_shift >= 0) {
+    ow = opix & ((1 << gm.ow_shift) - 1);
+    const int r = opix >> gm.ow_shift;
+    oh = r & ((1 << gm.oh_shift) - 1);
+    n = r >> gm.oh_shift;
+  } else {
+    const unsigned OW = gm.W >> 1, OH = gm.H >> 1;
+    ow = (unsigned)opix % OW;
+    const unsigned r = (unsigned)opix / OW;
+    oh = r % OH;
+    n = r / OH;
+  }
+  const int base = (n * gm.H + 2 * oh) * gm.W + 2 * ow;
+  in[0] = base; in[1] = base + 1; in[2] = base + gm.W; in[3] = base + gm.W + 1;
 }
 
 // Sum per-thread channel partials over the block's pixel lanes and add the result to gout[0..C).
@@ -64,6 +84,7 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   const int pl = threadIdx.x / groups;
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
+  const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
 
   float sc[V], sh[V];
 #pragma unroll
@@ -90,20 +111,20 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   if (training && blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
   if (pl >= ppb) return;
 
-  for (long long op = (long long)blockIdx.x * ppb + pl; op < Pout; op += (long long)gridDim.x * ppb) {
-    long long in[4];
-    window<POOL>(op, H, W, in);
+  for (int op = blockIdx.x * ppb + pl; op < (int)Pout; op += gridDim.x * ppb) {
+    int in[4];
+    window<POOL>(op, gm, in);
     float best[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) best[j] = 0.f;          // ReLU floor
 #pragma unroll
     for (int q = 0; q < (POOL ? 4 : 1); ++q) {
       float v[V];
-      load_vec<T>(y + in[q] * C + c0, v);
+      load_vec<T>(y + (size_t)in[q] * C + c0, v);
 #pragma unroll
       for (int j = 0; j < V; ++j) best[j] = fmaxf(best[j], fmaf(v[j], sc[j], sh[j]));
     }
-    store_vec<T>(out + op * C + c0, best);
+    store_vec<T>(out + (size_t)op * C + c0, best);
   }
 }
 
@@ -123,6 +144,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
   const int pl = threadIdx.x / groups;
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
+  const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
   float sc[V], sh[V], mu[V], is[V], a1[V], a2[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) {
@@ -132,18 +154,18 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
     a1[j] = 0.f; a2[j] = 0.f;
   }
   if (pl < ppb) {
-    for (long long op = (long long)blockIdx.x * ppb + pl; op < Pout; op += (long long)gridDim.x * ppb) {
-      long long in[4];
-      window<POOL>(op, H, W, in);
+    for (int op = blockIdx.x * ppb + pl; op < (int)Pout; op += gridDim.x * ppb) {
+      int in[4];
+      window<POOL>(op, gm, in);
       float d[V];
-      load_vec<T>(dout + op * C + c0, d);
+      load_vec<T>(dout + (size_t)op * C + c0, d);
       float bz[V], by[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) { bz[j] = 0.f; by[j] = 0.f; }
 #pragma unroll
       for (int q = 0; q < (POOL ? 4 : 1); ++q) {
         float v[V];
-        load_vec<T>(y + in[q] * C + c0, v);
+        load_vec<T>(y + (size_t)in[q] * C + c0, v);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           float z = fmaf(v[j], sc[j], sh[j]);
@@ -180,6 +202,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
   const int pl = threadIdx.x / groups;
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
+  const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
   float sc[V], sh[V], mu[V], is[V], k1[V], k2[V], ab[V];
   const float invP = 1.f / (float)P;
 #pragma unroll
@@ -193,11 +216,11 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
     if (blockIdx.x == 0 && pl == 0) { dbeta[c0 + j] = s1; dgamma[c0 + j] = s2; }
   }
   if (pl < ppb) {
-    for (long long op = (long long)blockIdx.x * ppb + pl; op < Pout; op += (long long)gridDim.x * ppb) {
-      long long in[4];
-      window<POOL>(op, H, W, in);
+    for (int op = blockIdx.x * ppb + pl; op < (int)Pout; op += gridDim.x * ppb) {
+      int in[4];
+      window<POOL>(op, gm, in);
       float d[V];
-      load_vec<T>(dout + op * C + c0, d);
+      load_vec<T>(dout + (size_t)op * C + c0, d);
       float v[POOL ? 4 : 1][V];
       float bz[V];
       int bq[V];
@@ -205,7 +228,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
       for (int j = 0; j < V; ++j) { bz[j] = 0.f; bq[j] = -1; }
 #pragma unroll
       for (int q = 0; q < (POOL ? 4 : 1); ++q) {
-        load_vec<T>(y + in[q] * C + c0, v[q]);
+        load_vec<T>(y + (size_t)in[q] * C + c0, v[q]);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           float z = fmaf(v[q][j], sc[j], sh[j]);
@@ -222,7 +245,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
           o[j] = sc[j] * (dz - k1[j] - xhat * k2[j]);
           ab[j] += o[j];
         }
-        store_vec<T>(dy + in[q] * C + c0, o);
+        store_vec<T>(dy + (size_t)in[q] * C + c0, o);
       }
     }
   }
@@ -261,11 +284,12 @@ __global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ out,
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Pout * C) return;
   int c = i % C;
-  long long in[4];
-  window<true>(i / C, H, W, in);
-  float m = to_f32(x[in[0] * C + c]);
+  int in[4];
+  const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
+  window<true>((int)(i / C), gm, in);
+  float m = to_f32(x[(size_t)in[0] * C + c]);
 #pragma unroll
-  for (int q = 1; q < 4; ++q) m = fmaxf(m, to_f32(x[in[q] * C + c]));
+  for (int q = 1; q < 4; ++q) m = fmaxf(m, to_f32(x[(size_t)in[q] * C + c]));
   out[i] = from_f32<T>(m);
 }
 
@@ -275,17 +299,18 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ x, const T* __restrict_
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Pout * C) return;
   int c = i % C;
-  long long in[4];
-  window<true>(i / C, H, W, in);
-  float m = to_f32(x[in[0] * C + c]);
+  int in[4];
+  const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
+  window<true>((int)(i / C), gm, in);
+  float m = to_f32(x[(size_t)in[0] * C + c]);
   int bq = 0;
 #pragma unroll
   for (int q = 1; q < 4; ++q) {
-    float v = to_f32(x[in[q] * C + c]);
+    float v = to_f32(x[(size_t)in[q] * C + c]);
     if (v > m) { m = v; bq = q; }
   }
 #pragma unroll
-  for (int q = 0; q < 4; ++q) dx[in[q] * C + c] = (q == bq) ? dout[i] : from_f32<T>(0.f);
+  for (int q = 0; q < 4; ++q) dx[(size_t)in[q] * C + c] = (q == bq) ? dout[i] : from_f32<T>(0.f);
 }
 
 // Persistent grid: at most one wave of resident blocks (148 SMs x blocks that fit per SM); the

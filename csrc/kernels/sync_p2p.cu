@@ -41,6 +41,7 @@ struct P2PArgs {
   float* mom;                          // local momentum (same offsets as the arenas)
   uint32_t* epochs;                    // local [slots][P2P_MAX_BLOCKS]
   int rank, world, slot;
+  int skip_exit_barrier;               // 1: a later launch of the same step ends with the barrier instead
   long long off, n;                    // element range, multiples of 4
   float lr, momentum, wd;
 };
@@ -176,7 +177,7 @@ p2p_kernel(const P2PArgs a) {
         if (r != a.rank) st_peer(a.grad[r] + e, v);
     }
   }
-  cta_barrier_all_ranks(a, 1);
+  if (!a.skip_exit_barrier) cta_barrier_all_ranks(a, 1);
 }
 
 }  // namespace ddpb
@@ -210,6 +211,8 @@ extern "C" int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, v
   a.mom = mom; a.epochs = (uint32_t*)epochs;
   a.rank = rank; a.world = world; a.slot = slot; a.off = off; a.n = n;
   a.lr = lr; a.momentum = momentum; a.wd = wd;
+  a.skip_exit_barrier = (mode & DDPB_P2P_NO_EXIT_BARRIER) ? 1 : 0;
+  mode &= ~DDPB_P2P_NO_EXIT_BARRIER;
   switch (mode) {
     case DDPB_P2P_ONESHOT: p2p_kernel<MODE_ONESHOT><<<blocks, 512, 0, stream>>>(a); break;
     case DDPB_P2P_TWOSHOT: p2p_kernel<MODE_TWOSHOT><<<blocks, 512, 0, stream>>>(a); break;

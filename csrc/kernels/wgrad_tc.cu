@@ -12,9 +12,9 @@
 //
 // One CTA owns: 128 output channels x 64 input channels x the three taps of one filter row
 // (3 accumulators of 64 TMEM columns that share every dY tile), over one slice of the pixels
-// (split-K).  Partial results are added to the fp32 gradient with vectorised RED
-// (red.global.add.v4.f32) straight into the gradient arena in KRSC order, i.e. the buffer the
-// peer-to-peer reduce kernels and the fused SGD read - there is no staging copy.
+// (split-K).  Partial results are added to the fp32 gradient with TMA reduce-add
+// (cp.reduce.async.bulk.tensor ... .add) straight into the gradient arena in KRSC order, i.e. the
+// buffer the peer-to-peer reduce kernels and the fused SGD read - there is no staging copy.
 #include "../common.cuh"
 #include "../../include/ddp_b200.h"
 #include "../runtime/tensormap.h"
@@ -43,7 +43,7 @@ void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn);   // conv_t
 template <int STAGES>
 __global__ void __launch_bounds__(192)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
-                float* __restrict__ dw, const WgradParams prm) {
+                const __grid_constant__ CUtensorMap tmW, const WgradParams prm) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * WG_STAGE);
@@ -62,6 +62,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmDY);
     tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmW);
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     mbar_init(accum_bar, 1);
     fence_mbar_init();
@@ -114,21 +115,38 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
         umma_commit(accum_bar);
       }
     } else {
+      // epilogue: TMEM -> registers -> shared memory (128B-swizzled [128 co][32 ci] fp32 boxes), then
+      // six TMA reduce-add operations accumulate the partial tile into the gradient arena with
+      // whole 128-byte lines (instead of 6144 scattered 16-byte RED instructions per CTA).
       const int q = warp & 3;
-      const int co = co_blk * WG_M + q * 32 + lane;
+      const int row = q * 32 + lane;             // output channel inside the tile
       mbar_wait(accum_bar, 0);
       tc_fence_after();
 #pragma unroll 1
       for (int t = 0; t < WG_TAPS; ++t) {
-        float* dst = dw + ((long long)co * 9 + (r * 3 + t)) * prm.Cin + ci_blk * WG_N;
 #pragma unroll 1
         for (int c = 0; c < WG_N; c += 32) {
           float v[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + t * WG_N + c, v);
           tmem_ld_wait();
+          uint8_t* rbase = smem + (t * 2 + (c >> 5)) * (WG_M * 128) + row * 128;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) red_add_v4(dst + c + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(rbase + ((j ^ (row & 7)) << 4)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         }
+      }
+      fence_async_proxy();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 64) {
+#pragma unroll
+        for (int t = 0; t < WG_TAPS; ++t)
+#pragma unroll
+          for (int hblk = 0; hblk < 2; ++hblk)
+            tma_reduce_add_2d(&tmW, smem + (t * 2 + hblk) * (WG_M * 128),
+                              (r * 3 + t) * prm.Cin + ci_blk * WG_N + hblk * 32, co_blk * WG_M);
+        tma_store_commit();
+        tma_store_wait_read();
       }
     }
   }
@@ -151,8 +169,10 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
                Cin, Cout);
   int bw, bh, bn;
   pixel_box(H, W, WG_K, &bw, &bh, &bn);
-  CUtensorMap tmDY, tmX;
-  int rc = make_tmap_nhwc_bf16(&tmDY, dy, B, H, W, Cout, 64, bw, bh, bn);
+  CUtensorMap tmDY, tmX, tmW;
+  int rc = make_tmap_2d_f32(&tmW, dw, Cout, 9LL * Cin, 32, WG_M);
+  if (rc) return rc;
+  rc = make_tmap_nhwc_bf16(&tmDY, dy, B, H, W, Cout, 64, bw, bh, bn);
   if (rc) return rc;
   rc = make_tmap_nhwc_bf16(&tmX, x, B, H, W, Cin, 64, bw, bh, bn);
   if (rc) return rc;
@@ -172,7 +192,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
     for (int s = 1; s <= max_split; ++s) {
       long long waves = ((long long)base_ctas * s + 147) / 148;
       long long iters = (prm.total_chunks + s - 1) / s;
-      long long cost = waves * (iters + 3);
+      long long cost = waves * (iters + 6);
       if (best_cost < 0 || cost < best_cost) { best_cost = cost; split_k = s; }
     }
   }
@@ -185,7 +205,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
     configured = true;
   }
   dim3 grid(base_ctas / 3, 3, split_k);
-  wgrad_tc_kernel<STAGES><<<grid, 192, smem, stream>>>(tmDY, tmX, dw, prm);
+  wgrad_tc_kernel<STAGES><<<grid, 192, smem, stream>>>(tmDY, tmX, tmW, prm);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

@@ -75,6 +75,10 @@ struct Engine {
   std::map<long long, Graph> graphs;     // key = kind * 1e6 + batch
   long long launches = 0, counting = 0;
   bool count_only = false;
+  // step-timeline profiling (ddpb_engine_profile_step): timing events, only recorded when prof_on
+  bool prof_on = false;
+  cudaEvent_t prof_start = nullptr, prof_fwd = nullptr, prof_bwd = nullptr, prof_end = nullptr;
+  std::vector<cudaEvent_t> prof_ready, prof_done;
 };
 
 #define ECHECK(call)        \
@@ -287,8 +291,16 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   void *g[DDPB_MAX_RANKS], *m[DDPB_MAX_RANKS], *sh[DDPB_MAX_RANKS], *f[DDPB_MAX_RANKS];
   peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
   peer_table(e, e->off_shadow, sh); peer_table(e, e->off_flags, f);
-  LAUNCH(e, ddpb_p2p_sync(b.mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
-                          c.momentum, c.wd, 0, s));
+  // Only the last bucket of the step needs the closing barrier: it is reached after every earlier
+  // bucket kernel of this rank has finished (same stream), so passing it proves that all peers are
+  // done reading our gradients and that all their weight pushes into our arena have landed.
+  const bool last = bi + 1 == (int)e->buckets.size();
+  const int mode = b.mode | (last ? 0 : DDPB_P2P_NO_EXIT_BARRIER);
+  // enough CTAs to keep ~16 B x 8 loads per thread in flight on big buckets, few on small ones
+  long long want = (b.numel / 4 + 512 * 4 - 1) / (512 * 4);
+  const int blocks = (int)(want < 1 ? 1 : (want > 48 ? 48 : want));
+  LAUNCH(e, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
+                          c.momentum, c.wd, blocks, s));
   return DDPB_OK;
 }
 
@@ -299,12 +311,15 @@ static int buckets_ready(Engine* e, int blk, cudaStream_t s) {
   if (c.strategy != 3) return DDPB_OK;        // only the bucketed strategy syncs during backward
   for (size_t i = 0; i < e->buckets.size(); ++i) {
     if (e->buckets[i].last_block != blk) continue;
+    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_ready[i], s));
     if (c.world > 1 && e->peers_set) {
       DDPB_CUDA_CHECK(cudaEventRecord(e->bucket_ev[i], s));
       DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, e->bucket_ev[i], 0));
       ECHECK(launch_bucket(e, (int)i, e->comm));
+      if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_done[i], e->comm));
     } else {
       ECHECK(launch_bucket(e, (int)i, s));
+      if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_done[i], s));
     }
   }
   return DDPB_OK;
@@ -341,6 +356,7 @@ static int backward(Engine* e, int B, cudaStream_t s) {
     }
     ECHECK(buckets_ready(e, i, s));
   }
+  if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_bwd, s));   // last compute kernel of backward
   // ---- end of backward: the non-overlapped strategies synchronise here, like the reference ----
   const bool p2p = c.world > 1 && e->peers_set;
   if (c.strategy == 3) {
@@ -533,6 +549,57 @@ extern "C" int ddpb_engine_train_step(void* handle, int batch, cudaStream_t s) {
   Engine* e = (Engine*)handle;
   DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_train_step: batch %d out of range", batch);
   return run_graphed(e, KIND_STEP, batch, s);
+}
+
+// One eager (non-graph) training step instrumented with CUDA events.  out[0] = forward end,
+// out[1] = last compute kernel of backward, out[2] = step end (after the gradient sync joined),
+// then per bucket i: out[3+2i] = its gradients ready, out[4+2i] = its fused reduce+update done;
+// all in milliseconds since the start of the step.  Exposed communication = out[2] - out[1].
+// Synchronises the stream.  Returns the number of floats written through *n_out.
+extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s, float* out, int max_out,
+                                        int* n_out) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(e && out && n_out, "engine_profile_step: null argument");
+  DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_profile_step: batch %d out of range", batch);
+  const int nb = (int)e->buckets.size();
+  DDPB_REQUIRE(max_out >= 3 + 2 * nb, "engine_profile_step: output buffer too small (%d < %d)", max_out, 3 + 2 * nb);
+  if (!e->prof_start) {
+    DDPB_CUDA_CHECK(cudaEventCreate(&e->prof_start)); DDPB_CUDA_CHECK(cudaEventCreate(&e->prof_fwd));
+    DDPB_CUDA_CHECK(cudaEventCreate(&e->prof_bwd)); DDPB_CUDA_CHECK(cudaEventCreate(&e->prof_end));
+    e->prof_ready.resize(nb); e->prof_done.resize(nb);
+    for (int i = 0; i < nb; ++i) {
+      DDPB_CUDA_CHECK(cudaEventCreate(&e->prof_ready[i]));
+      DDPB_CUDA_CHECK(cudaEventCreate(&e->prof_done[i]));
+    }
+  }
+  e->prof_on = true;
+  e->counting = 0;
+  int rc = DDPB_OK;
+  cudaEventRecord(e->prof_start, s);
+  rc = forward(e, batch, 1, s);
+  if (!rc) rc = loss_fwd(e, batch, 1, s);
+  cudaEventRecord(e->prof_fwd, s);
+  if (!rc) rc = backward(e, batch, s);
+  cudaEventRecord(e->prof_end, s);
+  e->prof_on = false;
+  e->launches += e->counting;
+  if (rc) return rc;
+  DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
+  DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e->prof_start, e->prof_fwd); out[0] = ms;
+  cudaEventElapsedTime(&ms, e->prof_start, e->prof_bwd); out[1] = ms;
+  cudaEventElapsedTime(&ms, e->prof_start, e->prof_end); out[2] = ms;
+  const bool bucketed = e->cfg.strategy == 3;
+  for (int i = 0; i < nb; ++i) {
+    out[3 + 2 * i] = out[4 + 2 * i] = -1.f;
+    if (!bucketed) continue;
+    if (cudaEventElapsedTime(&ms, e->prof_start, e->prof_ready[i]) == cudaSuccess) out[3 + 2 * i] = ms;
+    if (cudaEventElapsedTime(&ms, e->prof_start, e->prof_done[i]) == cudaSuccess) out[4 + 2 * i] = ms;
+  }
+  (void)cudaGetLastError();
+  *n_out = 3 + 2 * nb;
+  return DDPB_OK;
 }
 
 // Eval forward: BN uses running statistics; eval_loss += mean CE of the batch; correct += hits.

@@ -40,14 +40,14 @@ static EncodeTiledFn encode_fn() {
 }
 
 static int encode(CUtensorMap* out, const void* ptr, int rank, const cuuint64_t* dims, const cuuint64_t* strides,
-                  const cuuint32_t* box) {
+                  const cuuint32_t* box, CUtensorMapDataType dtype = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_last_error("cuTensorMapEncodeTiled is not available from this driver");
     return DDPB_ERR_UNSUPPORTED;
   }
   cuuint32_t ones[5] = {1, 1, 1, 1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), dims, strides, box, ones,
+  CUresult r = fn(out, dtype, rank, const_cast<void*>(ptr), dims, strides, box, ones,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -82,6 +82,18 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, long long rows, long lo
   cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
   cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   return encode(out, ptr, 2, dims, strides, box);
+}
+
+int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, long long rows, long long cols, int box_cols,
+                     int box_rows) {
+  if (box_cols != 32 || cols % 4 != 0) {
+    set_last_error("tensor map: fp32 2-D box must be 32 columns (128 bytes) wide, row pitch 16-byte aligned");
+    return DDPB_ERR_ARG;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  return encode(out, ptr, 2, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32);
 }
 
 }  // namespace ddpb

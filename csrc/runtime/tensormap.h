@@ -15,4 +15,8 @@ int make_tmap_nhwc_bf16(CUtensorMap* out, const void* ptr, int N, int H, int W, 
 int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, long long rows, long long cols, int box_cols,
                       int box_rows);
 
+// Row-major fp32 matrix [rows][cols]; box = 32 columns (128 B) x box_rows, 128-byte swizzle.
+int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, long long rows, long long cols, int box_cols,
+                     int box_rows);
+
 }  // namespace ddpb

@@ -30,6 +30,8 @@ extern "C" {
 #define DDPB_P2P_ROOT 2
 #define DDPB_P2P_BCAST 3
 #define DDPB_P2P_ALLGATHER 4
+/* OR into `mode`: skip the kernel's closing cross-rank barrier (a later launch on the same stream closes the step) */
+#define DDPB_P2P_NO_EXIT_BARRIER 0x100
 
 const char* ddpb_last_error(void);
 
@@ -199,6 +201,11 @@ int ddpb_engine_refresh_shadow(void* handle, cudaStream_t stream);
 int ddpb_engine_forward(void* handle, int batch, cudaStream_t stream);
 int ddpb_engine_backward(void* handle, int batch, cudaStream_t stream);
 int ddpb_engine_train_step(void* handle, int batch, cudaStream_t stream);
+/* One eager step instrumented with CUDA events (replaces the reference's host timers around the
+ * loop body, ref Part 1/main.py:33-43, with a device timeline).  out[0] forward end, out[1] last
+ * compute kernel of backward, out[2] step end, then (ready, done) per bucket; milliseconds since the
+ * step start.  Exposed communication = out[2] - out[1].  Synchronises `stream`. */
+int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t stream, float* out, int max_out, int* n_out);
 /* ref Part 1/main.py:61-76: eval-mode forward; accumulates info.eval_loss / info.correct. */
 int ddpb_engine_eval_step(void* handle, int batch, cudaStream_t stream);
 int ddpb_engine_eval_reset(void* handle, cudaStream_t stream);
