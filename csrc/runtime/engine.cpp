@@ -67,10 +67,10 @@ struct Engine {
   float *scratch = nullptr, *mean = nullptr, *invstd = nullptr, *logits = nullptr, *dlogits = nullptr;
   float *loss = nullptr, *eval_loss = nullptr; int *correct = nullptr; long long* nbt = nullptr;
   size_t scratch_floats = 0;
-  void *input = nullptr, *dy_buf = nullptr, *dact = nullptr; long long* target = nullptr;
+  void *input = nullptr, *dy_buf2[2] = {nullptr, nullptr}, *dact = nullptr; long long* target = nullptr;
   std::vector<Bucket> buckets;
-  cudaStream_t comm = nullptr;
-  std::vector<cudaEvent_t> bucket_ev;
+  cudaStream_t comm = nullptr, wg = nullptr;
+  std::vector<cudaEvent_t> bucket_ev, ev_dy, ev_dg, ev_wg;
   cudaEvent_t join_ev = nullptr, fork_ev = nullptr;
   std::map<long long, Graph> graphs;     // key = kind * 1e6 + batch
   long long launches = 0, counting = 0;
@@ -217,12 +217,20 @@ static int alloc_all(Engine* e) {
     DDPB_CUDA_CHECK(cudaMalloc(&b.y, B * y * e->esize));
     DDPB_CUDA_CHECK(cudaMalloc(&b.act, B * o * e->esize));
   }
-  DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf, B * max_y * e->esize));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf2[0], B * max_y * e->esize));
+  DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf2[1], B * max_y * e->esize));
   DDPB_CUDA_CHECK(cudaMalloc(&e->dact, B * max_act * e->esize));
   // BN defaults: gamma 1, running_var 1 (weights are loaded by the caller afterwards)
   DDPB_CUDA_CHECK(cudaMemset(e->mean, 0, e->total_c * 4));
   DDPB_CUDA_CHECK(cudaMemset(e->invstd, 0, e->total_c * 4));
   DDPB_CUDA_CHECK(cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking));
+  DDPB_CUDA_CHECK(cudaStreamCreateWithFlags(&e->wg, cudaStreamNonBlocking));
+  e->ev_dy.resize(c.num_blocks + 1); e->ev_dg.resize(c.num_blocks + 1); e->ev_wg.resize(c.num_blocks + 1);
+  for (int i = 0; i <= c.num_blocks; ++i) {
+    DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->ev_dy[i], cudaEventDisableTiming));
+    DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->ev_dg[i], cudaEventDisableTiming));
+    DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->ev_wg[i], cudaEventDisableTiming));
+  }
   e->bucket_ev.resize(e->buckets.size());
   for (auto& ev : e->bucket_ev) DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->join_ev, cudaEventDisableTiming));
@@ -304,67 +312,87 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   return DDPB_OK;
 }
 
-// After the producers of block `blk` (-1 = classifier) are enqueued on `s`: launch every bucket
-// whose last producer this was.  Overlapped strategies hand the bucket to the comm stream.
-static int buckets_ready(Engine* e, int blk, cudaStream_t s) {
+// Is the optimizer / gradient-sync work overlapped with backward?  The bucketed strategy by
+// definition; a single process as well (its optimizer step has no cross-rank dependency, so stepping
+// a layer as soon as its gradients are final is observably identical to stepping after backward).
+static bool overlapped(const Engine* e) {
   const auto& c = e->cfg;
-  if (c.strategy != 3) return DDPB_OK;        // only the bucketed strategy syncs during backward
+  if (c.external_sync) return false;
+  return c.strategy == 3 || c.world == 1;
+}
+
+// Block `blk` (-1 = classifier) is complete: its gradients have been produced (event ev_a) and every
+// reader of its current weights has run (event ev_b).  Hand each bucket that ends with this block to
+// the communication stream, where its fused reduce + optimizer kernel overlaps the rest of backward.
+static int buckets_ready(Engine* e, int blk, cudaEvent_t ev_a, cudaEvent_t ev_b) {
+  if (!overlapped(e)) return DDPB_OK;
   for (size_t i = 0; i < e->buckets.size(); ++i) {
     if (e->buckets[i].last_block != blk) continue;
-    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_ready[i], s));
-    if (c.world > 1 && e->peers_set) {
-      DDPB_CUDA_CHECK(cudaEventRecord(e->bucket_ev[i], s));
-      DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, e->bucket_ev[i], 0));
-      ECHECK(launch_bucket(e, (int)i, e->comm));
-      if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_done[i], e->comm));
-    } else {
-      ECHECK(launch_bucket(e, (int)i, s));
-      if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_done[i], s));
-    }
+    if (ev_a) DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, ev_a, 0));
+    if (ev_b) DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, ev_b, 0));
+    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_ready[i], e->comm));
+    ECHECK(launch_bucket(e, (int)i, e->comm));
+    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_done[i], e->comm));
   }
   return DDPB_OK;
 }
 
+// Backward runs on three streams:
+//   s    (critical path)  fc-bwd -> [BN-bwd(i) -> dgrad(i)] for i = last..0
+//   wg   (off the path)   wgrad(i), as soon as BN-bwd(i) has produced dY(i); overlaps the next
+//                         layers' BN-bwd / dgrad, which leave most SMs idle on the small layers
+//   comm                  the buckets' fused reduce + SGD kernels
+// dY is double-buffered so that BN-bwd(i-1) does not overwrite what wgrad(i) is still reading.
 static int backward(Engine* e, int B, cudaStream_t s) {
   const auto& c = e->cfg;
   const int dt = c.dtype;
+  const int L = (int)e->blocks.size();
   float* bsums = e->scratch + e->total_c * 2;
   DDPB_CUDA_CHECK(cudaMemsetAsync(e->grad, 0, e->arena_elems * 4, s));
   const Block& last = e->blocks.back();
   LAUNCH(e, ddpb_fc_bwd(last.act, e->master + e->fc_w.off, e->dlogits, e->dact, e->grad + e->fc_w.off,
                         e->grad + e->fc_b.off, B, dt, s));
-  ECHECK(buckets_ready(e, -1, s));
-  for (int i = (int)e->blocks.size() - 1; i >= 0; --i) {
+  DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[L], s));
+  ECHECK(buckets_ready(e, -1, e->ev_dg[L], nullptr));
+  for (int i = L - 1; i >= 0; --i) {
     Block& b = e->blocks[i];
     const void* x_in = i == 0 ? e->input : e->blocks[i - 1].act;
+    void* dy = e->dy_buf2[i & 1];
+    if (i + 2 < L) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[i + 2], 0));   // previous reader of this dY buffer
     LAUNCH(e, ddpb_bn_relu_pool_bwd(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off, e->master + b.bn_w.off,
-                                    e->master + b.bn_b.off, bsums + b.stat_off, e->dy_buf, e->grad + b.bn_w.off,
+                                    e->master + b.bn_b.off, bsums + b.stat_off, dy, e->grad + b.bn_w.off,
                                     e->grad + b.bn_b.off, e->grad + b.conv_b.off, B, b.hw, b.hw, b.cout, b.pool,
                                     dt, s));
     e->counting += 1;     // the BN backward is two launches (reduce + apply)
-    // dgrad BEFORE wgrad: (1) it is on the critical path of the next layer; (2) the bucket's fused
-    // reduce+SGD overwrites this layer's weights as soon as wgrad is done, so every reader of the
-    // old weights (dgrad) has to be ordered before the bucket's ready event.
-    if (use_tc(e, b)) {
-      if (i > 0)
-        LAUNCH(e, ddpb_conv3x3_dgrad_tc(e->dy_buf, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
-      LAUNCH(e, ddpb_conv3x3_wgrad_tc(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, s));
-    } else {
-      if (i > 0)
-        LAUNCH(e, ddpb_conv3x3_dgrad_simt(e->dy_buf, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
-      LAUNCH(e, ddpb_conv3x3_wgrad_simt(e->dy_buf, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, s));
+    DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dy[i], s));
+    // dgrad reads this layer's CURRENT weights; the bucket's fused reduce+SGD rewrites them, so the
+    // bucket may only start after dgrad (ev_dg) as well as after wgrad (ev_wg).
+    if (i > 0) {
+      if (use_tc(e, b))
+        LAUNCH(e, ddpb_conv3x3_dgrad_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+      else
+        LAUNCH(e, ddpb_conv3x3_dgrad_simt(dy, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
     }
-    ECHECK(buckets_ready(e, i, s));
+    DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[i], s));
+    DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->ev_dy[i], 0));
+    if (use_tc(e, b))
+      LAUNCH(e, ddpb_conv3x3_wgrad_tc(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, e->wg));
+    else
+      LAUNCH(e, ddpb_conv3x3_wgrad_simt(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, e->wg));
+    DDPB_CUDA_CHECK(cudaEventRecord(e->ev_wg[i], e->wg));
+    ECHECK(buckets_ready(e, i, e->ev_wg[i], e->ev_dg[i]));
   }
-  if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_bwd, s));   // last compute kernel of backward
-  // ---- end of backward: the non-overlapped strategies synchronise here, like the reference ----
+  // join the weight-gradient stream (wgrads of blocks >= 2 were already waited for above)
+  DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[0], 0));
+  if (L > 1) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[1], 0));
+  if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_bwd, s));   // all gradients of the step exist
   const bool p2p = c.world > 1 && e->peers_set;
-  if (c.strategy == 3) {
-    if (p2p) {   // join: the step is complete when every bucket kernel has finished
-      DDPB_CUDA_CHECK(cudaEventRecord(e->join_ev, e->comm));
-      DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->join_ev, 0));
-    }
+  if (overlapped(e)) {
+    // join: the step is complete when every bucket kernel has finished
+    DDPB_CUDA_CHECK(cudaEventRecord(e->join_ev, e->comm));
+    DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->join_ev, 0));
   } else if (!c.external_sync) {
+    // Parts 2a / 2b: synchronise strictly after backward, like the reference (Part 2a/main.py:94-96)
     if (p2p) {
       void *g[DDPB_MAX_RANKS], *m[DDPB_MAX_RANKS], *sh[DDPB_MAX_RANKS], *f[DDPB_MAX_RANKS];
       peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
@@ -404,6 +432,7 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
     e->launches += e->counting;
     DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
     DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm));
+    DDPB_CUDA_CHECK(cudaStreamSynchronize(e->wg));
     // NOTE: that eager run was a real step; the caller asked for exactly one, so capture only and
     // launch the graph from the NEXT call on.
     Graph g;
@@ -471,12 +500,16 @@ extern "C" int ddpb_engine_destroy(void* handle) {
     if (r != e->cfg.rank && e->peer_arena[r]) cudaIpcCloseMemHandle(e->peer_arena[r]);
   for (auto& b : e->blocks) { cudaFree(b.y); cudaFree(b.act); }
   void* frees[] = {e->epochs, e->scratch, e->mean, e->invstd, e->nbt, e->logits, e->dlogits, e->eval_loss,
-                   e->input, e->target, e->dy_buf, e->dact, e->arena};
+                   e->input, e->target, e->dy_buf2[0], e->dy_buf2[1], e->dact, e->arena};
   for (void* p : frees) if (p) cudaFree(p);
   for (auto& ev : e->bucket_ev) cudaEventDestroy(ev);
   if (e->join_ev) cudaEventDestroy(e->join_ev);
   if (e->fork_ev) cudaEventDestroy(e->fork_ev);
+  for (auto& ev : e->ev_dy) cudaEventDestroy(ev);
+  for (auto& ev : e->ev_dg) cudaEventDestroy(ev);
+  for (auto& ev : e->ev_wg) cudaEventDestroy(ev);
   if (e->comm) cudaStreamDestroy(e->comm);
+  if (e->wg) cudaStreamDestroy(e->wg);
   delete e;
   return DDPB_OK;
 }
@@ -590,7 +623,7 @@ extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s,
   cudaEventElapsedTime(&ms, e->prof_start, e->prof_fwd); out[0] = ms;
   cudaEventElapsedTime(&ms, e->prof_start, e->prof_bwd); out[1] = ms;
   cudaEventElapsedTime(&ms, e->prof_start, e->prof_end); out[2] = ms;
-  const bool bucketed = e->cfg.strategy == 3;
+  const bool bucketed = overlapped(e);
   for (int i = 0; i < nb; ++i) {
     out[3 + 2 * i] = out[4 + 2 * i] = -1.f;
     if (!bucketed) continue;
