@@ -241,8 +241,12 @@ static int alloc_all(Engine* e) {
 // ---------------------------------------------------------------------------------------------
 // forward / backward sequences
 // ---------------------------------------------------------------------------------------------
+// forward / dgrad tiles need Cin, Cout multiples of 64; the wgrad tile is 128 output channels wide
 static bool use_tc(const Engine* e, const Block& b) {
-  return e->cfg.dtype == DDPB_BF16 && e->cfg.use_tc && b.cin % 64 == 0 && b.cout % 128 == 0;
+  return e->cfg.dtype == DDPB_BF16 && e->cfg.use_tc && b.cin % 64 == 0 && b.cout % 64 == 0;
+}
+static bool use_tc_wgrad(const Engine* e, const Block& b) {
+  return use_tc(e, b) && b.cout % 128 == 0;
 }
 
 #define LAUNCH(e, call)   \
@@ -306,7 +310,7 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   const int mode = b.mode | (last ? 0 : DDPB_P2P_NO_EXIT_BARRIER);
   // enough CTAs to keep ~16 B x 8 loads per thread in flight on big buckets, few on small ones
   long long want = (b.numel / 4 + 512 * 4 - 1) / (512 * 4);
-  const int blocks = (int)(want < 1 ? 1 : (want > 48 ? 48 : want));
+  const int blocks = (int)(want < 1 ? 1 : (want > DDPB_P2P_MAX_BLOCKS ? DDPB_P2P_MAX_BLOCKS : want));
   LAUNCH(e, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
                           c.momentum, c.wd, blocks, s));
   return DDPB_OK;
@@ -375,7 +379,7 @@ static int backward(Engine* e, int B, cudaStream_t s) {
     }
     DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[i], s));
     DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->ev_dy[i], 0));
-    if (use_tc(e, b))
+    if (use_tc_wgrad(e, b))
       LAUNCH(e, ddpb_conv3x3_wgrad_tc(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, e->wg));
     else
       LAUNCH(e, ddpb_conv3x3_wgrad_simt(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, e->wg));

@@ -217,3 +217,34 @@ def test_bucket_plans_cover_arena():
         assert b[0][0] == 0 and all(x[0] + x[1] == y[0] for x, y in zip(b, b[1:]))
         assert b[-1][0] + b[-1][1] == int(nb.info.arena_elems)
         del nb
+
+
+@pytest.mark.parametrize("variant", ["VGG13", "VGG16"])
+def test_other_vgg_variants_run_on_the_native_engine(no_tf32, variant):
+    """The reference's table lists VGG13/16/19 too; their 64->64 layers use the tensor-core forward /
+    dgrad with a SIMT wgrad (the wgrad tile is 128 output channels wide)."""
+    from cs744_ddp_b200.backends import TorchBackend
+    from cs744_ddp_b200.engine import NativeBackend
+    torch.manual_seed(0)
+    tb = TorchBackend(_cfg(backend="torch", dtype="fp32", model=variant, global_batch=8), DEV)
+    nb = NativeBackend(_cfg(backend="native", dtype="bf16", model=variant, global_batch=8), DEV,
+                       init_state=tb.state_dict())
+    raw = _batches(1, 8, seed=11)[0]
+    lt = float(tb.train_step(*tb.prepare(raw), _T()))
+    ln = float(nb.train_step(*nb.prepare(raw), _T()))
+    print(f"[eng] {variant}: torch {lt:.4f} native bf16 {ln:.4f}")
+    assert abs(lt - ln) < 5e-2 * max(1.0, lt)
+    assert list(nb.state_dict().keys()) == list(tb.state_dict().keys())
+
+
+def test_profile_step_reports_a_consistent_timeline():
+    from cs744_ddp_b200.engine import NativeBackend
+    nb = NativeBackend(_cfg(backend="native", dtype="bf16", global_batch=32, sync="bucketed"), DEV)
+    raw = _batches(1, 32)[0]
+    nb.train_step(*nb.prepare(raw), _T())
+    tl = nb.profile_step(*nb.prepare(raw))
+    assert 0 < tl["forward_ms"] < tl["backward_compute_end_ms"] <= tl["step_ms"]
+    assert 0 <= tl["exposed_comm_frac"] < 0.5
+    ready = [b["ready_ms"] for b in tl["buckets"]]
+    assert ready == sorted(ready) and len(ready) == len(nb.buckets())
+    assert all(b["done_ms"] >= b["ready_ms"] for b in tl["buckets"])

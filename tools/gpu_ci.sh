@@ -37,6 +37,16 @@ bench2)
   run bench2_p2p 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 50 --warmup 10
   run bench2_nccl 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29534 bench.py --gpus 2 --steps 50 --warmup 10 --comm nccl
   run bench2_ref 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29535 bench.py --gpus 2 --steps 40 --warmup 10 --impl reference ;;
+sweep)
+  TAILN=20 run sweep 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node ${NGPU:-2} --master-addr 127.0.0.1 --master-port 29541 tools/allreduce_sweep.py ;;
+cli)
+  # the main.py-style entry points, one process per GPU, started by hand like the reference
+  ( python -m cs744_ddp_b200.parts.part3 --master 127.0.0.1 --num-nodes 2 --rank 1 --synthetic --dtype bf16 --iters 60 --train-size 20480 --test-size 1024 --port 6591 > $OUT/cli_part3_rank1.log 2>&1 & )
+  run cli_part3_rank0 600 python -m cs744_ddp_b200.parts.part3 --master 127.0.0.1 --num-nodes 2 --rank 0 --synthetic --dtype bf16 --iters 60 --train-size 20480 --test-size 1024 --port 6591
+  sleep 2
+  ( python -m cs744_ddp_b200.parts.part2a --master 127.0.0.1 --num-nodes 2 --rank 1 --synthetic --iters 40 --train-size 20480 --test-size 512 --port 6592 > $OUT/cli_part2a_rank1.log 2>&1 & )
+  run cli_part2a_rank0 600 python -m cs744_ddp_b200.parts.part2a --master 127.0.0.1 --num-nodes 2 --rank 0 --synthetic --iters 40 --train-size 20480 --test-size 512 --port 6592
+  sleep 2 ;;
 kbench)
   TAILN=80 run kernel_bench 600 python tools/kernel_bench.py ;;
 ref)
