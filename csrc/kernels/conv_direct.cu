@@ -246,21 +246,35 @@ first_layer_wgrad(const T* __restrict__ dy, const T* __restrict__ x, float* __re
 constexpr int FL_W = 32, FL_ROWS = 4, FL_TILE = FL_W * FL_ROWS;     // 128 pixels
 constexpr int FL_XR = FL_ROWS + 2, FL_XW = FL_W + 2;                // staged rows x (cols + halo)
 
+// Staging is split in two so the global loads of tile t+1 are in flight while tile t is computed:
+// fl_prefetch_x issues the loads into registers (threads 0..203 own one (row, col) position each),
+// fl_commit_x writes them to the other shared-memory buffer once the compute is done.
+struct FlPix { float v0, v1, v2; };
+
 template <typename T>
-__device__ __forceinline__ void fl_stage_x(const T* __restrict__ x, float (*xs)[FL_XW][3], long long tile, int H) {
-  // tile -> image n, first row h0; xs[r][c][ci] = x[n, h0-1+r, c-1, ci] or 0 outside the image
-  const int tiles_per_img = H / FL_ROWS;
-  const long long n = tile / tiles_per_img;
-  const int h0 = (int)(tile % tiles_per_img) * FL_ROWS;
-  for (int i = threadIdx.x; i < FL_XR * FL_XW; i += blockDim.x) {
+__device__ __forceinline__ FlPix fl_prefetch_x(const T* __restrict__ x, long long tile, long long tiles, int H) {
+  // tile -> image n, first row h0; position (r, c) <- x[n, h0-1+r, c-1, :] or 0 outside the image
+  FlPix px{0.f, 0.f, 0.f};
+  const int i = threadIdx.x;
+  if (tile < tiles && i < FL_XR * FL_XW) {
+    const int tiles_per_img = H / FL_ROWS;
+    const long long n = tile / tiles_per_img;
+    const int h0 = (int)(tile % tiles_per_img) * FL_ROWS;
     const int r = i / FL_XW, c = i % FL_XW;
     const int ih = h0 - 1 + r, iw = c - 1;
-    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
     if (ih >= 0 && ih < H && iw >= 0 && iw < FL_W) {
       const T* p = x + ((n * H + ih) * FL_W + iw) * 3;
-      v0 = to_f32(p[0]); v1 = to_f32(p[1]); v2 = to_f32(p[2]);
+      px.v0 = to_f32(p[0]); px.v1 = to_f32(p[1]); px.v2 = to_f32(p[2]);
     }
-    xs[r][c][0] = v0; xs[r][c][1] = v1; xs[r][c][2] = v2;
+  }
+  return px;
+}
+
+__device__ __forceinline__ void fl_commit_x(float (*xs)[FL_XW][3], const FlPix& px) {
+  const int i = threadIdx.x;
+  if (i < FL_XR * FL_XW) {
+    const int r = i / FL_XW, c = i % FL_XW;
+    xs[r][c][0] = px.v0; xs[r][c][1] = px.v1; xs[r][c][2] = px.v2;
   }
 }
 
@@ -284,9 +298,10 @@ first_layer_fwd_32(const T* __restrict__ x, const float* __restrict__ w, const f
 #pragma unroll
   for (int j = 0; j < CG; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
   int buf = 0;
+  fl_commit_x(xs[0], fl_prefetch_x<T>(x, blockIdx.x, tiles, H));
+  __syncthreads();
   for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, buf ^= 1) {
-    fl_stage_x<T>(x, xs[buf], tile, H);
-    __syncthreads();           // also orders the previous iteration's reads of the other buffer
+    const FlPix nxt = fl_prefetch_x<T>(x, tile + gridDim.x, tiles, H);      // in flight during the FMAs below
     float acc[2][CG];
 #pragma unroll
     for (int j = 0; j < CG; ++j) { acc[0][j] = sb[c0 + j]; acc[1][j] = acc[0][j]; }
@@ -339,6 +354,8 @@ first_layer_fwd_32(const T* __restrict__ x, const float* __restrict__ w, const f
         store_vec<T>(yp + q * V, tmp);
       }
     }
+    fl_commit_x(xs[buf ^ 1], nxt);
+    __syncthreads();           // next tile staged; everyone is done reading xs[buf]
   }
   if (stats) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -356,14 +373,33 @@ first_layer_fwd_32(const T* __restrict__ x, const float* __restrict__ w, const f
   }
 }
 
-// wgrad: dW[64][27] += dY^T * im2col(X).  Per tile: dY [128][64] and the 6 input rows are staged in
-// shared memory; thread = 8 output channels x 7 taps (56 accumulators) over 1 of 8 pixel streams.
+// wgrad: dW[64][27] += dY^T * im2col(X).  Per tile: dY [128][64] (kept in its storage dtype, copied
+// with cp.async into a double buffer) and the 6 input rows are staged in shared memory while the
+// previous tile is being multiplied; thread = 8 output channels x 7 taps (56 accumulators) over 1
+// of 8 pixel streams.
+__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <typename T>
+__device__ __forceinline__ void fl_prefetch_dy(T* sdst, const T* __restrict__ dy, long long tile, long long tiles) {
+  constexpr int V = 16 / sizeof(T), CO = 64;
+  if (tile < tiles)
+    for (int i = threadIdx.x; i < FL_TILE * CO / V; i += blockDim.x)
+      cp_async_16(sdst + (size_t)i * V, dy + tile * FL_TILE * CO + (long long)i * V);
+  cp_async_commit();
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 first_layer_wgrad_32(const T* __restrict__ dy, const T* __restrict__ x, float* __restrict__ dw, int B, int H) {
-  constexpr int CO = 64, K = 27, KP = 28;
-  __shared__ __align__(16) float sdy[FL_TILE][CO];      // 32 KB
-  __shared__ float xs[FL_XR][FL_XW][3];
+  constexpr int CO = 64, K = 27, KP = 28, V = 16 / sizeof(T);
+  extern __shared__ __align__(16) uint8_t fl_smem[];
+  T* sdy = reinterpret_cast<T*>(fl_smem);                                   // [2][FL_TILE][CO]
+  float (*xs)[FL_XR][FL_XW][3] =
+      reinterpret_cast<float (*)[FL_XR][FL_XW][3]>(fl_smem + 2 * FL_TILE * CO * sizeof(T));   // [2][6][34][3]
   const int lane = threadIdx.x & 31, stream = threadIdx.x >> 5;     // one warp per pixel stream
   const int cg = lane & 7, tg = lane >> 3;                          // 8 channel groups x 4 tap groups
   // offsets (relative to the pixel's top-left patch corner) of this thread's 7 patch elements
@@ -381,25 +417,23 @@ first_layer_wgrad_32(const T* __restrict__ dy, const T* __restrict__ x, float* _
 #pragma unroll
     for (int b = 0; b < 7; ++b) acc[a][b] = 0.f;
   const long long tiles = (long long)B * (H / FL_ROWS);
-  constexpr int V = 16 / sizeof(T);
-  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-    __syncthreads();
-    fl_stage_x<T>(x, xs, tile, H);
-    for (int i = threadIdx.x; i < FL_TILE * CO / V; i += blockDim.x) {
-      float tmp[V];
-      load_vec<T>(dy + tile * FL_TILE * CO + (long long)i * V, tmp);
-#pragma unroll
-      for (int j = 0; j < V; ++j) (&sdy[0][0])[i * V + j] = tmp[j];
-    }
-    __syncthreads();
-    const float* xflat = &xs[0][0][0];
+  int buf = 0;
+  fl_prefetch_dy<T>(sdy, dy, blockIdx.x, tiles);
+  fl_commit_x(xs[0], fl_prefetch_x<T>(x, blockIdx.x, tiles, H));
+  cp_async_wait_all();
+  __syncthreads();
+  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, buf ^= 1) {
+    fl_prefetch_dy<T>(sdy + (buf ^ 1) * FL_TILE * CO, dy, tile + gridDim.x, tiles);
+    const FlPix nxt = fl_prefetch_x<T>(x, tile + gridDim.x, tiles, H);
+    const float* xflat = &xs[buf][0][0][0];
+    const T* dtile = sdy + buf * FL_TILE * CO;
 #pragma unroll 2
     for (int i = 0; i < FL_TILE / 8; ++i) {
       const int pl = stream * (FL_TILE / 8) + i;            // pixel inside the tile
       const int base = ((pl / FL_W) * FL_XW + (pl % FL_W)) * 3;
-      const float4 d0 = *reinterpret_cast<const float4*>(&sdy[pl][cg * 8]);
-      const float4 d1 = *reinterpret_cast<const float4*>(&sdy[pl][cg * 8 + 4]);
-      const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+      float d[8];
+#pragma unroll
+      for (int q = 0; q < 8 / V; ++q) load_vec<T>(dtile + pl * CO + cg * 8 + q * V, d + q * V);
 #pragma unroll
       for (int b = 0; b < 7; ++b) {
         const float xv = xflat[base + koff[b]];
@@ -407,10 +441,12 @@ first_layer_wgrad_32(const T* __restrict__ dy, const T* __restrict__ x, float* _
         for (int a = 0; a < 8; ++a) acc[a][b] = fmaf(d[a], xv, acc[a][b]);
       }
     }
+    fl_commit_x(xs[buf ^ 1], nxt);
+    cp_async_wait_all();
+    __syncthreads();
   }
   // combine the 8 pixel streams (deterministic order), then one atomic per output element
-  __syncthreads();
-  float* sacc = &sdy[0][0];                              // reuse: [64][28]
+  float* sacc = reinterpret_cast<float*>(fl_smem);        // reuse: [64][28]
   for (int s = 0; s < 8; ++s) {
     if (stream == s) {
 #pragma unroll
@@ -424,6 +460,21 @@ first_layer_wgrad_32(const T* __restrict__ dy, const T* __restrict__ x, float* _
     __syncthreads();
   }
   for (int i = threadIdx.x; i < CO * K; i += blockDim.x) atomicAdd(&dw[i], sacc[(i / K) * KP + (i % K)]);
+}
+
+template <typename T>
+static int launch_first_layer_wgrad_32(const void* dy, const void* x, float* dw, int B, int H, cudaStream_t stream) {
+  const int smem = 2 * FL_TILE * 64 * (int)sizeof(T) + 2 * FL_XR * FL_XW * 3 * (int)sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CUDA_CHECK(cudaFuncSetAttribute(first_layer_wgrad_32<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  long long tiles = (long long)B * (H / FL_ROWS);
+  int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
+  first_layer_wgrad_32<T><<<grid, 256, smem, stream>>>((const T*)dy, (const T*)x, dw, B, H);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
 }
 
 }  // namespace ddpb
@@ -482,14 +533,8 @@ extern "C" int ddpb_conv3x3_dgrad_simt(const void* dy, const float* w, void* dx,
 extern "C" int ddpb_conv3x3_wgrad_simt(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
                                        int Cout, int dtype, cudaStream_t stream) {
   if (Cin == 3 && Cout == 64 && W == FL_W && H % FL_ROWS == 0) {
-    long long tiles = (long long)B * (H / FL_ROWS);
-    int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
-    if (dtype == DDPB_BF16)
-      first_layer_wgrad_32<bf16><<<grid, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, B, H);
-    else
-      first_layer_wgrad_32<float><<<grid, 256, 0, stream>>>((const float*)dy, (const float*)x, dw, B, H);
-    DDPB_LAUNCH_CHECK();
-    return DDPB_OK;
+    return dtype == DDPB_BF16 ? launch_first_layer_wgrad_32<bf16>(dy, x, dw, B, H, stream)
+                              : launch_first_layer_wgrad_32<float>(dy, x, dw, B, H, stream);
   }
   if (Cin == 3 && Cout == 64) {
     int grid = ceil_div((long long)B * H * W, 64);

@@ -223,7 +223,10 @@ static int alloc_all(Engine* e) {
   // BN defaults: gamma 1, running_var 1 (weights are loaded by the caller afterwards)
   DDPB_CUDA_CHECK(cudaMemset(e->mean, 0, e->total_c * 4));
   DDPB_CUDA_CHECK(cudaMemset(e->invstd, 0, e->total_c * 4));
-  DDPB_CUDA_CHECK(cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking));
+  // the bucket kernels are few, small CTAs on the step's critical tail: give them scheduling priority
+  int prio_lo = 0, prio_hi = 0;
+  DDPB_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->comm, cudaStreamNonBlocking, prio_hi));
   DDPB_CUDA_CHECK(cudaStreamCreateWithFlags(&e->wg, cudaStreamNonBlocking));
   e->ev_dy.resize(c.num_blocks + 1); e->ev_dg.resize(c.num_blocks + 1); e->ev_wg.resize(c.num_blocks + 1);
   for (int i = 0; i <= c.num_blocks; ++i) {
