@@ -339,7 +339,7 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--bucket-plan", default="per_layer", choices=["ddp", "per_layer", "single"])
-    ap.add_argument("--comm", default="auto", choices=["auto", "p2p", "nccl"])
+    ap.add_argument("--comm", default="auto", choices=["auto", "p2p", "nvls", "nccl"])
     ap.add_argument("--no-graph", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -36,7 +36,7 @@ def build_parser(part: str = "2a") -> argparse.ArgumentParser:
                    help="override the part's gradient-sync strategy")
     g.add_argument("--device", default="auto", choices=["auto", "cpu", "cuda"])
     g.add_argument("--backend", default="auto", choices=["auto", "torch", "native"])
-    g.add_argument("--comm", default="auto", choices=["auto", "gloo", "nccl", "p2p"])
+    g.add_argument("--comm", default="auto", choices=["auto", "gloo", "nccl", "p2p", "nvls"])
     g.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"])
     g.add_argument("--synthetic", action="store_true", help="CIFAR-shaped synthetic data")
     g.add_argument("--train-size", type=int, default=50_000)

@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import contextlib
 import ctypes
+import os
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -34,6 +35,7 @@ from .ops import native as nv
 from .ops.native import check, lib, stream_handle
 
 MAX_BLOCKS, MAX_SLOTS = 24, 64
+NVLS_DEFAULT = "0"      # comm="auto" tries the NVSwitch-multicast path only when DDPB_NVLS=1
 STRATEGY_CODE = {"none": 0, "gather_scatter": 1, "allreduce": 2, "bucketed": 3}
 PLAN_CODE = {"ddp": 0, "per_layer": 1, "single": 2}
 
@@ -47,6 +49,7 @@ class EngineConfig(ctypes.Structure):
         ("lr", ctypes.c_float), ("momentum", ctypes.c_float), ("wd", ctypes.c_float),
         ("bucket_plan", ctypes.c_int), ("first_bucket_mb", ctypes.c_float), ("bucket_cap_mb", ctypes.c_float),
         ("use_graph", ctypes.c_int), ("use_tc", ctypes.c_int), ("external_sync", ctypes.c_int),
+        ("external_arena", ctypes.c_void_p), ("external_arena_bytes", ctypes.c_size_t),
     ]
 
 
@@ -66,7 +69,7 @@ class EngineInfo(ctypes.Structure):
         ("bn_w_off", ctypes.c_longlong * MAX_BLOCKS), ("bn_b_off", ctypes.c_longlong * MAX_BLOCKS),
         ("ch_off", ctypes.c_longlong * MAX_BLOCKS),
         ("y", ctypes.c_void_p * MAX_BLOCKS), ("act", ctypes.c_void_p * MAX_BLOCKS),
-        ("launches", ctypes.c_longlong), ("graph_active", ctypes.c_int),
+        ("launches", ctypes.c_longlong), ("graph_active", ctypes.c_int), ("multicast", ctypes.c_int),
     ]
 
 
@@ -96,16 +99,29 @@ class NativeBackend:
         self._lib = lib()
         self._handle = ctypes.c_void_p()
         self._comm = "none"
-        want_p2p = self.world > 1 and cfg.comm in ("auto", "p2p")
-        self._create(external_sync=self.world > 1 and not want_p2p)
-        if want_p2p:
-            ok = self._connect_peers()
-            if not ok:
-                if cfg.comm == "p2p":
-                    raise nv.NativeError("comm=p2p requested but peer mappings could not be established")
-                self._destroy()
-                self._create(external_sync=True)
-        if self.world > 1 and self._comm != "p2p":
+        want_p2p = self.world > 1 and cfg.comm in ("auto", "p2p", "nvls")
+        self._vmm = None
+        if want_p2p and (cfg.comm == "nvls" or (cfg.comm == "auto" and os.environ.get("DDPB_NVLS", NVLS_DEFAULT) == "1")):
+            self._vmm = self._try_vmm_arena()           # NVSwitch multicast (NVLS) when the box exposes it
+            if self._vmm is None and cfg.comm == "nvls":
+                raise nv.NativeError("comm=nvls requested but the multicast arena could not be set up")
+        if self._vmm is not None:
+            self._create(external_sync=False, arena=self._vmm)
+            table = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(p) for p in self._vmm.peers])
+            check(self._lib.ddpb_engine_set_peers(self._handle, table), "engine_set_peers")
+            check(self._lib.ddpb_engine_set_multicast(self._handle, ctypes.c_void_p(self._vmm.mc)), "set_multicast")
+            self._comm = "nvls"
+            dist.barrier()
+        else:
+            self._create(external_sync=self.world > 1 and not want_p2p)
+            if want_p2p:
+                ok = self._connect_peers()
+                if not ok:
+                    if cfg.comm == "p2p":
+                        raise nv.NativeError("comm=p2p requested but peer mappings could not be established")
+                    self._destroy()
+                    self._create(external_sync=True)
+        if self.world > 1 and self._comm not in ("p2p", "nvls"):
             self._comm = "nccl" if dist.get_backend() == "nccl" else dist.get_backend()
         # weights: same construction order and RNG consumption as the reference (seeded by the trainer)
         sd = init_state if init_state is not None else build_model(cfg.model).state_dict()
@@ -115,7 +131,7 @@ class NativeBackend:
         torch.cuda.synchronize(device)
 
     # ---- engine life cycle ---------------------------------------------------------------------
-    def _create(self, external_sync: bool) -> None:
+    def _engine_config(self, external_sync: bool) -> "EngineConfig":
         cfg = self.cfg
         ec = EngineConfig()
         ec.dtype = nv.BF16 if cfg.dtype == "bf16" else nv.F32
@@ -131,6 +147,22 @@ class NativeBackend:
         ec.use_graph = int(cfg.use_cuda_graph)
         ec.use_tc = 1
         ec.external_sync = int(external_sync)
+        return ec
+
+    def _try_vmm_arena(self):
+        """Allocate the symmetric arena with the VMM API and bind it to a multicast object; None when
+        the box does not expose NVLS (every rank takes the same decision)."""
+        from .parallel.vmm import VmmArena
+        need = ctypes.c_size_t(0)
+        ec = self._engine_config(False)
+        check(self._lib.ddpb_engine_arena_bytes(ctypes.byref(ec), ctypes.byref(need)), "engine_arena_bytes")
+        return VmmArena.create(int(need.value), self.device)
+
+    def _create(self, external_sync: bool, arena=None) -> None:
+        ec = self._engine_config(external_sync)
+        if arena is not None:
+            ec.external_arena = ctypes.c_void_p(arena.local)
+            ec.external_arena_bytes = arena.bytes
         self._external_sync = external_sync
         torch.cuda.set_device(self.device)
         check(self._lib.ddpb_engine_create(ctypes.byref(ec), ctypes.byref(self._handle)), "engine_create")
@@ -296,7 +328,7 @@ class NativeBackend:
     def sync_buffers(self) -> None:
         if self.world == 1:
             return
-        if self._comm == "p2p":
+        if self._comm in ("p2p", "nvls"):
             check(self._lib.ddpb_engine_collective(self._handle, 1, stream_handle()), "bcast buffers")
         else:
             dist.broadcast(self.running_mean, src=0)
@@ -306,7 +338,7 @@ class NativeBackend:
     def broadcast_from_rank0(self) -> None:
         if self.world == 1:
             return
-        if self._comm == "p2p":
+        if self._comm in ("p2p", "nvls"):
             torch.cuda.synchronize(self.device)
             dist.barrier()
             check(self._lib.ddpb_engine_collective(self._handle, 0, stream_handle()), "bcast weights")
@@ -318,7 +350,7 @@ class NativeBackend:
     def gather_momentum(self) -> None:
         """The two-shot reduce keeps each momentum slice only on the rank that owns it; bring all
         shards everywhere before the optimizer state is read (checkpoint)."""
-        if self.world > 1 and self._comm == "p2p":
+        if self.world > 1 and self._comm in ("p2p", "nvls"):
             check(self._lib.ddpb_engine_collective(self._handle, 2, stream_handle()), "gather momentum")
 
     # ---- parameter access ---------------------------------------------------------------------------------

@@ -199,6 +199,73 @@ p2p_kernel(const P2PArgs a) {
   if (!a.skip_exit_barrier) cta_barrier_all_ranks(a, 1);
 }
 
+
+// ------------------------------------------------------------------------------------------
+// K-S3  NVLS all-reduce: the reduction happens INSIDE the NVSwitch.  `mc_*` are mappings of the
+// multicast object every rank's arena is bound to (runtime/vmm_arena.cpp): a multimem.ld_reduce on
+// such an address returns the sum of that element over all ranks, a multimem.st writes it to all
+// ranks.  Rank r owns slice r: one switch-reduced load, the SGD update on its momentum shard, one
+// multicast store of the new fp32 weight and one of the bf16 copy - about S bytes per direction per
+// GPU instead of 2(W-1)/W*S for the two-shot kernel, and no per-peer loop at all.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void multimem_st_bf16x4(void* mc, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(mc), "r"(v.x), "r"(v.y) : "memory");
+}
+
+struct NvlsArgs {
+  P2PArgs base;            // flags / epochs / rank / world / slot / range / hyper-parameters, master[rank] = local
+  float* mc_grad;
+  float* mc_master;
+  bf16* mc_shadow;         // may be null (fp32 compute)
+};
+
+__global__ void __launch_bounds__(512)
+p2p_nvls_kernel(const NvlsArgs n) {
+  const P2PArgs& a = n.base;
+  cta_barrier_all_ranks(a, 0);
+  const long long n4 = a.n / 4, base4 = a.off / 4;
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long nthr = (long long)gridDim.x * blockDim.x;
+  const float inv_w = 1.f / (float)a.world;
+  long long lo, hi;
+  slice_of(n4, a.world, a.rank, &lo, &hi);
+  constexpr int U = 4;
+  for (long long i0 = lo + tid; i0 < hi; i0 += nthr * U) {
+    float4 s[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * nthr;
+      s[u] = multimem_ld_reduce_add(n.mc_grad + (base4 + (i < hi ? i : lo)) * 4);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * nthr;
+      if (i >= hi) break;
+      const long long e = (base4 + i) * 4;
+      float4 p = *reinterpret_cast<const float4*>(a.master[a.rank] + e);
+      float4 m = *reinterpret_cast<const float4*>(a.mom + e);
+      sgd_update(s[u], p, m, inv_w, a.lr, a.momentum, a.wd);
+      *reinterpret_cast<float4*>(a.mom + e) = m;
+      multimem_st(n.mc_master + e, p);
+      if (n.mc_shadow) multimem_st_bf16x4(n.mc_shadow + e, make_uint2(pack_bf16x2(p.x, p.y), pack_bf16x2(p.z, p.w)));
+    }
+  }
+  if (!a.skip_exit_barrier) cta_barrier_all_ranks(a, 1);
+}
+
 }  // namespace ddpb
 
 using namespace ddpb;
@@ -240,6 +307,37 @@ extern "C" int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, v
     case DDPB_P2P_ALLGATHER: p2p_kernel<MODE_ALLGATHER><<<blocks, 512, 0, stream>>>(a); break;
     default: DDPB_REQUIRE(false, "p2p: unknown mode %d", mode);
   }
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+// NVLS variant of the two-shot fused reduce+SGD (see p2p_nvls_kernel).  mc_* point into the multicast
+// mapping of the symmetric arena at the same offsets as grad / master / shadow; master_local and mom
+// are this rank's own buffers; `flags` is the usual per-rank table of signal pads.
+extern "C" int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shadow, float* master_local,
+                                  void* const* flags, float* mom, void* epochs, int rank, int world, int slot,
+                                  long long off, long long n, float lr, float momentum, float wd, int blocks,
+                                  int skip_exit_barrier, cudaStream_t stream) {
+  DDPB_REQUIRE(world >= 2 && world <= P2P_MAX_RANKS && rank >= 0 && rank < world, "nvls: bad rank/world %d/%d", rank,
+               world);
+  DDPB_REQUIRE(off % 4 == 0 && n % 4 == 0, "nvls: range must be float4-aligned");
+  DDPB_REQUIRE(slot >= 0 && slot < DDPB_P2P_MAX_SLOTS, "nvls: slot %d out of range", slot);
+  DDPB_REQUIRE(mc_grad && mc_master && master_local && mom && flags, "nvls: null pointer");
+  if (blocks <= 0) {
+    long long want = (n / 4 / world + 512 * 4 - 1) / (512 * 4);
+    blocks = (int)(want < 1 ? 1 : (want > 32 ? 32 : want));
+  }
+  DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "nvls: at most %d blocks", P2P_MAX_BLOCKS);
+  NvlsArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int r = 0; r < world; ++r) a.base.flags[r] = (uint32_t*)flags[r];
+  a.base.master[rank] = master_local;
+  a.base.mom = mom; a.base.epochs = (uint32_t*)epochs;
+  a.base.rank = rank; a.base.world = world; a.base.slot = slot; a.base.off = off; a.base.n = n;
+  a.base.lr = lr; a.base.momentum = momentum; a.base.wd = wd;
+  a.base.skip_exit_barrier = skip_exit_barrier;
+  a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
+  p2p_nvls_kernel<<<blocks, 512, 0, stream>>>(a);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

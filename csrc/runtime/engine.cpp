@@ -62,6 +62,8 @@ struct Engine {
   size_t off_grad = 0, off_master = 0, off_mom = 0, off_shadow = 0, off_rstats = 0, off_flags = 0;
   void* peer_arena[DDPB_MAX_RANKS] = {nullptr};
   bool peers_set = false;
+  bool arena_external = false;     // caller-owned arena: never freed / IPC-closed here
+  void* mc_arena = nullptr;        // multicast mapping of the arena (NVLS), or null
   // local buffers
   uint32_t* epochs = nullptr;
   float *scratch = nullptr, *mean = nullptr, *invstd = nullptr, *logits = nullptr, *dlogits = nullptr;
@@ -170,11 +172,8 @@ static void plan_buckets(Engine* e) {
     b.mode = (c.world > 1 && b.numel * 4 >= 256 * 1024) ? DDPB_P2P_TWOSHOT : DDPB_P2P_ONESHOT;
 }
 
-static int alloc_all(Engine* e) {
-  const auto& c = e->cfg;
-  const long long B = c.max_batch;
-  e->esize = c.dtype == DDPB_BF16 ? 2 : 4;
-  // ---- symmetric arena ----
+// Offsets of the sub-buffers inside the symmetric arena (same on every rank).
+static void carve_arena(Engine* e) {
   size_t cur = 0;
   auto carve = [&](size_t bytes) { size_t o = cur; cur = (size_t)round_up((long long)(cur + bytes), 1024); return o; };
   e->off_grad = carve(e->arena_elems * 4);
@@ -184,7 +183,25 @@ static int alloc_all(Engine* e) {
   e->off_rstats = carve(e->total_c * 2 * 4);
   e->off_flags = carve((size_t)DDPB_P2P_MAX_SLOTS * 2 * DDPB_P2P_MAX_BLOCKS * DDPB_MAX_RANKS * 4);
   e->arena_bytes = cur;
-  ECHECK(ddpb_symm_alloc(e->arena_bytes, &e->arena, e->ipc_handle));
+}
+
+static int alloc_all(Engine* e) {
+  const auto& c = e->cfg;
+  const long long B = c.max_batch;
+  e->esize = c.dtype == DDPB_BF16 ? 2 : 4;
+  // ---- symmetric arena ----
+  carve_arena(e);
+  if (c.external_arena) {
+    // the caller owns the arena (e.g. cuMemCreate memory bound to an NVSwitch multicast object)
+    DDPB_REQUIRE(c.external_arena_bytes >= e->arena_bytes, "engine: external arena too small (%zu < %zu)",
+                 (size_t)c.external_arena_bytes, e->arena_bytes);
+    e->arena = c.external_arena;
+    e->arena_external = true;
+    memset(e->ipc_handle, 0, sizeof(e->ipc_handle));
+    DDPB_CUDA_CHECK(cudaMemset(e->arena, 0, e->arena_bytes));
+  } else {
+    ECHECK(ddpb_symm_alloc(e->arena_bytes, &e->arena, e->ipc_handle));
+  }
   char* a = (char*)e->arena;
   e->grad = (float*)(a + e->off_grad); e->master = (float*)(a + e->off_master);
   e->mom = (float*)(a + e->off_mom); e->shadow = (bf16*)(a + e->off_shadow);
@@ -314,6 +331,15 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   // enough CTAs to keep ~16 B x 8 loads per thread in flight on big buckets, few on small ones
   long long want = (b.numel / 4 + 512 * 4 - 1) / (512 * 4);
   const int blocks = (int)(want < 1 ? 1 : (want > DDPB_P2P_MAX_BLOCKS ? DDPB_P2P_MAX_BLOCKS : want));
+  if (e->mc_arena && b.mode == DDPB_P2P_TWOSHOT) {
+    // NVLS: the switch reduces, one multicast store publishes (sync_p2p.cu, p2p_nvls_kernel)
+    char* mc = (char*)e->mc_arena;
+    LAUNCH(e, ddpb_p2p_sync_nvls(mc + e->off_grad, mc + e->off_master,
+                                 c.dtype == DDPB_BF16 ? (void*)(mc + e->off_shadow) : nullptr, e->master, f, e->mom,
+                                 e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr, c.momentum, c.wd, 0,
+                                 last ? 0 : 1, s));
+    return DDPB_OK;
+  }
   LAUNCH(e, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
                           c.momentum, c.wd, blocks, s));
   return DDPB_OK;
@@ -484,6 +510,19 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
 
 using namespace ddpb;
 
+// Size of the symmetric arena an engine with this configuration needs (for callers that bring their
+// own arena through cfg.external_arena).  Allocates nothing.
+extern "C" int ddpb_engine_arena_bytes(const ddpb_engine_config* cfg, size_t* bytes) {
+  DDPB_REQUIRE(cfg && bytes, "engine_arena_bytes: null argument");
+  DDPB_REQUIRE(cfg->num_blocks > 0 && cfg->num_blocks <= DDPB_MAX_BLOCKS, "engine_arena_bytes: bad block count");
+  Engine tmp;
+  tmp.cfg = *cfg;
+  plan_layout(&tmp);
+  carve_arena(&tmp);
+  *bytes = tmp.arena_bytes;
+  return DDPB_OK;
+}
+
 extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) {
   DDPB_REQUIRE(cfg && handle, "engine_create: null argument");
   DDPB_REQUIRE(cfg->num_blocks > 0 && cfg->num_blocks <= DDPB_MAX_BLOCKS, "engine_create: bad block count");
@@ -504,10 +543,11 @@ extern "C" int ddpb_engine_destroy(void* handle) {
   cudaDeviceSynchronize();
   for (auto& kv : e->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (int r = 0; r < e->cfg.world; ++r)
-    if (r != e->cfg.rank && e->peer_arena[r]) cudaIpcCloseMemHandle(e->peer_arena[r]);
+    if (r != e->cfg.rank && e->peer_arena[r] && !e->arena_external) cudaIpcCloseMemHandle(e->peer_arena[r]);
   for (auto& b : e->blocks) { cudaFree(b.y); cudaFree(b.act); }
   void* frees[] = {e->epochs, e->scratch, e->mean, e->invstd, e->nbt, e->logits, e->dlogits, e->eval_loss,
-                   e->input, e->target, e->dy_buf2[0], e->dy_buf2[1], e->dact, e->arena};
+                   e->input, e->target, e->dy_buf2[0], e->dy_buf2[1], e->dact,
+                   e->arena_external ? nullptr : e->arena};
   for (void* p : frees) if (p) cudaFree(p);
   for (auto& ev : e->bucket_ev) cudaEventDestroy(ev);
   if (e->join_ev) cudaEventDestroy(e->join_ev);
@@ -544,6 +584,7 @@ extern "C" int ddpb_engine_info(void* handle, ddpb_engine_info_t* out) {
     out->bn_w_off[i] = b.bn_w.off; out->bn_b_off[i] = b.bn_b.off; out->ch_off[i] = b.ch_off;
     out->y[i] = b.y; out->act[i] = b.act;
   }
+  out->multicast = e->mc_arena != nullptr;
   out->launches = e->launches;
   out->graph_active = e->cfg.use_graph && !e->graphs.empty();
   return DDPB_OK;
@@ -555,6 +596,17 @@ extern "C" int ddpb_engine_set_peers(void* handle, void* const* peer_arena) {
   DDPB_REQUIRE(e && peer_arena, "engine_set_peers: null argument");
   for (int r = 0; r < e->cfg.world; ++r) e->peer_arena[r] = r == e->cfg.rank ? e->arena : peer_arena[r];
   e->peers_set = true;
+  return DDPB_OK;
+}
+
+// Multicast (NVLS) mapping of this rank's arena: same layout, every store reaches all ranks, every
+// multimem.ld_reduce returns the sum over all ranks.  Pass null to go back to the unicast kernels.
+extern "C" int ddpb_engine_set_multicast(void* handle, void* mc_arena) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(e, "engine_set_multicast: null handle");
+  e->mc_arena = mc_arena;
+  for (auto& kv : e->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  e->graphs.clear();
   return DDPB_OK;
 }
 

@@ -141,6 +141,26 @@ int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, void* const*
                   float* mom, void* epochs, int rank, int world, int slot, long long off, long long n, float lr,
                   float momentum, float wd, int blocks, cudaStream_t stream);
 
+/* NVLS variant of the two-shot mode: mc_* are multicast mappings (runtime/vmm_arena.cpp); the switch
+ * performs the reduction (multimem.ld_reduce) and the broadcast (multimem.st).  Replaces the same
+ * reference calls as ddpb_p2p_sync. */
+int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shadow, float* master_local, void* const* flags,
+                       float* mom, void* epochs, int rank, int world, int slot, long long off, long long n,
+                       float lr, float momentum, float wd, int blocks, int skip_exit_barrier, cudaStream_t stream);
+
+/* Virtual-memory-management arena with an NVSwitch multicast mapping (csrc/runtime/vmm_arena.cpp).
+ * ddpb_vmm_alloc ALLOCATES (cuMemCreate); fds are POSIX file descriptors to pass between processes. */
+int ddpb_vmm_supported(int* multicast_supported);
+int ddpb_vmm_padded_size(size_t bytes, int num_devices, size_t* padded);
+int ddpb_vmm_alloc(size_t bytes, void** ptr, int* fd, unsigned long long* handle);
+int ddpb_vmm_import(int fd, size_t bytes, void** ptr);
+int ddpb_mc_create(size_t bytes, int num_devices, int* fd, unsigned long long* mc_handle);
+int ddpb_mc_import(int fd, unsigned long long* mc_handle);
+int ddpb_mc_add_device(unsigned long long mc_handle);
+int ddpb_mc_bind_and_map(unsigned long long mc_handle, unsigned long long mem_handle, size_t bytes, void** mc_ptr);
+int ddpb_vmm_unmap(void* ptr, size_t bytes);
+int ddpb_vmm_release(unsigned long long handle);
+
 /* Symmetric memory: ALLOCATES `bytes` of zeroed device memory with cudaMalloc on the current
  * device and returns it with a 64-byte IPC handle that peers open with ddpb_symm_open. */
 int ddpb_symm_alloc(size_t bytes, void** ptr, void* handle64);
@@ -169,6 +189,9 @@ typedef struct ddpb_engine_config {
   int use_tc;           /* tcgen05 kernels for bf16 layers with Cin%64==0, Cout%128==0 */
   int external_sync;    /* 1: the engine neither syncs nor steps; the caller reduces `grad` and calls
                            ddpb_sgd_step (NCCL baseline path) */
+  void* external_arena; /* non-null: caller-owned symmetric arena (e.g. cuMemCreate memory bound to a
+                           multicast object, runtime/vmm_arena.cpp) of external_arena_bytes bytes */
+  size_t external_arena_bytes;
 } ddpb_engine_config;
 
 typedef struct ddpb_engine_info_t {
@@ -186,13 +209,17 @@ typedef struct ddpb_engine_info_t {
   void *y[DDPB_MAX_BLOCKS], *act[DDPB_MAX_BLOCKS];
   long long launches;   /* kernels launched by the engine so far (graph replays included) */
   int graph_active;     /* 1 when steps are being replayed from captured CUDA graphs */
+  int multicast;        /* 1 when the NVLS (multimem) reduce kernels are in use */
 } ddpb_engine_info_t;
 
 /* ALLOCATES all device buffers (cudaMalloc), including the symmetric arena. */
+/* Bytes of symmetric arena this configuration needs (for cfg.external_arena); allocates nothing. */
+int ddpb_engine_arena_bytes(const ddpb_engine_config* cfg, size_t* bytes);
 int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle);
 int ddpb_engine_destroy(void* handle);
 int ddpb_engine_info(void* handle, ddpb_engine_info_t* out);
 int ddpb_engine_set_peers(void* handle, void* const* peer_arena);
+int ddpb_engine_set_multicast(void* handle, void* mc_arena);
 int ddpb_engine_set_lr(void* handle, float lr);
 int ddpb_engine_refresh_shadow(void* handle, cudaStream_t stream);
 /* One iteration on the batch already staged in info.input / info.target.  forward = conv stack +

@@ -87,6 +87,31 @@ def test_p2p_strategy_matches_nccl_baseline(sync):
         assert torch.equal(m, p2p[1]["mom"][i]), (sync, i)
 
 
+def test_nvls_multicast_reduce_matches_nccl_baseline():
+    """K-S3: the in-switch reduction (multimem.ld_reduce / multimem.st) where the box exposes NVSwitch
+    multicast; skipped (not failed) when it does not."""
+    from cs744_ddp_b200.parallel.vmm import VmmArena
+    if not VmmArena.supported(torch.device("cuda", 0)):
+        pytest.skip("this device/driver does not report multicast support")
+    os.environ["DDPB_NVLS"] = "1"
+    try:
+        got = _run("bucketed", "auto")
+    finally:
+        os.environ.pop("DDPB_NVLS", None)
+    if got[0]["comm"] != "nvls":
+        pytest.skip(f"multicast arena could not be set up on this box (fell back to {got[0]['comm']})")
+    nccl = _run("bucketed", "nccl")
+    for r in range(WORLD):
+        for a, b in zip(got[r]["losses"], nccl[r]["losses"]):
+            assert abs(a - b) < 2e-3 * max(1.0, abs(b)), (got[r]["losses"], nccl[r]["losses"])
+    for k, v in got[0]["sd"].items():
+        if "running" in k or "num_batches" in k:
+            continue
+        assert torch.equal(v, got[1]["sd"][k]), k
+        if not (k.endswith(".bias") and "layers" in k):
+            assert _rel(v, nccl[0]["sd"][k]) < 5e-3, k
+
+
 def test_bucketed_bf16_ddp_plan_runs_and_replicas_agree():
     out = _run("bucketed", "p2p", dtype="bf16", plan="ddp")
     for k, v in out[0]["sd"].items():
