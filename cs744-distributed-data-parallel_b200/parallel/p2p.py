@@ -34,7 +34,7 @@ class SymmetricArena:
 
     FLAG_BYTES = nv.P2P_MAX_SLOTS * 2 * nv.P2P_MAX_BLOCKS * nv.MAX_RANKS * 4
 
-    def __init__(self, numel: int, device: torch.device, with_shadow: bool = True) -> None:
+    def __init__(self, numel: int, device: torch.device, with_shadow: bool = True, nvls: bool = False) -> None:
         if not dist.is_initialized():
             raise RuntimeError("SymmetricArena needs an initialised process group (control plane)")
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
@@ -49,21 +49,29 @@ class SymmetricArena:
         self.nbytes = self.off_flags + self.FLAG_BYTES
         self._lib = lib()
         torch.cuda.set_device(device)
-        base = ctypes.c_void_p()
-        handle = (ctypes.c_ubyte * 64)()
-        check(self._lib.ddpb_symm_alloc(ctypes.c_size_t(self.nbytes), ctypes.byref(base), handle), "symm_alloc")
-        self.base = int(base.value)
-        handles: List[Optional[bytes]] = [None] * self.world
-        dist.all_gather_object(handles, bytes(handle))
-        self.peer_base: List[int] = []
-        for r, h in enumerate(handles):
-            if r == self.rank:
-                self.peer_base.append(self.base)
-                continue
-            p = ctypes.c_void_p()
-            buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
-            check(self._lib.ddpb_symm_open(buf, ctypes.byref(p)), f"symm_open(rank {r})")
-            self.peer_base.append(int(p.value))
+        self.mc_base = 0                     # multicast mapping (NVLS) or 0
+        self._vmm = None
+        if nvls:
+            from .vmm import VmmArena
+            self._vmm = VmmArena.create(self.nbytes, device, tag=f"symm{numel}")
+        if self._vmm is not None:
+            self.base, self.peer_base, self.mc_base = self._vmm.local, list(self._vmm.peers), self._vmm.mc
+        else:
+            base = ctypes.c_void_p()
+            handle = (ctypes.c_ubyte * 64)()
+            check(self._lib.ddpb_symm_alloc(ctypes.c_size_t(self.nbytes), ctypes.byref(base), handle), "symm_alloc")
+            self.base = int(base.value)
+            handles: List[Optional[bytes]] = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle))
+            self.peer_base: List[int] = []
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    self.peer_base.append(self.base)
+                    continue
+                p = ctypes.c_void_p()
+                buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+                check(self._lib.ddpb_symm_open(buf, ctypes.byref(p)), f"symm_open(rank {r})")
+                self.peer_base.append(int(p.value))
         self.with_shadow = with_shadow
         view = lambda off, n, dt: nv.DeviceBuffer(self.base + off, n * torch.empty((), dtype=dt).element_size()) \
             .as_tensor(device).view(dt)
@@ -86,6 +94,19 @@ class SymmetricArena:
                    self._table(self.off_shadow) if self.with_shadow else None, self._table(self.off_flags),
                    self.mom, self.epochs, self.rank, self.world, slot, off, n, lr, momentum, wd, blocks, stream)
 
+    def sync_nvls(self, off: int = 0, n: Optional[int] = None, lr: float = 0.0, momentum: float = 0.0,
+                  wd: float = 0.0, slot: int = 1, blocks: int = 0, stream=None) -> None:
+        """Two-shot reduce + SGD with the reduction done inside the NVSwitch (needs ``nvls=True``)."""
+        if not self.mc_base:
+            raise RuntimeError("this arena has no multicast mapping")
+        n = self.numel - off if n is None else n
+        tbl = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(b + self.off_flags) for b in self.peer_base])
+        check(self._lib.ddpb_p2p_sync_nvls(
+            ctypes.c_void_p(self.mc_base + self.off_grad), ctypes.c_void_p(self.mc_base + self.off_master),
+            ctypes.c_void_p(self.mc_base + self.off_shadow if self.with_shadow else 0), nv.ptr(self.master), tbl,
+            nv.ptr(self.mom), nv.ptr(self.epochs), self.rank, self.world, slot, nv.cll(off), nv.cll(n), nv.cf(lr),
+            nv.cf(momentum), nv.cf(wd), blocks, 0, nv.stream_handle(stream)), "p2p_sync_nvls")
+
     def allreduce_mean_(self, off: int = 0, n: Optional[int] = None, two_shot: Optional[bool] = None,
                         blocks: int = 0) -> torch.Tensor:
         """Average ``grad[off:off+n]`` over ranks.  With lr = wd = momentum = 0 the fused epilogue
@@ -98,6 +119,9 @@ class SymmetricArena:
         return self.mom[off: off + n]
 
     def close(self) -> None:
+        if self._vmm is not None:        # VMM mappings live until process exit
+            self.peer_base = []
+            return
         for r, p in enumerate(self.peer_base):
             if r != self.rank:
                 self._lib.ddpb_symm_close(ctypes.c_void_p(p))

@@ -48,7 +48,8 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
     max_bytes = int(os.environ.get("SWEEP_MAX_MB", "512")) << 20
-    arena = SymmetricArena(max_bytes // 4, torch.device("cuda", local))
+    arena = SymmetricArena(max_bytes // 4, torch.device("cuda", local), nvls=os.environ.get("SWEEP_NVLS", "1") == "1")
+    has_nvls = bool(arena.mc_base)
     arena.grad.normal_()
     flat = torch.randn(max_bytes // 4, device="cuda")
     p_, m_ = torch.zeros_like(flat), torch.zeros_like(flat)
@@ -62,6 +63,7 @@ def main():
             iters = 50 if size <= (8 << 20) else 10
             two = size >= 256 * 1024
             t_p2p = timed(lambda: arena.sync(nv.P2P_TWOSHOT if two else nv.P2P_ONESHOT, 0, n, 0.1, 0.9, 1e-4), iters, world)
+            t_nvls = timed(lambda: arena.sync_nvls(0, n, 0.1, 0.9, 1e-4), iters, world) if has_nvls and two else float("nan")
             t_nccl = timed(lambda: dist.all_reduce(flat[:n]), iters, world)
 
             def nccl_sgd():
@@ -71,11 +73,12 @@ def main():
             wire = (2.0 * (world - 1) / world * size) if two else ((world - 1) * size)
             roof_us = wire / (LINK_GBS * 1e3)
             rows.append({"bytes": size, "mode": "two-shot" if two else "one-shot", "p2p_fused_us": t_p2p,
+                         "nvls_fused_us": t_nvls, "nvls_frac_of_nvlink_roofline": (size / (LINK_GBS * 1e3)) / t_nvls,
                          "nccl_us": t_nccl, "nccl_plus_sgd_us": t_ns, "p2p_algbw_gbs": size / t_p2p / 1e3,
                          "nccl_algbw_gbs": size / t_nccl / 1e3, "p2p_frac_of_nvlink_roofline": roof_us / t_p2p})
             if rank == 0:
                 r = rows[-1]
-                print(f"{size:>11d} B {r['mode']:8s} p2p+sgd {t_p2p:9.1f} us | nccl {t_nccl:9.1f} us | nccl+sgd {t_ns:9.1f} us"
+                print(f"{size:>11d} B {r['mode']:8s} p2p+sgd {t_p2p:9.1f} us | nvls+sgd {t_nvls:9.1f} us | nccl {t_nccl:9.1f} us | nccl+sgd {t_ns:9.1f} us"
                       f" | p2p algbw {r['p2p_algbw_gbs']:7.1f} GB/s | roofline frac {r['p2p_frac_of_nvlink_roofline']:.2f}",
                       flush=True)
             size *= 4

@@ -35,6 +35,7 @@ bench)
   run bench_ours_nograph 600 python bench.py --steps 50 --warmup 10 --no-graph ;;
 bench2)
   run bench2_p2p 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 50 --warmup 10
+  run bench2_nvls 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29536 bench.py --gpus 2 --steps 50 --warmup 10 --comm nvls
   run bench2_nccl 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29534 bench.py --gpus 2 --steps 50 --warmup 10 --comm nccl
   run bench2_ref 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29535 bench.py --gpus 2 --steps 40 --warmup 10 --impl reference ;;
 sweep)
