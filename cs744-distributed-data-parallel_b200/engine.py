@@ -35,7 +35,7 @@ from .ops import native as nv
 from .ops.native import check, lib, stream_handle
 
 MAX_BLOCKS, MAX_SLOTS = 24, 64
-NVLS_DEFAULT = "0"      # comm="auto" tries the NVSwitch-multicast path only when DDPB_NVLS=1
+NVLS_DEFAULT = "1"      # comm="auto" tries the NVSwitch-multicast (NVLS) path first; DDPB_NVLS=0 disables it
 STRATEGY_CODE = {"none": 0, "gather_scatter": 1, "allreduce": 2, "bucketed": 3}
 PLAN_CODE = {"ddp": 0, "per_layer": 1, "single": 2}
 

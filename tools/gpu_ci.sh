@@ -38,6 +38,15 @@ bench2)
   run bench2_nvls 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29536 bench.py --gpus 2 --steps 50 --warmup 10 --comm nvls
   run bench2_nccl 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29534 bench.py --gpus 2 --steps 50 --warmup 10 --comm nccl
   run bench2_ref 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29535 bench.py --gpus 2 --steps 40 --warmup 10 --impl reference ;;
+benchN)
+  # scaling runs on N GPUs of one box: ours (auto -> NVLS when available), P2P unicast, NCCL baseline, reference
+  for n in ${NLIST:-4 8}; do
+    port=$((29600 + n))
+    run benchN_${n}_auto 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port bench.py --gpus $n --steps 50 --warmup 10
+    run benchN_${n}_p2p 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((port+10)) bench.py --gpus $n --steps 50 --warmup 10 --comm p2p
+    run benchN_${n}_nccl 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((port+20)) bench.py --gpus $n --steps 50 --warmup 10 --comm nccl
+    run benchN_${n}_ref 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((port+30)) bench.py --gpus $n --steps 40 --warmup 10 --impl reference
+  done ;;
 sweep)
   TAILN=20 run sweep 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node ${NGPU:-2} --master-addr 127.0.0.1 --master-port 29541 tools/allreduce_sweep.py ;;
 cli)
