@@ -19,6 +19,8 @@
 //   sum / sum-of-squares reduction for fprop).  Stages are handed over with mbarriers;
 //   tcgen05.commit releases a stage the moment the MMAs that read it retire.
 // * smem is sized so two CTAs fit per SM: one CTA's epilogue overlaps the other's main loop.
+#include <stdlib.h>
+
 #include "../common.cuh"
 #include "../../include/ddp_b200.h"
 #include "../runtime/tensormap.h"
@@ -260,6 +262,31 @@ static long long cta_count(int B, int H, int W, int n_channels, int tile_n) {
   return m_tiles * (n_channels / tile_n);
 }
 
+// CTA-pair (cta_group::2) variant, conv_tc2.cu
+int launch_conv_tc2(bool dgrad, int bn, const void* in, const void* w, void* out, const float* bias, float* stats,
+                    int B, int H, int W, int Cin, int Cout, cudaStream_t stream);
+
+// tile_n codes: 64 / 128 = one CTA per tile; 2128 / 2256 = CTA pair with 128 / 256 channels per tile;
+// 0 = automatic.  DDPB_CONV_2CTA=0 in the environment keeps the automatic choice on single CTAs.
+static bool pair_tiles_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DDPB_CONV_2CTA");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+static int auto_tile(int B, int H, int W, int n_channels) {
+  const long long pixels = (long long)B * H * W;
+  if (pair_tiles_enabled() && pixels >= 2 * TILE_M) {
+    // a pair tile is worth it when it still leaves >= ~1 CTA per SM
+    if (n_channels % 256 == 0 && (pixels / TILE_M) * (n_channels / 256) >= 120) return 2256;
+    if (n_channels % 128 == 0 && (pixels / TILE_M) * (n_channels / 128) >= 120) return 2128;
+  }
+  return (n_channels % 128 == 0 && pixels * n_channels >= 128LL * 128 * 148) ? 128 : 64;
+}
+
 static int check_shapes(int B, int H, int W, int Cin, int Cout) {
   DDPB_REQUIRE(B > 0 && H == W && (H == 32 || H == 16 || H == 8 || H == 4 || H == 2),
                "conv_tc: unsupported spatial size %dx%d", H, W);
@@ -278,7 +305,11 @@ extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const floa
                                    int B, int H, int W, int Cin, int Cout, int tile_n, cudaStream_t stream) {
   int rc = check_shapes(B, H, W, Cin, Cout);
   if (rc) return rc;
-  if (tile_n == 0) tile_n = (Cout % 128 == 0 && (long long)B * H * W * Cout >= 128LL * 128 * 148) ? 128 : 64;
+  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cout);
+  if (tile_n > 2000) {
+    DDPB_REQUIRE(Cout % (tile_n - 2000) == 0, "conv_tc fwd: Cout %d not a multiple of pair tile %d", Cout, tile_n - 2000);
+    return launch_conv_tc2(false, tile_n - 2000, x, w_bf16, y, bias, stats, B, H, W, Cin, Cout, stream);
+  }
   DDPB_REQUIRE(Cout % tile_n == 0, "conv_tc fwd: Cout %d not a multiple of tile %d", Cout, tile_n);
   if (tile_n == 128)
     return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
@@ -296,7 +327,11 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
                                      int Cout, int tile_n, cudaStream_t stream) {
   int rc = check_shapes(B, H, W, Cin, Cout);
   if (rc) return rc;
-  if (tile_n == 0) tile_n = (Cin % 128 == 0 && (long long)B * H * W * Cin >= 128LL * 128 * 148) ? 128 : 64;
+  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cin);
+  if (tile_n > 2000) {
+    DDPB_REQUIRE(Cin % (tile_n - 2000) == 0, "conv_tc dgrad: Cin %d not a multiple of pair tile %d", Cin, tile_n - 2000);
+    return launch_conv_tc2(true, tile_n - 2000, dy, w_bf16, dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+  }
   DDPB_REQUIRE(Cin % tile_n == 0, "conv_tc dgrad: Cin %d not a multiple of tile %d", Cin, tile_n);
   if (tile_n == 128)
     return launch<128, 3, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);

@@ -165,8 +165,10 @@ TC_SHAPES = [  # (hw, cin, cout) of VGG-11 blocks 1..7
 
 @pytest.mark.parametrize("b", [16, 10])
 @pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
-@pytest.mark.parametrize("tile_n", [64, 128])
+@pytest.mark.parametrize("tile_n", [64, 128, 2128, 2256])
 def test_conv_tc_forward(F, R, b, hw, cin, cout, tile_n):
+    if cout % (tile_n % 2000):
+        pytest.skip("tile wider than Cout")
     torch.manual_seed(3)
     x = torch.randn(b, hw, hw, cin, device=DEV).to(torch.bfloat16)
     w = (torch.randn(cout, 3, 3, cin, device=DEV) * 0.05).to(torch.bfloat16)
@@ -180,9 +182,9 @@ def test_conv_tc_forward(F, R, b, hw, cin, cout, tile_n):
 
 @pytest.mark.parametrize("b", [16, 10])
 @pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
-@pytest.mark.parametrize("tile_n", [64, 128])
+@pytest.mark.parametrize("tile_n", [64, 128, 2128, 2256])
 def test_conv_tc_dgrad(F, R, b, hw, cin, cout, tile_n):
-    if cin % tile_n:
+    if cin % (tile_n % 2000):
         pytest.skip("tile wider than Cin")
     torch.manual_seed(4)
     dy = torch.randn(b, hw, hw, cout, device=DEV).to(torch.bfloat16)

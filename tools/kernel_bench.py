@@ -65,12 +65,12 @@ def main():
             total["fwd"] += line(f"first_layer_fwd  {tag}", timeit(lambda: F.conv_fwd_simt(x, w32, bias, True)), flops)
             total["wgrad"] += line(f"first_layer_wgrad {tag}", timeit(lambda: F.conv_wgrad_simt(dy, x)), flops)
         else:
-            for tn in (64, 128):
-                if cout % tn == 0:
+            for tn in (64, 128, 2128, 2256):
+                if cout % (tn % 2000) == 0:
                     t = line(f"conv_fwd_tc n{tn}   {tag}", timeit(lambda: F.conv_fwd_tc(x, w16, bias, True, tn)), flops)
             total["fwd"] += timeit(lambda: F.conv_fwd_tc(x, w16, bias, True, 0))
-            for tn in (64, 128):
-                if cin % tn == 0:
+            for tn in (64, 128, 2128, 2256):
+                if cin % (tn % 2000) == 0:
                     line(f"conv_dgrad_tc n{tn} {tag}", timeit(lambda: F.conv_dgrad_tc(dy, w16, tn)), flops)
             total["dgrad"] += timeit(lambda: F.conv_dgrad_tc(dy, w16, 0))
             dw = torch.zeros(cout, 3, 3, cin, device=DEV)
