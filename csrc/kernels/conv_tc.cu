@@ -40,9 +40,14 @@ struct ConvTcParams {
   int n_out;               // output channels (row pitch of `out`)
   int k_chunks;            // input channels / 64
   int k_total_cols;        // fprop: Cin (column stride between taps in the weight matrix)
+  int slice_dim;           // NC > 1: tensor dimension (2 = h, 3 = n) along which the A box is cut into NC slices
+  int slice_extent;        // NC > 1: extent of one slice along slice_dim
 };
 
-template <int BN, int STAGES, bool DGRAD>
+// NC > 1: the NC CTAs of a cluster (consecutive n-tiles, same pixel tile) need the SAME activation
+// tile.  Each loads 1/NC of it and multicasts that slice into all NC shared memories, so the tile is
+// read from L2 once per cluster instead of once per CTA (the kernels are bound by L2 -> SM traffic).
+template <int BN, int STAGES, bool DGRAD, int NC>
 __global__ void __launch_bounds__(192)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias,
@@ -71,7 +76,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    // a stage is written by all NC CTAs (multicast slices), so it is free only when all NC have consumed it
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], NC); }
     mbar_init(accum_bar, 1);
     fence_mbar_init();
   }
@@ -79,8 +85,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? bias[n_tile * BN + i] : 0.f;
   tc_fence_before();
   __syncthreads();
+  if (NC > 1) cluster_barrier();      // every CTA's barriers exist before a peer's multicast can touch them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  constexpr uint16_t MC_MASK = (uint16_t)((1u << NC) - 1);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -95,7 +103,15 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
         // fprop reads X at p + (r-1, s-1); dgrad reads dY at p - (r-1, s-1)
         const int dh = DGRAD ? 1 - r : r - 1, dw = DGRAD ? 1 - s : s - 1;
-        tma_load_4d(sa, &tmA, &full_bar[stage], kc * KCHUNK, dw, h0 + dh, n0);
+        if (NC == 1) {
+          tma_load_4d(sa, &tmA, &full_bar[stage], kc * KCHUNK, dw, h0 + dh, n0);
+        } else {
+          // tmA's box is one slice here; slice `cr` of the tile goes to every CTA of the cluster
+          const int cr = (int)cluster_rank();
+          const int hh = h0 + dh + (prm.slice_dim == 2 ? cr * prm.slice_extent : 0);
+          const int nn = n0 + (prm.slice_dim == 3 ? cr * prm.slice_extent : 0);
+          tma_load_4d_mc(sa + cr * (A_BYTES / NC), &tmA, &full_bar[stage], kc * KCHUNK, dw, hh, nn, MC_MASK);
+        }
         if (!DGRAD) {
           // weights as a [Cout][9*Cin] matrix: BN rows (co), 64 contiguous K columns
           tma_load_2d(sb, &tmB, &full_bar[stage], tap * prm.k_total_cols + kc * KCHUNK, n_tile * BN);
@@ -127,7 +143,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                                     : umma_desc(sb + kk * 32, 16, 1024);
           umma_bf16(tmem_base, da, db, idesc, (it | kk) != 0);
         }
-        umma_commit(&empty_bar[stage]);        // frees the stage when these MMAs have read it
+        // frees the stage when these MMAs have read it (in every CTA that multicasts into it)
+        if (NC == 1) umma_commit(&empty_bar[stage]); else umma_commit_mc(&empty_bar[stage], MC_MASK);
       }
       umma_commit(accum_bar);                  // accumulator complete
     }
@@ -206,6 +223,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (NC > 1) cluster_barrier();      // peers may still arrive on our barriers: do not exit before them
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
 }
 
@@ -218,15 +236,24 @@ void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn) {
   else { *bw = W; *bh = H; *bn = pixels / (H * W); }
 }
 
-template <int BN, int STAGES, bool DGRAD>
+template <int BN, int STAGES, bool DGRAD, int NC = 1>
 static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, float* stats, int B, int H, int W,
                   int Cin, int Cout, cudaStream_t stream) {
   const int Kc = DGRAD ? Cout : Cin;     // reduction channels
   const int Nc = DGRAD ? Cin : Cout;     // output channels
   int bw, bh, bn;
   pixel_box(H, W, TILE_M, &bw, &bh, &bn);
+  ConvTcParams prm;
+  prm.slice_dim = 0; prm.slice_extent = 0;
+  int sbh = bh, sbn = bn;                // box of one multicast slice
+  if (NC > 1) {
+    if (bn % NC == 0) { sbn = bn / NC; prm.slice_dim = 3; prm.slice_extent = sbn; }
+    else if (bn == 1 && bh % NC == 0) { sbh = bh / NC; prm.slice_dim = 2; prm.slice_extent = sbh; }
+    else DDPB_REQUIRE(false, "conv_tc: cannot cut a %dx%dx%d pixel box into %d multicast slices", bw, bh, bn, NC);
+    DDPB_REQUIRE((Nc / BN) % NC == 0, "conv_tc: %d channel tiles are not a multiple of the cluster size %d", Nc / BN, NC);
+  }
   CUtensorMap tmA, tmB, tmC;
-  int rc = make_tmap_nhwc_bf16(&tmA, in, B, H, W, Kc, KCHUNK, bw, bh, bn);
+  int rc = make_tmap_nhwc_bf16(&tmA, in, B, H, W, Kc, KCHUNK, bw, sbh, sbn);
   if (rc) return rc;
   // output matrix [pixels][Nc]; the epilogue stores 64-column x 128-row boxes (clipped at the edge)
   rc = make_tmap_2d_bf16(&tmC, out, (long long)B * H * W, Nc, 64, TILE_M);
@@ -234,7 +261,6 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   // weight matrix [Cout rows][9*Cin cols]; fprop box = 64 cols x BN rows, dgrad box = 64 cols x 64 rows
   rc = make_tmap_2d_bf16(&tmB, w, Cout, 9LL * Cin, KCHUNK, DGRAD ? 64 : BN);
   if (rc) return rc;
-  ConvTcParams prm;
   prm.H = H; prm.W = W;
   prm.tiles_per_img = H * W >= TILE_M ? H * W / TILE_M : 0;
   prm.imgs_per_tile = H * W >= TILE_M ? 0 : TILE_M / (H * W);
@@ -246,13 +272,24 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   int m_tiles = prm.tiles_per_img > 0 ? B * prm.tiles_per_img : ceil_div(B, prm.imgs_per_tile);
   dim3 grid(m_tiles, Nc / BN);
   constexpr int smem = conv_tc_smem<BN, STAGES>();
-  auto kern = conv3x3_tc_kernel<BN, STAGES, DGRAD>;
+  auto kern = conv3x3_tc_kernel<BN, STAGES, DGRAD, NC>;
   static bool configured = false;
   if (!configured) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  kern<<<grid, 192, smem, stream>>>(tmA, tmB, tmC, bias, stats, prm);
+  if (NC == 1) {
+    kern<<<grid, 192, smem, stream>>>(tmA, tmB, tmC, bias, stats, prm);
+  } else {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid; cfg.blockDim = dim3(192); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 1; attr.val.clusterDim.y = NC; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr; cfg.numAttrs = 1;
+    DDPB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, bias, stats, prm));
+  }
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -266,8 +303,9 @@ static long long cta_count(int B, int H, int W, int n_channels, int tile_n) {
 int launch_conv_tc2(bool dgrad, int bn, const void* in, const void* w, void* out, const float* bias, float* stats,
                     int B, int H, int W, int Cin, int Cout, cudaStream_t stream);
 
-// tile_n codes: 64 / 128 = one CTA per tile; 2128 / 2256 = CTA pair with 128 / 256 channels per tile;
-// 0 = automatic.  DDPB_CONV_2CTA=0 in the environment keeps the automatic choice on single CTAs.
+// tile_n codes: 64 / 128 = one CTA per tile; 1864 / 1464 / 1264 = 64-channel tiles in clusters of 8 / 4 / 2
+// CTAs that multicast the activation tile, 1228 = 128-channel tiles in clusters of 2; 2128 / 2256 = CTA
+// pair (cta_group::2) with 128 / 256 channels per tile; 0 = automatic.  DDPB_CONV_2CTA=0 in the environment keeps the automatic choice on single CTAs.
 static bool pair_tiles_enabled() {
   static int v = -1;
   if (v < 0) {
@@ -310,6 +348,21 @@ extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const floa
     DDPB_REQUIRE(Cout % (tile_n - 2000) == 0, "conv_tc fwd: Cout %d not a multiple of pair tile %d", Cout, tile_n - 2000);
     return launch_conv_tc2(false, tile_n - 2000, x, w_bf16, y, bias, stats, B, H, W, Cin, Cout, stream);
   }
+  if (tile_n > 1000) {          // 1<cluster><tile>: activation tile multicast across a cluster of n-tiles
+    const bf16 *xi = (const bf16*)x, *wi = (const bf16*)w_bf16;
+    bf16* yo = (bf16*)y;
+    const bool deep = cta_count(B, H, W, Cout, 64) <= 148;
+    switch (tile_n) {
+      case 1864: return deep ? launch<64, 8, false, 8>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
+                             : launch<64, 4, false, 8>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      case 1464: return deep ? launch<64, 8, false, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
+                             : launch<64, 4, false, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      case 1264: return launch<64, 4, false, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      case 1228: return launch<128, 3, false, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      case 1428: return launch<128, 3, false, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      default: DDPB_REQUIRE(false, "conv_tc fwd: unknown multicast tile code %d", tile_n);
+    }
+  }
   DDPB_REQUIRE(Cout % tile_n == 0, "conv_tc fwd: Cout %d not a multiple of tile %d", Cout, tile_n);
   if (tile_n == 128)
     return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
@@ -331,6 +384,21 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
   if (tile_n > 2000) {
     DDPB_REQUIRE(Cin % (tile_n - 2000) == 0, "conv_tc dgrad: Cin %d not a multiple of pair tile %d", Cin, tile_n - 2000);
     return launch_conv_tc2(true, tile_n - 2000, dy, w_bf16, dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+  }
+  if (tile_n > 1000) {
+    const bf16 *di = (const bf16*)dy, *wi = (const bf16*)w_bf16;
+    bf16* xo = (bf16*)dx;
+    const bool deep = cta_count(B, H, W, Cin, 64) <= 148;
+    switch (tile_n) {
+      case 1864: return deep ? launch<64, 8, true, 8>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
+                             : launch<64, 4, true, 8>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      case 1464: return deep ? launch<64, 8, true, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
+                             : launch<64, 4, true, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      case 1264: return launch<64, 4, true, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      case 1228: return launch<128, 3, true, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      case 1428: return launch<128, 3, true, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      default: DDPB_REQUIRE(false, "conv_tc dgrad: unknown multicast tile code %d", tile_n);
+    }
   }
   DDPB_REQUIRE(Cin % tile_n == 0, "conv_tc dgrad: Cin %d not a multiple of tile %d", Cin, tile_n);
   if (tile_n == 128)

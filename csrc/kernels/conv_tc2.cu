@@ -293,8 +293,8 @@ int launch_conv_tc2(bool dgrad, int bn, const void* in, const void* w, void* out
   const bf16* ww = (const bf16*)w;
   bf16* o = (bf16*)out;
   if (bn == 256) {
-    return dgrad ? launch2<256, 3, true>(i, ww, o, nullptr, nullptr, B, H, W, Cin, Cout, stream)
-                 : launch2<256, 3, false>(i, ww, o, bias, stats, B, H, W, Cin, Cout, stream);
+    return dgrad ? launch2<256, 6, true>(i, ww, o, nullptr, nullptr, B, H, W, Cin, Cout, stream)
+                 : launch2<256, 6, false>(i, ww, o, bias, stats, B, H, W, Cin, Cout, stream);
   }
   if (bn == 128) {
     return dgrad ? launch2<128, 4, true>(i, ww, o, nullptr, nullptr, B, H, W, Cin, Cout, stream)

@@ -159,16 +159,31 @@ def test_conv_simt(F, R, dtype, b, hw, cin, cout):
     _report("simt_wgrad", F.conv_wgrad_simt(dy, x), R.conv_wgrad(dy, x), 1e-4)
 
 
+def _tile_ok(code, channels, hw):
+    """Can this tile code run a layer with `channels` output channels on hw x hw images?"""
+    if code < 1000:
+        return channels % code == 0
+    if code > 2000:
+        return channels % (code - 2000) == 0
+    nc, tile = (code // 100) % 10, (64 if code % 100 == 64 else 128)
+    if channels % tile or (channels // tile) % nc:
+        return False
+    bh, bn = (128 // hw, 1) if hw * hw >= 128 else (hw, 128 // (hw * hw))
+    return bn % nc == 0 or (bn == 1 and bh % nc == 0)
+
+
+TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256]
+
 TC_SHAPES = [  # (hw, cin, cout) of VGG-11 blocks 1..7
     (16, 64, 128), (8, 128, 256), (8, 256, 256), (4, 256, 512), (4, 512, 512), (2, 512, 512)]
 
 
 @pytest.mark.parametrize("b", [16, 10])
 @pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
-@pytest.mark.parametrize("tile_n", [64, 128, 2128, 2256])
+@pytest.mark.parametrize("tile_n", TILE_CODES)
 def test_conv_tc_forward(F, R, b, hw, cin, cout, tile_n):
-    if cout % (tile_n % 2000):
-        pytest.skip("tile wider than Cout")
+    if not _tile_ok(tile_n, cout, hw):
+        pytest.skip("tile code does not fit this layer")
     torch.manual_seed(3)
     x = torch.randn(b, hw, hw, cin, device=DEV).to(torch.bfloat16)
     w = (torch.randn(cout, 3, 3, cin, device=DEV) * 0.05).to(torch.bfloat16)
@@ -182,10 +197,10 @@ def test_conv_tc_forward(F, R, b, hw, cin, cout, tile_n):
 
 @pytest.mark.parametrize("b", [16, 10])
 @pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
-@pytest.mark.parametrize("tile_n", [64, 128, 2128, 2256])
+@pytest.mark.parametrize("tile_n", TILE_CODES)
 def test_conv_tc_dgrad(F, R, b, hw, cin, cout, tile_n):
-    if cin % (tile_n % 2000):
-        pytest.skip("tile wider than Cin")
+    if not _tile_ok(tile_n, cin, hw):
+        pytest.skip("tile code does not fit this layer")
     torch.manual_seed(4)
     dy = torch.randn(b, hw, hw, cout, device=DEV).to(torch.bfloat16)
     w = (torch.randn(cout, 3, 3, cin, device=DEV) * 0.05).to(torch.bfloat16)

@@ -8,6 +8,21 @@ import sys
 
 import torch
 
+
+def tile_ok(code, channels, hw):
+    if code < 1000:
+        return channels % code == 0
+    if code > 2000:
+        return channels % (code - 2000) == 0
+    nc, tile = (code // 100) % 10, (64 if code % 100 == 64 else 128)
+    if channels % tile or (channels // tile) % nc:
+        return False
+    bh, bn = (128 // hw, 1) if hw * hw >= 128 else (hw, 128 // (hw * hw))
+    return bn % nc == 0 or (bn == 1 and bh % nc == 0)
+
+
+TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256]
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cs744_ddp_b200.models.vgg import conv_blocks  # noqa: E402
 from cs744_ddp_b200.ops import functional as F  # noqa: E402
@@ -65,12 +80,12 @@ def main():
             total["fwd"] += line(f"first_layer_fwd  {tag}", timeit(lambda: F.conv_fwd_simt(x, w32, bias, True)), flops)
             total["wgrad"] += line(f"first_layer_wgrad {tag}", timeit(lambda: F.conv_wgrad_simt(dy, x)), flops)
         else:
-            for tn in (64, 128, 2128, 2256):
-                if cout % (tn % 2000) == 0:
+            for tn in TILE_CODES:
+                if tile_ok(tn, cout, hw):
                     t = line(f"conv_fwd_tc n{tn}   {tag}", timeit(lambda: F.conv_fwd_tc(x, w16, bias, True, tn)), flops)
             total["fwd"] += timeit(lambda: F.conv_fwd_tc(x, w16, bias, True, 0))
-            for tn in (64, 128, 2128, 2256):
-                if cin % (tn % 2000) == 0:
+            for tn in TILE_CODES:
+                if tile_ok(tn, cin, hw):
                     line(f"conv_dgrad_tc n{tn} {tag}", timeit(lambda: F.conv_dgrad_tc(dy, w16, tn)), flops)
             total["dgrad"] += timeit(lambda: F.conv_dgrad_tc(dy, w16, 0))
             dw = torch.zeros(cout, 3, 3, cin, device=DEV)
