@@ -179,6 +179,31 @@ def conv_wgrad_tc(dy, x, split_k: int = 0, out: Optional[torch.Tensor] = None):
     return dw
 
 
+def first_layer_fwd_tc(x, w_bf16, bias, want_stats: bool = False):
+    """conv3x3(3 -> Cout) on the tensor cores: im2col to [pixels][64], then a 1x1 convolution.
+    Returns (y, stats | None, cols) - ``cols`` is what the weight gradient needs later."""
+    b, h, w_, cin = x.shape
+    assert cin == 3 and x.dtype == torch.bfloat16
+    cout = w_bf16.shape[0]
+    cols = torch.empty((b, h, w_, 64), dtype=torch.bfloat16, device=x.device)
+    w_pad = torch.empty((cout, 64), dtype=torch.bfloat16, device=x.device)
+    y = torch.empty((b, h, w_, cout), dtype=torch.bfloat16, device=x.device)
+    stats = torch.zeros(2 * cout, dtype=torch.float32, device=x.device) if want_stats else None
+    check(lib().ddpb_im2col3x3_c3(ptr(x), ptr(w_bf16), ptr(cols), ptr(w_pad), b, h, w_, cout, stream_handle()),
+          "im2col3x3_c3")
+    check(lib().ddpb_conv1x1_fwd_tc(ptr(cols), ptr(w_pad), ptr(bias), ptr(y), ptr(stats), b, h, w_, 64, cout,
+                                    stream_handle()), "conv1x1_fwd_tc")
+    return y, stats, cols
+
+
+def first_layer_wgrad_tc(dy, cols, split_k: int = 0):
+    b, h, w_, cout = dy.shape
+    dw = torch.zeros((cout, 3, 3, 3), dtype=torch.float32, device=dy.device)
+    check(lib().ddpb_patch_wgrad_tc(ptr(dy), ptr(cols), ptr(dw), b, h, w_, cout, 27, 27, split_k, stream_handle()),
+          "patch_wgrad_tc")
+    return dw
+
+
 # ---- P2P sync ---------------------------------------------------------------------------------
 def _ptr_table(ptrs: Optional[Sequence[int]]):
     if ptrs is None:

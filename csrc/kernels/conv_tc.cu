@@ -42,12 +42,20 @@ struct ConvTcParams {
   int k_total_cols;        // fprop: Cin (column stride between taps in the weight matrix)
   int slice_dim;           // NC > 1: tensor dimension (2 = h, 3 = n) along which the A box is cut into NC slices
   int slice_extent;        // NC > 1: extent of one slice along slice_dim
+  int taps;                // 9 = 3x3 filter, 1 = 1x1 (plain GEMM over the pixel rows; first-layer patch matrix)
+  bf16* out_raw;           // KS > 1: output matrix [total_pixels][n_out] (written with plain stores)
 };
 
 // NC > 1: the NC CTAs of a cluster (consecutive n-tiles, same pixel tile) need the SAME activation
 // tile.  Each loads 1/NC of it and multicasts that slice into all NC shared memories, so the tile is
 // read from L2 once per cluster instead of once per CTA (the kernels are bound by L2 -> SM traffic).
-template <int BN, int STAGES, bool DGRAD, int NC>
+//
+// KS > 1 (cluster split-K): the deep layers have few output tiles (64 for the 2x2 layers) but a long
+// reduction (K = 4608), and one CTA cannot pull more than ~30-50 B/clk through TMA.  KS CTAs of a
+// cluster (blockIdx.z) each accumulate 1/KS of the K range of the SAME tile; then every CTA sends the
+// other CTAs' column blocks of its fp32 partial tile through distributed shared memory and finishes
+// BN/KS columns itself (reduce-scatter), so the epilogue work is split KS ways too.
+template <int BN, int STAGES, bool DGRAD, int NC, int KS>
 __global__ void __launch_bounds__(192)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias,
@@ -70,7 +78,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   int n0, h0;
   if (prm.tiles_per_img > 0) { n0 = m_tile / prm.tiles_per_img; h0 = (m_tile % prm.tiles_per_img) * prm.rows_per_tile; }
   else { n0 = m_tile * prm.imgs_per_tile; h0 = 0; }
-  const int k_iters = 9 * prm.k_chunks;
+  const int k_total = prm.taps * prm.k_chunks;
+  const int ks_rank = KS > 1 ? (int)blockIdx.z : 0;
+  const int it_lo = KS > 1 ? k_total * ks_rank / KS : 0;
+  const int k_iters = (KS > 1 ? k_total * (ks_rank + 1) / KS : k_total) - it_lo;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -96,8 +107,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int it = 0; it < k_iters; ++it) {
         const int stage = it % STAGES, use = it / STAGES;
         if (use > 0) mbar_wait(&empty_bar[stage], (use - 1) & 1);
-        const int tap = it / prm.k_chunks, kc = it % prm.k_chunks;
-        const int r = tap / 3, s = tap % 3;
+        const int tap = (it_lo + it) / prm.k_chunks, kc = (it_lo + it) % prm.k_chunks;
+        const int r = prm.taps == 1 ? 1 : tap / 3, s = prm.taps == 1 ? 1 : tap % 3;
         uint8_t* sa = smem + stage * STAGE_BYTES;
         uint8_t* sb = sa + A_BYTES;
         mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
@@ -162,6 +173,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     float* red = reinterpret_cast<float*>(smem + 32768);      // [parts][2*BN]
     mbar_wait(accum_bar, 0);
     tc_fence_after();
+    if constexpr (KS == 1) {
 #pragma unroll 1
     for (int c = 0; c < BN; c += 32) {
       float v[32];
@@ -220,6 +232,93 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
     }
     if (t == 0) tma_store_wait_read();        // shared memory must stay valid until TMA has read it
+    }  // KS == 1
+  }
+  if constexpr (KS > 1) {
+    constexpr int CW = BN / KS;                 // columns this CTA finishes
+    constexpr int RP = 128;                     // receive buffer: [sender][column][row] fp32 (column-major: conflict-free)
+    float* recv = reinterpret_cast<float*>(smem);
+    float* colbuf = recv + (KS - 1) * CW * RP;  // [CW][129] rounded outputs for the BN statistics
+    float* red = colbuf + CW * 129;             // [128 / CW][2 * CW]
+    const int q = warp & 3, row = q * 32 + lane, t = threadIdx.x - 64;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+    __syncwarp();
+    // #0: every CTA's accumulator is complete, i.e. every CTA's pipeline stages are free to be overwritten
+    cluster_barrier();
+    if (warp >= 2) {
+#pragma unroll 1
+      for (int d = 0; d < KS; ++d) {
+        if (d == ks_rank) continue;
+        const int slot = ks_rank < d ? ks_rank : ks_rank - 1;
+        const uint32_t remote = cluster_map_shared(smem_u32(recv + slot * CW * RP), (uint32_t)d);
+#pragma unroll 1
+        for (int c = 0; c < CW; c += 16) {
+          float v[16];
+          tmem_ld_32x32_x16(lane_base + d * CW + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) st_cluster_f32(remote + (uint32_t)(((c + j) * RP + row) * 4), v[j]);
+        }
+      }
+    }
+    __syncwarp();
+    cluster_barrier();                          // #1: all partial column blocks have been delivered
+    if (warp >= 2) {
+      const long long grow = (long long)m_tile * TILE_M + row;
+      const bool valid = grow < prm.total_pixels;
+      bf16* orow = prm.out_raw + grow * prm.n_out + n_tile * BN + ks_rank * CW;
+      const bool want_stats = !DGRAD && stats != nullptr;
+#pragma unroll 1
+      for (int c = 0; c < CW; c += 16) {
+        float v[16];
+        tmem_ld_32x32_x16(lane_base + ks_rank * CW + c, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int sl = 0; sl < KS - 1; ++sl)
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] += recv[(sl * CW + c + j) * RP + row];
+        if (!DGRAD) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] += bias_s[ks_rank * CW + c + j];
+        }
+        uint32_t pk[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+        if (valid) {
+          reinterpret_cast<uint4*>(orow + c)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          reinterpret_cast<uint4*>(orow + c)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+        }
+        if (want_stats) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float2 f = unpack_bf16x2(pk[j]);      // statistics of the ROUNDED tile, like KS == 1
+            colbuf[(c + 2 * j) * 129 + row] = valid ? f.x : 0.f;
+            colbuf[(c + 2 * j + 1) * 129 + row] = valid ? f.y : 0.f;
+          }
+        }
+      }
+      if (want_stats) {
+        constexpr int PARTS = 128 / CW;           // each part sums CW rows of one column
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int col = t % CW, part = t / CW;
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll 8
+        for (int r = part * CW; r < (part + 1) * CW; ++r) {
+          const float f = colbuf[col * 129 + r];
+          s1 += f; s2 = fmaf(f, f, s2);
+        }
+        red[part * 2 * CW + col] = s1;
+        red[part * 2 * CW + CW + col] = s2;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (t < 2 * CW) {
+          float acc = 0.f;
+#pragma unroll
+          for (int pz = 0; pz < PARTS; ++pz) acc += red[pz * 2 * CW + t];
+          const int cc = t < CW ? t : t - CW;
+          atomicAdd(&stats[(t < CW ? 0 : prm.n_out) + n_tile * BN + ks_rank * CW + cc], acc);
+        }
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -236,9 +335,9 @@ void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn) {
   else { *bw = W; *bh = H; *bn = pixels / (H * W); }
 }
 
-template <int BN, int STAGES, bool DGRAD, int NC = 1>
+template <int BN, int STAGES, bool DGRAD, int NC = 1, int KS = 1>
 static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, float* stats, int B, int H, int W,
-                  int Cin, int Cout, cudaStream_t stream) {
+                  int Cin, int Cout, cudaStream_t stream, int taps = 9) {
   const int Kc = DGRAD ? Cout : Cin;     // reduction channels
   const int Nc = DGRAD ? Cin : Cout;     // output channels
   int bw, bh, bn;
@@ -259,7 +358,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   rc = make_tmap_2d_bf16(&tmC, out, (long long)B * H * W, Nc, 64, TILE_M);
   if (rc) return rc;
   // weight matrix [Cout rows][9*Cin cols]; fprop box = 64 cols x BN rows, dgrad box = 64 cols x 64 rows
-  rc = make_tmap_2d_bf16(&tmB, w, Cout, 9LL * Cin, KCHUNK, DGRAD ? 64 : BN);
+  rc = make_tmap_2d_bf16(&tmB, w, Cout, (long long)taps * Cin, KCHUNK, DGRAD ? 64 : BN);
   if (rc) return rc;
   prm.H = H; prm.W = W;
   prm.tiles_per_img = H * W >= TILE_M ? H * W / TILE_M : 0;
@@ -269,16 +368,21 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   prm.n_out = Nc;
   prm.k_chunks = Kc / KCHUNK;
   prm.k_total_cols = Cin;
+  prm.taps = taps;
+  prm.out_raw = out;
+  static_assert(KS == 1 || NC == 1, "split-K and multicast clusters are separate variants");
+  static_assert(KS == 1 || ((KS - 1) * (BN / KS) * 128 + (BN / KS) * 129 + 256) * 4 <= STAGES * (A_BYTES + BN * KCHUNK * 2),
+                "split-K receive buffers must fit in the pipeline stages");
   int m_tiles = prm.tiles_per_img > 0 ? B * prm.tiles_per_img : ceil_div(B, prm.imgs_per_tile);
-  dim3 grid(m_tiles, Nc / BN);
+  dim3 grid(m_tiles, Nc / BN, KS);
   constexpr int smem = conv_tc_smem<BN, STAGES>();
-  auto kern = conv3x3_tc_kernel<BN, STAGES, DGRAD, NC>;
+  auto kern = conv3x3_tc_kernel<BN, STAGES, DGRAD, NC, KS>;
   static bool configured = false;
   if (!configured) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  if (NC == 1) {
+  if (NC == 1 && KS == 1) {
     kern<<<grid, 192, smem, stream>>>(tmA, tmB, tmC, bias, stats, prm);
   } else {
     cudaLaunchConfig_t cfg;
@@ -286,7 +390,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     cfg.gridDim = grid; cfg.blockDim = dim3(192); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cudaLaunchAttribute attr;
     attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = 1; attr.val.clusterDim.y = NC; attr.val.clusterDim.z = 1;
+    attr.val.clusterDim.x = 1; attr.val.clusterDim.y = NC; attr.val.clusterDim.z = KS;
     cfg.attrs = &attr; cfg.numAttrs = 1;
     DDPB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, bias, stats, prm));
   }
@@ -303,7 +407,8 @@ static long long cta_count(int B, int H, int W, int n_channels, int tile_n) {
 int launch_conv_tc2(bool dgrad, int bn, const void* in, const void* w, void* out, const float* bias, float* stats,
                     int B, int H, int W, int Cin, int Cout, cudaStream_t stream);
 
-// tile_n codes: 64 / 128 = one CTA per tile; 1864 / 1464 / 1264 = 64-channel tiles in clusters of 8 / 4 / 2
+// tile_n codes: 4264 / 4464 / 4228 / 4428 = cluster split-K (2 or 4 CTAs per 64- or 128-channel tile);
+// 64 / 128 = one CTA per tile; 1864 / 1464 / 1264 = 64-channel tiles in clusters of 8 / 4 / 2
 // CTAs that multicast the activation tile, 1228 = 128-channel tiles in clusters of 2; 2128 / 2256 = CTA
 // pair (cta_group::2) with 128 / 256 channels per tile; 0 = automatic.  DDPB_CONV_2CTA=1 in the environment lets the automatic choice use pair tiles.
 static bool pair_tiles_enabled() {
@@ -315,14 +420,26 @@ static bool pair_tiles_enabled() {
   return v == 1;
 }
 
-static int auto_tile(int B, int H, int W, int n_channels) {
+static int auto_tile(int B, int H, int W, int n_channels, int k_channels) {
   const long long pixels = (long long)B * H * W;
   if (pair_tiles_enabled() && pixels >= 2 * TILE_M) {
     // a pair tile is worth it when it still leaves >= ~1 CTA per SM
     if (n_channels % 256 == 0 && (pixels / TILE_M) * (n_channels / 256) >= 120) return 2256;
     if (n_channels % 128 == 0 && (pixels / TILE_M) * (n_channels / 128) >= 120) return 2128;
   }
-  return (n_channels % 128 == 0 && pixels * n_channels >= 128LL * 128 * 148) ? 128 : 64;
+  // One CTA ingests only ~30 B/clk, two per SM ~45 (the chip-wide L2 limit): aim for >= 256 CTAs, with
+  // the widest tile (least L2 traffic per FLOP) that gets there, splitting K across a cluster when the
+  // layer has too few output tiles (measured per layer in profiles/kernel_bench_r1.log).
+  const long long t128 = n_channels % 128 == 0 ? cta_count(B, H, W, n_channels, 128) : 0;
+  const long long t64 = cta_count(B, H, W, n_channels, 64);
+  const int k_total = 9 * (k_channels / KCHUNK);
+  const int max_ks = k_total >= 36 ? 4 : (k_total >= 18 ? 2 : 1);     // keep >= 9 k-iterations per CTA
+  if (t128 >= 256) return 128;
+  if (max_ks >= 2 && t128 * 2 >= 256) return 4228;
+  if (max_ks >= 4 && t128 * 4 >= 256) return 4428;
+  if (t64 >= 256 || max_ks == 1) return t128 >= 148 ? 128 : 64;
+  if (t64 * 2 >= 256 || max_ks == 2) return 4264;
+  return 4464;
 }
 
 static int check_shapes(int B, int H, int W, int Cin, int Cout) {
@@ -343,10 +460,24 @@ extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const floa
                                    int B, int H, int W, int Cin, int Cout, int tile_n, cudaStream_t stream) {
   int rc = check_shapes(B, H, W, Cin, Cout);
   if (rc) return rc;
-  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cout);
-  if (tile_n > 2000) {
+  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cout, Cin);
+  if (tile_n > 2000 && tile_n < 4000) {
     DDPB_REQUIRE(Cout % (tile_n - 2000) == 0, "conv_tc fwd: Cout %d not a multiple of pair tile %d", Cout, tile_n - 2000);
     return launch_conv_tc2(false, tile_n - 2000, x, w_bf16, y, bias, stats, B, H, W, Cin, Cout, stream);
+  }
+  if (tile_n > 4000) {          // 4<splits><tile>: cluster split-K
+    const bf16 *xi = (const bf16*)x, *wi = (const bf16*)w_bf16;
+    bf16* yo = (bf16*)y;
+    DDPB_REQUIRE(Cout % (tile_n % 100 == 28 ? 128 : 64) == 0, "conv_tc fwd: Cout %d does not fit tile code %d", Cout, tile_n);
+    switch (tile_n) {
+      case 4264: return cta_count(B, H, W, Cout, 64) * 2 <= 148
+                            ? launch<64, 8, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
+                            : launch<64, 4, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      case 4464: return launch<64, 4, false, 1, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      case 4228: return launch<128, 3, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      case 4428: return launch<128, 3, false, 1, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
+      default: DDPB_REQUIRE(false, "conv_tc fwd: unknown split-K tile code %d", tile_n);
+    }
   }
   if (tile_n > 1000) {          // 1<cluster><tile>: activation tile multicast across a cluster of n-tiles
     const bf16 *xi = (const bf16*)x, *wi = (const bf16*)w_bf16;
@@ -380,10 +511,24 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
                                      int Cout, int tile_n, cudaStream_t stream) {
   int rc = check_shapes(B, H, W, Cin, Cout);
   if (rc) return rc;
-  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cin);
-  if (tile_n > 2000) {
+  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cin, Cout);
+  if (tile_n > 2000 && tile_n < 4000) {
     DDPB_REQUIRE(Cin % (tile_n - 2000) == 0, "conv_tc dgrad: Cin %d not a multiple of pair tile %d", Cin, tile_n - 2000);
     return launch_conv_tc2(true, tile_n - 2000, dy, w_bf16, dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+  }
+  if (tile_n > 4000) {
+    const bf16 *di = (const bf16*)dy, *wi = (const bf16*)w_bf16;
+    bf16* xo = (bf16*)dx;
+    DDPB_REQUIRE(Cin % (tile_n % 100 == 28 ? 128 : 64) == 0, "conv_tc dgrad: Cin %d does not fit tile code %d", Cin, tile_n);
+    switch (tile_n) {
+      case 4264: return cta_count(B, H, W, Cin, 64) * 2 <= 148
+                            ? launch<64, 8, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
+                            : launch<64, 4, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      case 4464: return launch<64, 4, true, 1, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      case 4228: return launch<128, 3, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      case 4428: return launch<128, 3, true, 1, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
+      default: DDPB_REQUIRE(false, "conv_tc dgrad: unknown split-K tile code %d", tile_n);
+    }
   }
   if (tile_n > 1000) {
     const bf16 *di = (const bf16*)dy, *wi = (const bf16*)w_bf16;
@@ -409,4 +554,16 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
     return launch<64, 4, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
   }
   DDPB_REQUIRE(false, "conv_tc dgrad: tile_n must be 64 or 128");
+}
+
+// y[B,H,W,Cout] = x[B,H,W,Cin] * w[Cout,Cin]^T + bias: the same kernel with a single (centre) tap.
+// Used for the first VGG layer, whose 3x3x3 patches are laid out as a [pixels][64] matrix first
+// (ddpb_im2col3x3_c3) so that it runs on the tensor cores like every other layer.
+extern "C" int ddpb_conv1x1_fwd_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats,
+                                   int B, int H, int W, int Cin, int Cout, cudaStream_t stream) {
+  int rc = check_shapes(B, H, W, Cin, Cout);
+  if (rc) return rc;
+  if (Cout % 128 == 0 && cta_count(B, H, W, Cout, 128) >= 148)
+    return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
+  return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
 }

@@ -97,6 +97,48 @@ __global__ void nchw_to_nhwc_kernel(const TI* __restrict__ src, TO* __restrict__
   dst[i] = from_f32<TO>(to_f32(src[((long long)b * c + ch) * hw + p]));
 }
 
+// First layer on the tensor cores: its 3x3x3 patches become rows of a [pixels][64] bf16 matrix
+// (columns (r*3+s)*3+c, 27 real + 37 zero), zero outside the image = the convolution's padding.
+// One thread writes one 16-byte segment, so a warp writes four whole 128-byte rows.  The first
+// Cout*8 threads also lay the [Cout][27] bf16 weights out as [Cout][64] (zero padded).
+__global__ void __launch_bounds__(256)
+im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
+                    bf16* __restrict__ w_pad, long long n_seg, int H, int W, int h_shift, int w_shift, int Cout) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
+  if (i < (long long)Cout * 8) {
+    const int co = (int)(i >> 3), seg = (int)(i & 7);
+    const unsigned short* ws = reinterpret_cast<const unsigned short*>(w) + co * 27;
+    unsigned short v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { const int k = seg * 8 + j; v[j] = k < 27 ? ws[k] : (unsigned short)0; }
+    uint4 pk = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+    reinterpret_cast<uint4*>(w_pad)[i] = pk;
+  }
+  if (i >= n_seg) return;
+  const int seg = (int)(i & 7);
+  uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+  if (seg < 4) {
+    // 32-bit index math (B*H*W*8 < 2^31 is checked by the launcher); H, W are powers of two
+    const unsigned p = (unsigned)(i >> 3);
+    const int wx = (int)(p & (unsigned)(W - 1));
+    const int hy = (int)((p >> w_shift) & (unsigned)(H - 1));
+    const unsigned img = p >> (w_shift + h_shift);
+    unsigned short v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = seg * 8 + j;
+      const int tap = k / 3, c = k - tap * 3;
+      const int r = tap / 3, s2 = tap - r * 3;
+      const int yy = hy + r - 1, xx = wx + s2 - 1;
+      const bool ok = k < 27 && yy >= 0 && yy < H && xx >= 0 && xx < W;
+      v[j] = ok ? xs[((((img << h_shift) + (unsigned)yy) << w_shift) + (unsigned)xx) * 3u + (unsigned)c] : (unsigned short)0;
+    }
+    pk = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+  }
+  reinterpret_cast<uint4*>(cols)[i] = pk;
+}
+
 static int grid_for(long long n, int block, int cap = 148 * 16) {
   long long g = (n + block - 1) / block;
   if (g < 1) g = 1;
@@ -160,6 +202,24 @@ extern "C" int ddpb_nchw_to_nhwc(const void* src, void* dst, int n, int c, int h
     nchw_to_nhwc_kernel<bf16, bf16><<<blocks, 256, 0, stream>>>((const bf16*)src, (bf16*)dst, n, c, hw);
   else
     DDPB_REQUIRE(false, "nchw_to_nhwc: unsupported dtype pair");
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+// x bf16 [B,H,W,3] -> cols bf16 [B*H*W][64] (3x3 patches, zero padded), w bf16 [Cout][27] -> w_pad [Cout][64].
+extern "C" int ddpb_im2col3x3_c3(const void* x, const void* w_bf16, void* cols, void* w_pad, int B, int H, int W,
+                                 int Cout, cudaStream_t stream) {
+  DDPB_REQUIRE(B > 0 && H > 0 && W > 0 && Cout > 0 && (H & (H - 1)) == 0 && (W & (W - 1)) == 0,
+               "im2col3x3_c3: H and W must be powers of two");
+  const long long n_seg = (long long)B * H * W * 8;
+  DDPB_REQUIRE(n_seg < (1LL << 31), "im2col3x3_c3: batch too large");
+  int h_shift = 0, w_shift = 0;
+  while ((1 << h_shift) < H) ++h_shift;
+  while ((1 << w_shift) < W) ++w_shift;
+  DDPB_REQUIRE(n_seg >= (long long)Cout * 8, "im2col3x3_c3: fewer pixels than output channels");
+  const long long blocks = (n_seg + 255) / 256;
+  im2col3x3_c3_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
+                                                            (bf16*)w_pad, n_seg, H, W, h_shift, w_shift, Cout);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

@@ -26,8 +26,6 @@ constexpr int WG_N = 64;             // input channels per CTA (per tap)
 constexpr int WG_K = 64;             // pixels per pipeline stage
 constexpr int WG_TAPS = 3;           // taps per CTA (one filter row)
 constexpr int WG_BOX = WG_K * 128;   // bytes of one 64x64 bf16 box
-constexpr int WG_STAGE = (WG_M / 64 + WG_TAPS) * WG_BOX;     // 2 dY boxes + 3 X boxes = 40 KB
-constexpr int WG_TMEM_COLS = 256;    // 3 x 64 used
 
 struct WgradParams {
   int H, W;
@@ -36,14 +34,21 @@ struct WgradParams {
   int rows_per_chunk;
   int total_chunks;     // ceil(B*H*W / 64)
   int Cin, Cout;
+  float* dw_raw;        // M == 64 variant: gradient matrix [64][ld_raw], columns < cols_raw are accumulated
+  int ld_raw, cols_raw;
 };
 
 void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn);   // conv_tc.cu
 
-template <int STAGES>
+// M = 128, TAPS = 3: the 3x3 layers.  M = 64, TAPS = 1: the first layer as a plain GEMM over its patch
+// matrix (x = [pixels][64], 27 valid columns); the 64x27 result is added with scalar atomics.
+template <int STAGES, int M, int TAPS>
 __global__ void __launch_bounds__(192)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                 const __grid_constant__ CUtensorMap tmW, const WgradParams prm) {
+  constexpr int A_BOXES = M / 64;
+  constexpr int WG_STAGE = (A_BOXES + TAPS) * WG_BOX;       // 3x3: 2 dY boxes + 3 X boxes = 40 KB
+  constexpr int WG_TMEM_COLS = TAPS == 3 ? 256 : 64;        // TAPS x 64 used
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * WG_STAGE);
@@ -53,7 +58,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int co_blk = blockIdx.x / (prm.Cin / WG_N), ci_blk = blockIdx.x % (prm.Cin / WG_N);
-  const int r = blockIdx.y;                      // filter row
+  const int r = TAPS == 3 ? blockIdx.y : 1;      // filter row (1x1: the centre)
   const int split = blockIdx.z, nsplit = gridDim.z;
   const int chunk_lo = (int)((long long)prm.total_chunks * split / nsplit);
   const int chunk_hi = (int)((long long)prm.total_chunks * (split + 1) / nsplit);
@@ -85,16 +90,18 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
           else { n0 = chunk * prm.imgs_per_chunk; h0 = 0; }
           uint8_t* s = smem + stage * WG_STAGE;
           mbar_expect_tx(&full_bar[stage], WG_STAGE);
-          tma_load_4d(s, &tmDY, &full_bar[stage], co_blk * WG_M, 0, h0, n0);
-          tma_load_4d(s + WG_BOX, &tmDY, &full_bar[stage], co_blk * WG_M + 64, 0, h0, n0);
 #pragma unroll
-          for (int t = 0; t < WG_TAPS; ++t)
-            tma_load_4d(s + (2 + t) * WG_BOX, &tmX, &full_bar[stage], ci_blk * WG_N, t - 1, h0 + r - 1, n0);
+          for (int a = 0; a < A_BOXES; ++a)
+            tma_load_4d(s + a * WG_BOX, &tmDY, &full_bar[stage], co_blk * M + a * 64, 0, h0, n0);
+#pragma unroll
+          for (int t = 0; t < TAPS; ++t)
+            tma_load_4d(s + (A_BOXES + t) * WG_BOX, &tmX, &full_bar[stage], ci_blk * WG_N, TAPS == 3 ? t - 1 : 0,
+                        h0 + r - 1, n0);
         }
       }
     } else if (warp == 1) {
       if (lane == 0) {
-        constexpr uint32_t idesc = umma_idesc_bf16(WG_M, WG_N, true, true);
+        constexpr uint32_t idesc = umma_idesc_bf16(M, WG_N, true, true);
         for (int it = 0; it < k_iters; ++it) {
           const int stage = it % STAGES, use = it / STAGES;
           mbar_wait(&full_bar[stage], use & 1);
@@ -105,14 +112,32 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
             // MN-major A: two 64-channel blocks WG_BOX apart (LBO), 8-pixel groups 1024 B apart (SBO)
             const uint64_t da = umma_desc(s + kk * 2048, WG_BOX, 1024);
 #pragma unroll
-            for (int t = 0; t < WG_TAPS; ++t) {
-              const uint64_t db = umma_desc(s + (2 + t) * WG_BOX + kk * 2048, WG_BOX, 1024);
+            for (int t = 0; t < TAPS; ++t) {
+              const uint64_t db = umma_desc(s + (A_BOXES + t) * WG_BOX + kk * 2048, WG_BOX, 1024);
               umma_bf16(tmem_base + t * WG_N, da, db, idesc, (it | kk) != 0);
             }
           }
           umma_commit(&empty_bar[stage]);
         }
         umma_commit(accum_bar);
+      }
+    } else if (M == 64) {
+      // 64-row accumulator: row i lives in TMEM lane (i % 16) + 32 * (i / 16), i.e. the lower half of
+      // each warp's lane quarter.  Only cols_raw (27) of the 64 columns are real.
+      const int q = warp & 3;
+      mbar_wait(accum_bar, 0);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < WG_N; c += 32) {
+        float v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c, v);
+        tmem_ld_wait();
+        if (lane < 16) {
+          float* dst = prm.dw_raw + (size_t)(co_blk * 64 + q * 16 + lane) * prm.ld_raw;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c + j < prm.cols_raw) atomicAdd(dst + c + j, v[j]);
+        }
       }
     } else {
       // epilogue: TMEM -> registers -> shared memory (128B-swizzled [128 co][32 ci] fp32 boxes), then
@@ -123,7 +148,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
       mbar_wait(accum_bar, 0);
       tc_fence_after();
 #pragma unroll 1
-      for (int t = 0; t < WG_TAPS; ++t) {
+      for (int t = 0; t < TAPS; ++t) {
 #pragma unroll 1
         for (int c = 0; c < WG_N; c += 32) {
           float v[32];
@@ -140,7 +165,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (threadIdx.x == 64) {
 #pragma unroll
-        for (int t = 0; t < WG_TAPS; ++t)
+        for (int t = 0; t < TAPS; ++t)
 #pragma unroll
           for (int hblk = 0; hblk < 2; ++hblk)
             tma_reduce_add_2d(&tmW, smem + (t * 2 + hblk) * (WG_M * 128),
@@ -197,15 +222,57 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
     }
   }
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
+  prm.dw_raw = nullptr; prm.ld_raw = 0; prm.cols_raw = 0;
   constexpr int STAGES = 4;
-  constexpr int smem = STAGES * WG_STAGE + (2 * STAGES + 1) * 8 + 16 + 1024;
+  constexpr int smem = STAGES * (WG_M / 64 + WG_TAPS) * WG_BOX + (2 * STAGES + 1) * 8 + 16 + 1024;
+  auto kern = wgrad_tc_kernel<STAGES, WG_M, WG_TAPS>;
   static bool configured = false;
   if (!configured) {
-    DDPB_CUDA_CHECK(cudaFuncSetAttribute(wgrad_tc_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
   dim3 grid(base_ctas / 3, 3, split_k);
-  wgrad_tc_kernel<STAGES><<<grid, 192, smem, stream>>>(tmDY, tmX, tmW, prm);
+  kern<<<grid, 192, smem, stream>>>(tmDY, tmX, tmW, prm);
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
+}
+
+// dw (fp32 [64][ld], columns < cols) += dy[pixels][64]^T * x[pixels][64]: the first layer's weight
+// gradient from its patch matrix (ddpb_im2col3x3_c3), split over ~148 CTAs along the pixels.
+extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw, int B, int H, int W, int Cout,
+                                   int ld, int cols, int split_k, cudaStream_t stream) {
+  DDPB_REQUIRE(B > 0 && H == W && (H == 32 || H == 16 || H == 8), "patch_wgrad_tc: unsupported spatial size %dx%d", H, W);
+  DDPB_REQUIRE(Cout % 64 == 0 && cols >= 1 && cols <= 64 && ld >= cols, "patch_wgrad_tc: bad shape (Cout %d, cols %d, ld %d)",
+               Cout, cols, ld);
+  int bw, bh, bn;
+  pixel_box(H, W, WG_K, &bw, &bh, &bn);
+  CUtensorMap tmDY, tmX;
+  int rc = make_tmap_nhwc_bf16(&tmDY, dy, B, H, W, Cout, 64, bw, bh, bn);
+  if (rc) return rc;
+  rc = make_tmap_nhwc_bf16(&tmX, x_cols, B, H, W, 64, 64, bw, bh, bn);
+  if (rc) return rc;
+  WgradParams prm;
+  prm.H = H; prm.W = W;
+  prm.chunks_per_img = H * W / WG_K;
+  prm.imgs_per_chunk = 0;
+  prm.rows_per_chunk = bh;
+  prm.total_chunks = B * prm.chunks_per_img;
+  prm.Cin = 64; prm.Cout = Cout;
+  prm.dw_raw = dw; prm.ld_raw = ld; prm.cols_raw = cols;
+  const int base_ctas = Cout / 64;
+  if (split_k <= 0) split_k = 148 / base_ctas;
+  if (split_k > prm.total_chunks) split_k = prm.total_chunks;
+  if (split_k < 1) split_k = 1;
+  constexpr int STAGES = 8;
+  constexpr int smem = STAGES * 2 * WG_BOX + (2 * STAGES + 1) * 8 + 16 + 1024;
+  auto kern = wgrad_tc_kernel<STAGES, 64, 1>;
+  static bool configured = false;
+  if (!configured) {
+    DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(base_ctas, 1, split_k);
+  kern<<<grid, 192, smem, stream>>>(tmDY, tmX, tmDY /* unused */, prm);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

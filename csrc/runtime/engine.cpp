@@ -70,6 +70,7 @@ struct Engine {
   float *loss = nullptr, *eval_loss = nullptr; int *correct = nullptr; long long* nbt = nullptr;
   size_t scratch_floats = 0;
   void *input = nullptr, *dy_buf2[2] = {nullptr, nullptr}, *dact = nullptr; long long* target = nullptr;
+  void *x0cols = nullptr, *w0pad = nullptr;   // first layer as a GEMM: patch matrix [B*1024][64], weights [64][64]
   std::vector<Bucket> buckets;
   cudaStream_t comm = nullptr, wg = nullptr;
   std::vector<cudaEvent_t> bucket_ev, ev_dy, ev_dg, ev_wg;
@@ -226,6 +227,10 @@ static int alloc_all(Engine* e) {
   DDPB_CUDA_CHECK(cudaMemset(e->eval_loss, 0, 64));
   DDPB_CUDA_CHECK(cudaMalloc(&e->input, B * 32 * 32 * 3 * e->esize));
   DDPB_CUDA_CHECK(cudaMalloc(&e->target, B * 8));
+  if (c.dtype == DDPB_BF16 && c.use_tc && e->blocks[0].cin == 3 && e->blocks[0].cout % 64 == 0) {
+    DDPB_CUDA_CHECK(cudaMalloc(&e->x0cols, B * 32 * 32 * 64 * 2));
+    DDPB_CUDA_CHECK(cudaMalloc(&e->w0pad, (size_t)e->blocks[0].cout * 64 * 2));
+  }
   long long max_y = 0, max_act = 512;
   for (auto& b : e->blocks) {
     long long y = (long long)b.hw * b.hw * b.cout;
@@ -268,6 +273,10 @@ static bool use_tc(const Engine* e, const Block& b) {
 static bool use_tc_wgrad(const Engine* e, const Block& b) {
   return use_tc(e, b) && b.cout % 128 == 0;
 }
+// the 3-channel first layer: im2col to a [pixels][64] matrix, then 1x1-conv forward and GEMM wgrad
+static bool use_tc_first(const Engine* e, const Block& b) {
+  return e->cfg.dtype == DDPB_BF16 && e->cfg.use_tc && b.cin == 3 && b.cout % 64 == 0 && b.hw == 32 && e->x0cols;
+}
 
 #define LAUNCH(e, call)   \
   do {                    \
@@ -288,7 +297,10 @@ static int forward(Engine* e, int B, int training, cudaStream_t s) {
     const float* bias = e->master + b.conv_b.off;
     if (use_tc(e, b))
       LAUNCH(e, ddpb_conv3x3_fwd_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0, s));
-    else {
+    else if (use_tc_first(e, b)) {
+      LAUNCH(e, ddpb_im2col3x3_c3(x, e->shadow + b.conv_w.off, e->x0cols, e->w0pad, B, b.hw, b.hw, b.cout, s));
+      LAUNCH(e, ddpb_conv1x1_fwd_tc(e->x0cols, e->w0pad, bias, b.y, st, B, b.hw, b.hw, 64, b.cout, s));
+    } else {
       LAUNCH(e, ddpb_conv3x3_fwd_simt(x, e->master + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, dt, s));
       if (st && !(b.cin == 3 && b.cout == 64)) e->counting += 1;       // separate channel_stats launch
     }
@@ -410,6 +422,8 @@ static int backward(Engine* e, int B, cudaStream_t s) {
     DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->ev_dy[i], 0));
     if (use_tc_wgrad(e, b))
       LAUNCH(e, ddpb_conv3x3_wgrad_tc(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, e->wg));
+    else if (use_tc_first(e, b))
+      LAUNCH(e, ddpb_patch_wgrad_tc(dy, e->x0cols, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cout, 27, 27, 0, e->wg));
     else
       LAUNCH(e, ddpb_conv3x3_wgrad_simt(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, e->wg));
     DDPB_CUDA_CHECK(cudaEventRecord(e->ev_wg[i], e->wg));
@@ -546,7 +560,7 @@ extern "C" int ddpb_engine_destroy(void* handle) {
     if (r != e->cfg.rank && e->peer_arena[r] && !e->arena_external) cudaIpcCloseMemHandle(e->peer_arena[r]);
   for (auto& b : e->blocks) { cudaFree(b.y); cudaFree(b.act); }
   void* frees[] = {e->epochs, e->scratch, e->mean, e->invstd, e->nbt, e->logits, e->dlogits, e->eval_loss,
-                   e->input, e->target, e->dy_buf2[0], e->dy_buf2[1], e->dact,
+                   e->input, e->target, e->dy_buf2[0], e->dy_buf2[1], e->dact, e->x0cols, e->w0pad,
                    e->arena_external ? nullptr : e->arena};
   for (void* p : frees) if (p) cudaFree(p);
   for (auto& ev : e->bucket_ev) cudaEventDestroy(ev);

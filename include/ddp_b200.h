@@ -130,6 +130,22 @@ int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* dx, int B, i
 int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
                           int split_k, cudaStream_t stream);
 
+/* First layer (Cin = 3) on the tensor cores: its 3x3x3 patches are laid out as a [B*H*W][64] bf16
+ * matrix (27 real columns), after which forward is a 1x1 convolution and the weight gradient a plain
+ * split-K GEMM.  im2col also pads the bf16 weights [Cout][27] -> [Cout][64]. */
+int ddpb_im2col3x3_c3(const void* x_nhwc3, const void* w_bf16, void* cols, void* w_pad, int B, int H, int W, int Cout,
+                      cudaStream_t stream);
+int ddpb_conv1x1_fwd_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats, int B, int H,
+                        int W, int Cin, int Cout, cudaStream_t stream);
+/* dw (fp32 [Cout][ld], columns < cols) accumulates dy^T * x_cols. */
+int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw, int B, int H, int W, int Cout, int ld, int cols,
+                        int split_k, cudaStream_t stream);
+
+/* Diagnostic (csrc/kernels/tma_probe.cu, tools/tma_probe.py): per-CTA L2 -> shared-memory ingest rate of
+ * the conv load patterns.  No reference counterpart. */
+int ddpb_probe_tma(int mode, int stages, int iters, int ctas, int smem_pad_kb, const void* act, const void* wgt,
+                   const void* flat, long long flat_bytes, cudaStream_t stream);
+
 /* ---- peer-to-peer gradient engine (csrc/kernels/sync_p2p.cu, csrc/runtime/symm_mem.cpp) --- */
 
 /* One fused reduce(+SGD) / broadcast / all-gather step over elements [off, off+n) of the symmetric

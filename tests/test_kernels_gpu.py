@@ -163,6 +163,8 @@ def _tile_ok(code, channels, hw):
     """Can this tile code run a layer with `channels` output channels on hw x hw images?"""
     if code < 1000:
         return channels % code == 0
+    if code > 4000:           # cluster split-K: 4<splits><tile>
+        return channels % (64 if code % 100 == 64 else 128) == 0
     if code > 2000:
         return channels % (code - 2000) == 0
     nc, tile = (code // 100) % 10, (64 if code % 100 == 64 else 128)
@@ -172,7 +174,7 @@ def _tile_ok(code, channels, hw):
     return bn % nc == 0 or (bn == 1 and bh % nc == 0)
 
 
-TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256]
+TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256, 4264, 4464, 4228, 4428]
 
 TC_SHAPES = [  # (hw, cin, cout) of VGG-11 blocks 1..7
     (16, 64, 128), (8, 128, 256), (8, 256, 256), (4, 256, 512), (4, 512, 512), (2, 512, 512)]
@@ -219,6 +221,26 @@ def test_conv_tc_wgrad(F, R, b, hw, cin, cout, split_k):
     dw = F.conv_wgrad_tc(dy, x, split_k=split_k)
     torch.cuda.synchronize()
     _report(f"tc_wgrad hw{hw} {cin}->{cout} b{b} s{split_k}", dw, R.conv_wgrad(dy, x), 2e-3)
+
+
+@pytest.mark.parametrize("b", [16, 5])
+@pytest.mark.parametrize("cout", [64, 128])
+def test_first_layer_tc(F, R, b, cout):
+    """3-channel first layer as im2col + tensor-core GEMM: forward, BN statistics and weight gradient."""
+    torch.manual_seed(15)
+    x = torch.randn(b, 32, 32, 3, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(cout, 3, 3, 3, device=DEV) * 0.2).to(torch.bfloat16)
+    bias = torch.randn(cout, device=DEV) * 0.1
+    y, stats, cols = F.first_layer_fwd_tc(x, w, bias, want_stats=True)
+    torch.cuda.synchronize()
+    assert cols[..., 27:].abs().max().item() == 0
+    _report(f"first_tc_fwd b{b} c{cout}", y, R.conv_fwd(x, w, bias), 6e-3)
+    _report("first_tc_stats", stats, R.channel_stats(y), 1e-3)
+    dy = torch.randn(b, 32, 32, cout, device=DEV).to(torch.bfloat16)
+    for split_k in (0, 1, 7):
+        dw = F.first_layer_wgrad_tc(dy, cols, split_k=split_k)
+        torch.cuda.synchronize()
+        _report(f"first_tc_wgrad b{b} c{cout} s{split_k}", dw, R.conv_wgrad(dy, x), 2e-3)
 
 
 @pytest.mark.parametrize("mode_name", ["oneshot", "twoshot", "root"])

@@ -12,6 +12,8 @@ import torch
 def tile_ok(code, channels, hw):
     if code < 1000:
         return channels % code == 0
+    if code > 4000:           # cluster split-K: 4<splits><tile>
+        return channels % (64 if code % 100 == 64 else 128) == 0
     if code > 2000:
         return channels % (code - 2000) == 0
     nc, tile = (code // 100) % 10, (64 if code % 100 == 64 else 128)
@@ -21,7 +23,7 @@ def tile_ok(code, channels, hw):
     return bn % nc == 0 or (bn == 1 and bh % nc == 0)
 
 
-TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256]
+TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256, 4264, 4464, 4228, 4428]
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cs744_ddp_b200.models.vgg import conv_blocks  # noqa: E402
@@ -77,8 +79,11 @@ def main():
         bias = torch.zeros(cout, device=DEV)
         tag = f"L{blk.index} {hw}x{hw} {cin}->{cout}"
         if cin == 3:
-            total["fwd"] += line(f"first_layer_fwd  {tag}", timeit(lambda: F.conv_fwd_simt(x, w32, bias, True)), flops)
-            total["wgrad"] += line(f"first_layer_wgrad {tag}", timeit(lambda: F.conv_wgrad_simt(dy, x)), flops)
+            line(f"first_layer_fwd (simt) {tag}", timeit(lambda: F.conv_fwd_simt(x, w32, bias, True)), flops)
+            line(f"first_layer_wgrad (simt) {tag}", timeit(lambda: F.conv_wgrad_simt(dy, x)), flops)
+            total["fwd"] += line(f"first_layer_fwd im2col+tc {tag}", timeit(lambda: F.first_layer_fwd_tc(x, w16, bias, True)), flops)
+            cols = F.first_layer_fwd_tc(x, w16, bias, True)[2]
+            total["wgrad"] += line(f"first_layer_wgrad tc {tag}", timeit(lambda: F.first_layer_wgrad_tc(dy, cols)), flops)
         else:
             for tn in TILE_CODES:
                 if tile_ok(tn, cout, hw):
