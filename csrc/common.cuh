@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 #define DDPB_OK 0
 #define DDPB_ERR_CUDA 1
@@ -39,6 +40,36 @@ void set_last_error(const char* fmt, ...);
   } while (0)
 
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// Programmatic dependent launch: a kernel launched through launch_ex(..., pdl = true) may be scheduled
+// while its predecessor on the stream is still running, so its prologue (barrier init, TMEM
+// allocation, descriptor prefetch, index math) and the launch latency overlap the predecessor's tail.
+// Such a kernel MUST execute pdl_wait() before its first access to global memory; every kernel calls
+// pdl_launch_dependents() early so that ITS successor can be scheduled.  DDPB_PDL=0 disables it.
+bool pdl_enabled();
+int pdl_mask();         // DDPB_PDL_MASK: bit per kernel family (debugging aid), default all ones
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                    dim3 cluster, int pdl, Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (cluster.x * cluster.y * cluster.z > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster.x; attr[n].val.clusterDim.y = cluster.y; attr[n].val.clusterDim.z = cluster.z;
+    ++n;
+  }
+  if (pdl && pdl_enabled() && (pdl_mask() & pdl)) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr; cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 typedef __nv_bfloat16 bf16;
 
@@ -76,6 +107,28 @@ template <> __device__ __forceinline__ void load_vec<bf16>(const bf16* p, float*
   out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
   out[4] = c.x; out[5] = c.y; out[6] = d.x; out[7] = d.y;
 }
+// Coherent variants (ld.global.ca, never ld.global.nc).  Kernels launched as programmatic dependents
+// must use these for everything an earlier kernel wrote: their lifetime overlaps the producer's, so the
+// read-only path (LDG.CONSTANT) the compiler picks for const __restrict__ pointers returns stale lines
+// (measured: BatchNorm statistics of the PREVIOUS step).  ld.global.cg would also be correct but
+// compiles to LDG.STRONG.GPU, which made the BatchNorm kernels ~2x slower.
+template <typename T> __device__ __forceinline__ void load_vec_coh(const T* p, float* out);
+template <> __device__ __forceinline__ void load_vec_coh<float>(const float* p, float* out) {
+  float4 v = __ldca(reinterpret_cast<const float4*>(p));
+  out[0] = v.x; out[1] = v.y; out[2] = v.z; out[3] = v.w;
+}
+template <> __device__ __forceinline__ void load_vec_coh<bf16>(const bf16* p, float* out) {
+  uint4 v = __ldca(reinterpret_cast<const uint4*>(p));
+  float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z), d = unpack_bf16x2(v.w);
+  out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
+  out[4] = c.x; out[5] = c.y; out[6] = d.x; out[7] = d.y;
+}
+__device__ __forceinline__ float ld_coh(const float* p) { return __ldca(p); }
+__device__ __forceinline__ float ld_coh_any(const float* p) { return __ldca(p); }
+__device__ __forceinline__ bf16 ld_coh_any(const bf16* p) {
+  unsigned short u = __ldca(reinterpret_cast<const unsigned short*>(p));
+  return *reinterpret_cast<bf16*>(&u);
+}
 template <typename T> __device__ __forceinline__ void store_vec(T* p, const float* in);
 template <> __device__ __forceinline__ void store_vec<float>(float* p, const float* in) {
   *reinterpret_cast<float4*>(p) = make_float4(in[0], in[1], in[2], in[3]);
@@ -96,6 +149,9 @@ __device__ __forceinline__ float warp_sum(float v) {
 // ------------------------------------------------------------------------------------------
 // sm_100a PTX wrappers (device only)
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

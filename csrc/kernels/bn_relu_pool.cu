@@ -85,27 +85,29 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
+  pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  pdl_wait();
 
   float sc[V], sh[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) {
     float mean, var;
     if (training) {
-      mean = stats[c0 + j] / (float)P;
-      var = fmaxf(stats[C + c0 + j] / (float)P - mean * mean, 0.f);
+      mean = ld_coh(&stats[c0 + j]) / (float)P;
+      var = fmaxf(ld_coh(&stats[C + c0 + j]) / (float)P - mean * mean, 0.f);
     } else {
-      mean = running_mean[c0 + j];
-      var = running_var[c0 + j];
+      mean = ld_coh(&running_mean[c0 + j]);
+      var = ld_coh(&running_var[c0 + j]);
     }
     float invstd = rsqrtf(var + eps);
-    sc[j] = gamma[c0 + j] * invstd;
-    sh[j] = beta[c0 + j] - mean * sc[j];
+    sc[j] = ld_coh(&gamma[c0 + j]) * invstd;
+    sh[j] = ld_coh(&beta[c0 + j]) - mean * sc[j];
     if (training && blockIdx.x == 0 && pl == 0) {
       save_mean[c0 + j] = mean;
       save_invstd[c0 + j] = invstd;
       float unbiased = P > 1 ? var * ((float)P / (float)(P - 1)) : var;
-      running_mean[c0 + j] = (1.f - momentum) * running_mean[c0 + j] + momentum * mean;
-      running_var[c0 + j] = (1.f - momentum) * running_var[c0 + j] + momentum * unbiased;
+      running_mean[c0 + j] = (1.f - momentum) * ld_coh(&running_mean[c0 + j]) + momentum * mean;
+      running_var[c0 + j] = (1.f - momentum) * ld_coh(&running_var[c0 + j]) + momentum * unbiased;
     }
   }
   if (training && blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
@@ -120,7 +122,7 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
 #pragma unroll
     for (int q = 0; q < (POOL ? 4 : 1); ++q) {
       float v[V];
-      load_vec<T>(y + (size_t)in[q] * C + c0, v);
+      load_vec_coh<T>(y + (size_t)in[q] * C + c0, v);
 #pragma unroll
       for (int j = 0; j < V; ++j) best[j] = fmaxf(best[j], fmaf(v[j], sc[j], sh[j]));
     }
@@ -145,12 +147,14 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
+  pdl_launch_dependents();
+  pdl_wait();
   float sc[V], sh[V], mu[V], is[V], a1[V], a2[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) {
-    mu[j] = mean[c0 + j]; is[j] = invstd[c0 + j];
-    sc[j] = gamma[c0 + j] * is[j];
-    sh[j] = beta[c0 + j] - mu[j] * sc[j];
+    mu[j] = ld_coh(&mean[c0 + j]); is[j] = ld_coh(&invstd[c0 + j]);
+    sc[j] = ld_coh(&gamma[c0 + j]) * is[j];
+    sh[j] = ld_coh(&beta[c0 + j]) - mu[j] * sc[j];
     a1[j] = 0.f; a2[j] = 0.f;
   }
   if (pl < ppb) {
@@ -158,14 +162,14 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
       int in[4];
       window<POOL>(op, gm, in);
       float d[V];
-      load_vec<T>(dout + (size_t)op * C + c0, d);
+      load_vec_coh<T>(dout + (size_t)op * C + c0, d);
       float bz[V], by[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) { bz[j] = 0.f; by[j] = 0.f; }
 #pragma unroll
       for (int q = 0; q < (POOL ? 4 : 1); ++q) {
         float v[V];
-        load_vec<T>(y + (size_t)in[q] * C + c0, v);
+        load_vec_coh<T>(y + (size_t)in[q] * C + c0, v);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           float z = fmaf(v[j], sc[j], sh[j]);
@@ -203,14 +207,16 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
+  pdl_launch_dependents();
+  pdl_wait();
   float sc[V], sh[V], mu[V], is[V], k1[V], k2[V], ab[V];
   const float invP = 1.f / (float)P;
 #pragma unroll
   for (int j = 0; j < V; ++j) {
-    mu[j] = mean[c0 + j]; is[j] = invstd[c0 + j];
-    sc[j] = gamma[c0 + j] * is[j];
-    sh[j] = beta[c0 + j] - mu[j] * sc[j];
-    float s1 = sums[c0 + j], s2 = sums[C + c0 + j];
+    mu[j] = ld_coh(&mean[c0 + j]); is[j] = ld_coh(&invstd[c0 + j]);
+    sc[j] = ld_coh(&gamma[c0 + j]) * is[j];
+    sh[j] = ld_coh(&beta[c0 + j]) - mu[j] * sc[j];
+    float s1 = ld_coh(&sums[c0 + j]), s2 = ld_coh(&sums[C + c0 + j]);
     k1[j] = s1 * invP; k2[j] = s2 * invP;
     ab[j] = 0.f;
     if (blockIdx.x == 0 && pl == 0) { dbeta[c0 + j] = s1; dgamma[c0 + j] = s2; }
@@ -220,7 +226,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
       int in[4];
       window<POOL>(op, gm, in);
       float d[V];
-      load_vec<T>(dout + (size_t)op * C + c0, d);
+      load_vec_coh<T>(dout + (size_t)op * C + c0, d);
       float v[POOL ? 4 : 1][V];
       float bz[V];
       int bq[V];
@@ -228,7 +234,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
       for (int j = 0; j < V; ++j) { bz[j] = 0.f; bq[j] = -1; }
 #pragma unroll
       for (int q = 0; q < (POOL ? 4 : 1); ++q) {
-        load_vec<T>(y + (size_t)in[q] * C + c0, v[q]);
+        load_vec_coh<T>(y + (size_t)in[q] * C + c0, v[q]);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           float z = fmaf(v[q][j], sc[j], sh[j]);
@@ -349,10 +355,9 @@ int fwd_launch(const void* y, const float* stats, const float* gamma, const floa
   if (rc) return rc;
   long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
   int ppb = 256 / (C / VecOf<T>::N);
-  bn_fwd_kernel<T, POOL><<<bn_grid(bn_fwd_kernel<T, POOL>, Pout, ppb, 0), 256, 0, stream>>>(
-      (const T*)y, stats, gamma, beta, (T*)out, save_mean, save_invstd, rm, rv, nbt, P, Pout, C, H, W, eps,
-      momentum, training);
-  DDPB_LAUNCH_CHECK();
+  DDPB_CUDA_CHECK(launch_ex(bn_fwd_kernel<T, POOL>, dim3(bn_grid(bn_fwd_kernel<T, POOL>, Pout, ppb, 0)), dim3(256), 0,
+                            stream, dim3(1, 1, 1), 4, (const T*)y, stats, gamma, beta, (T*)out, save_mean,
+                            save_invstd, rm, rv, nbt, P, Pout, C, H, W, eps, momentum, training));
   return DDPB_OK;
 }
 
@@ -365,13 +370,12 @@ int bwd_launch(const void* dout, const void* y, const float* mean, const float* 
   long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
   int ppb = 256 / (C / VecOf<T>::N);
   const int smem = 256 * VecOf<T>::N * sizeof(float);      // [ppb][C] partials
-  bn_bwd_reduce_kernel<T, POOL><<<bn_grid(bn_bwd_reduce_kernel<T, POOL>, Pout, ppb, smem), 256, smem, stream>>>(
-      (const T*)dout, (const T*)y, mean, invstd, gamma, beta, sums, Pout, C, H, W);
-  DDPB_LAUNCH_CHECK();
-  bn_bwd_apply_kernel<T, POOL><<<bn_grid(bn_bwd_apply_kernel<T, POOL>, Pout, ppb, smem), 256, smem, stream>>>(
-      (const T*)dout, (const T*)y, mean, invstd, gamma, beta, sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C,
-      H, W);
-  DDPB_LAUNCH_CHECK();
+  DDPB_CUDA_CHECK(launch_ex(bn_bwd_reduce_kernel<T, POOL>, dim3(bn_grid(bn_bwd_reduce_kernel<T, POOL>, Pout, ppb, smem)),
+                            dim3(256), smem, stream, dim3(1, 1, 1), 8, (const T*)dout, (const T*)y, mean, invstd,
+                            gamma, beta, sums, Pout, C, H, W));
+  DDPB_CUDA_CHECK(launch_ex(bn_bwd_apply_kernel<T, POOL>, dim3(bn_grid(bn_bwd_apply_kernel<T, POOL>, Pout, ppb, smem)),
+                            dim3(256), smem, stream, dim3(1, 1, 1), 16, (const T*)dout, (const T*)y, mean, invstd,
+                            gamma, beta, (const float*)sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C, H, W));
   return DDPB_OK;
 }
 

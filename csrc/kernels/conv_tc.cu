@@ -93,7 +93,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<BN>(tmem_slot);
-  if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? bias[n_tile * BN + i] : 0.f;
+  // everything above is private to this CTA and overlaps the previous kernel's tail (programmatic
+  // dependent launch); global memory may only be touched after pdl_wait()
+  pdl_launch_dependents();
+  pdl_wait();
+  if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? ld_coh(&bias[n_tile * BN + i]) : 0.f;
   tc_fence_before();
   __syncthreads();
   if (NC > 1) cluster_barrier();      // every CTA's barriers exist before a peer's multicast can touch them
@@ -382,18 +386,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  if (NC == 1 && KS == 1) {
-    kern<<<grid, 192, smem, stream>>>(tmA, tmB, tmC, bias, stats, prm);
-  } else {
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = grid; cfg.blockDim = dim3(192); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-    cudaLaunchAttribute attr;
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = 1; attr.val.clusterDim.y = NC; attr.val.clusterDim.z = KS;
-    cfg.attrs = &attr; cfg.numAttrs = 1;
-    DDPB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, bias, stats, prm));
-  }
+  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, NC, KS), 1, tmA, tmB, tmC, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

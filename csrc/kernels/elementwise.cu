@@ -104,6 +104,7 @@ __global__ void nchw_to_nhwc_kernel(const TI* __restrict__ src, TO* __restrict__
 __global__ void __launch_bounds__(256)
 im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
                     bf16* __restrict__ w_pad, long long n_seg, int H, int W, int h_shift, int w_shift, int Cout) {
+  pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
   if (i < (long long)Cout * 8) {

@@ -21,7 +21,9 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
                  const int64_t* __restrict__ target, float* __restrict__ logits, float* __restrict__ dlogits,
                  float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch) {
   __shared__ float ws[NCLS * FEAT];
-  for (int i = threadIdx.x; i < NCLS * FEAT; i += blockDim.x) ws[i] = w[i];
+  pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  pdl_wait();
+  for (int i = threadIdx.x; i < NCLS * FEAT; i += blockDim.x) ws[i] = ld_coh(&w[i]);   // ld.global.cg: see load_vec_coh in common.cuh
   __syncthreads();
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int b = blockIdx.x * (blockDim.x >> 5) + warp;
@@ -31,12 +33,12 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
   for (int j = 0; j < NCLS; ++j) acc[j] = 0.f;
   const T* a = act + (size_t)b * FEAT;
   for (int k = lane; k < FEAT; k += 32) {
-    float av = to_f32(a[k]);
+    float av = to_f32(ld_coh_any(&a[k]));
 #pragma unroll
     for (int j = 0; j < NCLS; ++j) acc[j] = fmaf(av, ws[j * FEAT + k], acc[j]);
   }
 #pragma unroll
-  for (int j = 0; j < NCLS; ++j) acc[j] = warp_sum(acc[j]) + bias[j];
+  for (int j = 0; j < NCLS; ++j) acc[j] = warp_sum(acc[j]) + ld_coh(&bias[j]);
   // every lane now holds all ten logits
   float mx = acc[0];
   int arg = 0;
@@ -47,7 +49,7 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
 #pragma unroll
   for (int j = 0; j < NCLS; ++j) se += expf(acc[j] - mx);
   float lse = mx + logf(se);
-  int t = (int)target[b];
+  int t = (int)__ldca(reinterpret_cast<const long long*>(&target[b]));
   if (lane == 0) {
     float lt = 0.f;
 #pragma unroll
@@ -67,6 +69,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 fc_bwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ dlogits,
               T* __restrict__ dact, float* __restrict__ dw, float* __restrict__ db, int batch, int blocks_da) {
+  pdl_launch_dependents();     // launched normally itself (it follows the gradient memset)
   if ((int)blockIdx.x < blocks_da) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= batch * FEAT) return;
@@ -109,12 +112,13 @@ extern "C" int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias
   int blocks = ceil_div(batch, 8);
   float inv = 1.f / (float)loss_divisor;
   if (dtype == DDPB_BF16)
-    fc_ce_fwd_kernel<bf16><<<blocks, 256, 0, stream>>>((const bf16*)act, w, bias, (const int64_t*)target_i64,
-                                                      logits, dlogits, loss, correct, batch, inv);
+    DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<bf16>, dim3(blocks), dim3(256), 0, stream, dim3(1, 1, 1), 32,
+                              (const bf16*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
+                              batch, inv));
   else
-    fc_ce_fwd_kernel<float><<<blocks, 256, 0, stream>>>((const float*)act, w, bias, (const int64_t*)target_i64,
-                                                       logits, dlogits, loss, correct, batch, inv);
-  DDPB_LAUNCH_CHECK();
+    DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<float>, dim3(blocks), dim3(256), 0, stream, dim3(1, 1, 1), 32,
+                              (const float*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
+                              batch, inv));
   return DDPB_OK;
 }
 

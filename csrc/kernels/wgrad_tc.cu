@@ -73,6 +73,8 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<WG_TMEM_COLS>(tmem_slot);
+  pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  pdl_wait();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -232,7 +234,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
     configured = true;
   }
   dim3 grid(base_ctas / 3, 3, split_k);
-  kern<<<grid, 192, smem, stream>>>(tmDY, tmX, tmW, prm);
+  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmW, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -272,7 +274,7 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
     configured = true;
   }
   dim3 grid(base_ctas, 1, split_k);
-  kern<<<grid, 192, smem, stream>>>(tmDY, tmX, tmDY /* unused */, prm);
+  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmDY /* unused */, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -21,6 +22,24 @@ void set_last_error(const char* fmt, ...) {
 }
 
 const char* last_error() { return g_last_error; }
+
+// programmatic dependent launch switch: environment DDPB_PDL (default on), overridable at run time
+static int g_pdl = -1;
+bool pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("DDPB_PDL");
+    g_pdl = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl == 1;
+}
+int pdl_mask() {
+  static int m = -2;
+  if (m == -2) {
+    const char* e = getenv("DDPB_PDL_MASK");
+    m = e ? atoi(e) : -1;
+  }
+  return m;
+}
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -99,3 +118,10 @@ int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, long long rows, long lon
 }  // namespace ddpb
 
 extern "C" const char* ddpb_last_error() { return ddpb::last_error(); }
+
+// 1 / 0 = allow / forbid programmatic dependent launches from now on; returns the previous setting.
+extern "C" int ddpb_set_pdl(int on) {
+  const int prev = ddpb::pdl_enabled() ? 1 : 0;
+  ddpb::g_pdl = on ? 1 : 0;
+  return prev;
+}

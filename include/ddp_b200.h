@@ -143,7 +143,7 @@ int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw, int B, in
 
 /* Diagnostic (csrc/kernels/tma_probe.cu, tools/tma_probe.py): per-CTA L2 -> shared-memory ingest rate of
  * the conv load patterns.  No reference counterpart. */
-int ddpb_probe_tma(int mode, int stages, int iters, int ctas, int smem_pad_kb, const void* act, const void* wgt,
+int ddpb_probe_tma(int mode, int stages, int iters, int ctas, int smem_pad_kb, int cols, const void* act, const void* wgt,
                    const void* flat, long long flat_bytes, cudaStream_t stream);
 
 /* ---- peer-to-peer gradient engine (csrc/kernels/sync_p2p.cu, csrc/runtime/symm_mem.cpp) --- */
