@@ -55,17 +55,23 @@ def channel_stats(y: torch.Tensor, stats: Optional[torch.Tensor] = None) -> torc
 
 def bn_relu_pool_fwd(y: torch.Tensor, stats: Optional[torch.Tensor], gamma, beta, running_mean, running_var,
                      nbt: Optional[torch.Tensor], pool: bool, training: bool = True,
-                     out: Optional[torch.Tensor] = None):
+                     out: Optional[torch.Tensor] = None, want_winner: bool = False):
+    """Returns (out, save_mean, save_invstd) and, with ``want_winner``, the tensor of window winners
+    (the conv output that won each ReLU + pool window, NaN where ReLU blocked it)."""
     b, h, w, c = y.shape
     oh, ow = (h // 2, w // 2) if pool else (h, w)
     if out is None:
         out = torch.empty((b, oh, ow, c), dtype=y.dtype, device=y.device)
     save_mean = torch.empty(c, dtype=torch.float32, device=y.device)
     save_invstd = torch.empty(c, dtype=torch.float32, device=y.device)
-    check(lib().ddpb_bn_relu_pool_fwd(ptr(y), ptr(stats), ptr(gamma), ptr(beta), ptr(out), ptr(save_mean),
-                                      ptr(save_invstd), ptr(running_mean), ptr(running_var), ptr(nbt), b, h, w,
-                                      c, int(pool), int(training), cf(BN_EPS), cf(BN_MOMENTUM),
-                                      dtype_code(y.dtype), stream_handle()), "bn_relu_pool_fwd")
+    winner = torch.empty_like(out) if want_winner else None
+    check(lib().ddpb_bn_relu_pool_fwd_winner(ptr(y), ptr(stats), ptr(gamma), ptr(beta), ptr(out), ptr(save_mean),
+                                             ptr(save_invstd), ptr(running_mean), ptr(running_var), ptr(nbt),
+                                             ptr(winner), b, h, w, c, int(pool), int(training), cf(BN_EPS),
+                                             cf(BN_MOMENTUM), dtype_code(y.dtype), stream_handle()),
+          "bn_relu_pool_fwd")
+    if want_winner:
+        return out, save_mean, save_invstd, winner
     return out, save_mean, save_invstd
 
 
@@ -79,6 +85,20 @@ def bn_relu_pool_bwd(dout: torch.Tensor, y: torch.Tensor, save_mean, save_invstd
     check(lib().ddpb_bn_relu_pool_bwd(ptr(dout), ptr(y), ptr(save_mean), ptr(save_invstd), ptr(gamma), ptr(beta),
                                       ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), ptr(dbias), b, h, w, c,
                                       int(pool), dtype_code(y.dtype), stream_handle()), "bn_relu_pool_bwd")
+    return dy, dgamma, dbeta
+
+
+def bn_relu_pool_bwd_apply(dout: torch.Tensor, y: torch.Tensor, save_mean, save_invstd, gamma, beta, sums, pool: bool,
+                           dbias: Optional[torch.Tensor] = None):
+    """Second BN-backward pass only; ``sums`` comes from ``conv_dgrad_bnred_tc``."""
+    b, h, w, c = y.shape
+    dy = torch.empty_like(y)
+    dgamma = torch.empty(c, dtype=torch.float32, device=y.device)
+    dbeta = torch.empty(c, dtype=torch.float32, device=y.device)
+    check(lib().ddpb_bn_relu_pool_bwd_apply(ptr(dout), ptr(y), ptr(save_mean), ptr(save_invstd), ptr(gamma),
+                                            ptr(beta), ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), ptr(dbias), b, h,
+                                            w, c, int(pool), dtype_code(y.dtype), stream_handle()),
+          "bn_relu_pool_bwd_apply")
     return dy, dgamma, dbeta
 
 
@@ -168,6 +188,21 @@ def conv_dgrad_tc(dy, w_bf16, tile_n: int = 0):
     check(lib().ddpb_conv3x3_dgrad_tc(ptr(dy), ptr(w_bf16), ptr(dx), b, h, w_, cin, cout, tile_n,
                                       stream_handle()), "conv_dgrad_tc")
     return dx
+
+
+def conv_dgrad_bnred_tc(dy, w_bf16, y_win, save_mean, save_invstd, gamma, beta, tile_n: int = 0):
+    """dgrad whose epilogue also reduces the previous block's BN backward sums.  ``y_win``: the previous
+    block's window winners (``bn_relu_pool_fwd(..., want_winner=True)``), or its conv output when it
+    does not pool.  Returns (dx, sums[2*Cin])."""
+    b, h, w_, cout = dy.shape
+    cin = w_bf16.shape[3]
+    assert tuple(y_win.shape) == (b, h, w_, cin)
+    dx = torch.empty((b, h, w_, cin), dtype=torch.bfloat16, device=dy.device)
+    sums = torch.zeros(2 * cin, dtype=torch.float32, device=dy.device)
+    check(lib().ddpb_conv3x3_dgrad_bnred_tc(ptr(dy), ptr(w_bf16), ptr(dx), b, h, w_, cin, cout, tile_n, ptr(y_win),
+                                            ptr(save_mean), ptr(save_invstd), ptr(gamma), ptr(beta), ptr(sums),
+                                            stream_handle()), "conv_dgrad_bnred_tc")
+    return dx, sums
 
 
 def conv_wgrad_tc(dy, x, split_k: int = 0, out: Optional[torch.Tensor] = None):

@@ -43,7 +43,8 @@ static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) 
 
 // Programmatic dependent launch: a kernel launched through launch_ex(..., pdl = true) may be scheduled
 // while its predecessor on the stream is still running, so its prologue (barrier init, TMEM
-// allocation, descriptor prefetch, index math) and the launch latency overlap the predecessor's tail.
+// allocation, descriptor prefetch, index math) and the launch latency overlap the predecessor's tail
+// (applied while a CUDA graph is being captured only, see launch_ex).
 // Such a kernel MUST execute pdl_wait() before its first access to global memory; every kernel calls
 // pdl_launch_dependents() early so that ITS successor can be scheduled.  DDPB_PDL=0 disables it.
 bool pdl_enabled();
@@ -62,7 +63,13 @@ static inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 bloc
     attr[n].val.clusterDim.x = cluster.x; attr[n].val.clusterDim.y = cluster.y; attr[n].val.clusterDim.z = cluster.z;
     ++n;
   }
-  if (pdl && pdl_enabled() && (pdl_mask() & pdl)) {
+  // Only inside a stream capture: there every dependency (events between the engine's streams included)
+  // becomes an explicit graph edge.  In plain stream order, mixing programmatic launches with the
+  // event waits of the three-stream backward gave slightly wrong gradients (measured), so eager runs
+  // keep ordinary launches.
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (pdl && pdl_enabled() && (pdl_mask() & pdl) && cudaStreamIsCapturing(stream, &cap) == cudaSuccess &&
+      cap == cudaStreamCaptureStatusActive) {
     attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[n].val.programmaticStreamSerializationAllowed = 1;
     ++n;

@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(256)
 bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const float* __restrict__ gamma,
               const float* __restrict__ beta, T* __restrict__ out, float* __restrict__ save_mean,
               float* __restrict__ save_invstd, float* __restrict__ running_mean,
-              float* __restrict__ running_var, long long* __restrict__ nbt, long long P, long long Pout,
-              int C, int H, int W, float eps, float momentum, int training) {
+              float* __restrict__ running_var, long long* __restrict__ nbt, T* __restrict__ winner,
+              long long P, long long Pout, int C, int H, int W, float eps, float momentum, int training) {
   constexpr int V = VecOf<T>::N;
   const int groups = C / V;
   const int g = threadIdx.x % groups;
@@ -116,17 +116,23 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   for (int op = blockIdx.x * ppb + pl; op < (int)Pout; op += gridDim.x * ppb) {
     int in[4];
     window<POOL>(op, gm, in);
-    float best[V];
+    float best[V], by[V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) best[j] = 0.f;          // ReLU floor
+    for (int j = 0; j < V; ++j) { best[j] = 0.f; by[j] = __int_as_float(0x7fc00000); }   // ReLU floor; NaN = "no winner"
 #pragma unroll
     for (int q = 0; q < (POOL ? 4 : 1); ++q) {
       float v[V];
       load_vec_coh<T>(y + (size_t)in[q] * C + c0, v);
 #pragma unroll
-      for (int j = 0; j < V; ++j) best[j] = fmaxf(best[j], fmaf(v[j], sc[j], sh[j]));
+      for (int j = 0; j < V; ++j) {
+        const float z = fmaf(v[j], sc[j], sh[j]);
+        if (z > best[j]) { best[j] = z; by[j] = v[j]; }      // strict >: the first maximum wins, like the backward pass
+      }
     }
     store_vec<T>(out + (size_t)op * C + c0, best);
+    // the conv output that won the window (NaN when ReLU blocked all of them): lets the next layer's
+    // dgrad epilogue do this block's BN-backward reduction from one value per output pixel
+    if (winner) store_vec<T>(winner + (size_t)op * C + c0, by);
   }
 }
 
@@ -349,30 +355,31 @@ namespace {
 
 template <typename T, bool POOL>
 int fwd_launch(const void* y, const float* stats, const float* gamma, const float* beta, void* out,
-               float* save_mean, float* save_invstd, float* rm, float* rv, long long* nbt, int batch, int H,
-               int W, int C, int training, float eps, float momentum, cudaStream_t stream) {
+               float* save_mean, float* save_invstd, float* rm, float* rv, long long* nbt, void* winner, int batch,
+               int H, int W, int C, int training, float eps, float momentum, cudaStream_t stream) {
   int rc = bn_check<T>(C, H, W, POOL);
   if (rc) return rc;
   long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
   int ppb = 256 / (C / VecOf<T>::N);
   DDPB_CUDA_CHECK(launch_ex(bn_fwd_kernel<T, POOL>, dim3(bn_grid(bn_fwd_kernel<T, POOL>, Pout, ppb, 0)), dim3(256), 0,
                             stream, dim3(1, 1, 1), 4, (const T*)y, stats, gamma, beta, (T*)out, save_mean,
-                            save_invstd, rm, rv, nbt, P, Pout, C, H, W, eps, momentum, training));
+                            save_invstd, rm, rv, nbt, (T*)winner, P, Pout, C, H, W, eps, momentum, training));
   return DDPB_OK;
 }
 
 template <typename T, bool POOL>
 int bwd_launch(const void* dout, const void* y, const float* mean, const float* invstd, const float* gamma,
                const float* beta, float* sums, void* dy, float* dgamma, float* dbeta, float* dbias, int batch,
-               int H, int W, int C, cudaStream_t stream) {
+               int H, int W, int C, cudaStream_t stream, bool reduce = true) {
   int rc = bn_check<T>(C, H, W, POOL);
   if (rc) return rc;
   long long P = (long long)batch * H * W, Pout = POOL ? P / 4 : P;
   int ppb = 256 / (C / VecOf<T>::N);
   const int smem = 256 * VecOf<T>::N * sizeof(float);      // [ppb][C] partials
-  DDPB_CUDA_CHECK(launch_ex(bn_bwd_reduce_kernel<T, POOL>, dim3(bn_grid(bn_bwd_reduce_kernel<T, POOL>, Pout, ppb, smem)),
-                            dim3(256), smem, stream, dim3(1, 1, 1), 8, (const T*)dout, (const T*)y, mean, invstd,
-                            gamma, beta, sums, Pout, C, H, W));
+  if (reduce)
+    DDPB_CUDA_CHECK(launch_ex(bn_bwd_reduce_kernel<T, POOL>, dim3(bn_grid(bn_bwd_reduce_kernel<T, POOL>, Pout, ppb, smem)),
+                              dim3(256), smem, stream, dim3(1, 1, 1), 8, (const T*)dout, (const T*)y, mean, invstd,
+                              gamma, beta, sums, Pout, C, H, W));
   DDPB_CUDA_CHECK(launch_ex(bn_bwd_apply_kernel<T, POOL>, dim3(bn_grid(bn_bwd_apply_kernel<T, POOL>, Pout, ppb, smem)),
                             dim3(256), smem, stream, dim3(1, 1, 1), 16, (const T*)dout, (const T*)y, mean, invstd,
                             gamma, beta, (const float*)sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C, H, W));
@@ -381,16 +388,28 @@ int bwd_launch(const void* dout, const void* y, const float* mean, const float* 
 
 }  // namespace
 
+// winner (may be null; same shape and dtype as `out`): for every output element the conv output y that
+// won the ReLU + max-pool window, NaN where ReLU blocked the whole window (see ddpb_conv3x3_dgrad_bnred_tc).
+extern "C" int ddpb_bn_relu_pool_fwd_winner(const void* y, const float* stats, const float* gamma, const float* beta,
+                                            void* out, float* save_mean, float* save_invstd, float* running_mean,
+                                            float* running_var, long long* num_batches_tracked, void* winner,
+                                            int batch, int H, int W, int C, int pool, int training, float eps,
+                                            float momentum, int dtype, cudaStream_t stream) {
+#define ARGS y, stats, gamma, beta, out, save_mean, save_invstd, running_mean, running_var, \
+             num_batches_tracked, winner, batch, H, W, C, training, eps, momentum, stream
+  if (dtype == DDPB_BF16) return pool ? fwd_launch<bf16, true>(ARGS) : fwd_launch<bf16, false>(ARGS);
+  return pool ? fwd_launch<float, true>(ARGS) : fwd_launch<float, false>(ARGS);
+#undef ARGS
+}
+
 extern "C" int ddpb_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma, const float* beta,
                                      void* out, float* save_mean, float* save_invstd, float* running_mean,
                                      float* running_var, long long* num_batches_tracked, int batch, int H,
                                      int W, int C, int pool, int training, float eps, float momentum,
                                      int dtype, cudaStream_t stream) {
-#define ARGS y, stats, gamma, beta, out, save_mean, save_invstd, running_mean, running_var, \
-             num_batches_tracked, batch, H, W, C, training, eps, momentum, stream
-  if (dtype == DDPB_BF16) return pool ? fwd_launch<bf16, true>(ARGS) : fwd_launch<bf16, false>(ARGS);
-  return pool ? fwd_launch<float, true>(ARGS) : fwd_launch<float, false>(ARGS);
-#undef ARGS
+  return ddpb_bn_relu_pool_fwd_winner(y, stats, gamma, beta, out, save_mean, save_invstd, running_mean, running_var,
+                                      num_batches_tracked, nullptr, batch, H, W, C, pool, training, eps, momentum,
+                                      dtype, stream);
 }
 
 // `sums` is a zeroed [2*C] scratch; dgamma/dbeta are overwritten, dbias (may be null) accumulated.
@@ -400,6 +419,19 @@ extern "C" int ddpb_bn_relu_pool_bwd(const void* dout, const void* y, const floa
                                      int batch, int H, int W, int C, int pool, int dtype,
                                      cudaStream_t stream) {
 #define ARGS dout, y, save_mean, save_invstd, gamma, beta, sums, dy, dgamma, dbeta, dbias, batch, H, W, C, stream
+  if (dtype == DDPB_BF16) return pool ? bwd_launch<bf16, true>(ARGS) : bwd_launch<bf16, false>(ARGS);
+  return pool ? bwd_launch<float, true>(ARGS) : bwd_launch<float, false>(ARGS);
+#undef ARGS
+}
+
+// Second pass only: `sums` already holds sum dz and sum dz * xhat (produced by the epilogue of the
+// following layer's data-gradient kernel, ddpb_conv3x3_dgrad_bnred_tc).
+extern "C" int ddpb_bn_relu_pool_bwd_apply(const void* dout, const void* y, const float* save_mean,
+                                           const float* save_invstd, const float* gamma, const float* beta,
+                                           float* sums, void* dy, float* dgamma, float* dbeta, float* dbias,
+                                           int batch, int H, int W, int C, int pool, int dtype,
+                                           cudaStream_t stream) {
+#define ARGS dout, y, save_mean, save_invstd, gamma, beta, sums, dy, dgamma, dbeta, dbias, batch, H, W, C, stream, false
   if (dtype == DDPB_BF16) return pool ? bwd_launch<bf16, true>(ARGS) : bwd_launch<bf16, false>(ARGS);
   return pool ? bwd_launch<float, true>(ARGS) : bwd_launch<float, false>(ARGS);
 #undef ARGS

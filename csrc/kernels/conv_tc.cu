@@ -43,8 +43,25 @@ struct ConvTcParams {
   int slice_dim;           // NC > 1: tensor dimension (2 = h, 3 = n) along which the A box is cut into NC slices
   int slice_extent;        // NC > 1: extent of one slice along slice_dim
   int taps;                // 9 = 3x3 filter, 1 = 1x1 (plain GEMM over the pixel rows; first-layer patch matrix)
-  bf16* out_raw;           // KS > 1: output matrix [total_pixels][n_out] (written with plain stores)
+  bf16* out_raw;           // output matrix [total_pixels][n_out]
+  int w_shift, h_shift;    // log2(W), log2(H)
+  // dgrad only: BatchNorm-backward reduction of the previous block, fused into the epilogue (bn_y == null: off).
+  // bn_y: per output pixel and channel, the previous block's conv output that won its ReLU / pool window
+  // (NaN = blocked), [total_pixels][n_out].
+  const bf16* bn_y;
+  const float *bn_mean, *bn_invstd, *bn_gamma, *bn_beta;
+  float* bn_sums;          // [2 * n_out], accumulated
 };
+
+// XOR swizzle of the 16-byte chunks of the epilogue's bf16 tile ([128 rows][CH chunks]): both the
+// row-per-thread writes and the chunk-per-thread reads then spread over all shared-memory banks.
+template <int CH>
+__device__ __forceinline__ int tile_swizzle(int row) {
+  if (CH >= 8) return row & 7;
+  if (CH == 4) return (row >> 1) & 3;
+  if (CH == 2) return (row >> 2) & 1;
+  return 0;
+}
 
 // NC > 1: the NC CTAs of a cluster (consecutive n-tiles, same pixel tile) need the SAME activation
 // tile.  Each loads 1/NC of it and multicasts that slice into all NC shared memories, so the tile is
@@ -58,8 +75,7 @@ struct ConvTcParams {
 template <int BN, int STAGES, bool DGRAD, int NC, int KS>
 __global__ void __launch_bounds__(192)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias,
-                  float* __restrict__ stats, const ConvTcParams prm) {
+                  const float* __restrict__ bias, float* __restrict__ stats, const ConvTcParams prm) {
   constexpr int B_BYTES = BN * KCHUNK * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
@@ -86,7 +102,6 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    tma_prefetch_desc(&tmC);
     // a stage is written by all NC CTAs (multicast slices), so it is free only when all NC have consumed it
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], NC); }
     mbar_init(accum_bar, 1);
@@ -104,6 +119,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint16_t MC_MASK = (uint16_t)((1u << NC) - 1);
+  uint4 ywin[BN / KS / 8];               // dgrad + fused BN reduction only (epilogue warps)
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -164,88 +180,42 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       umma_commit(accum_bar);                  // accumulator complete
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
-    // 1. TMEM -> registers -> (+bias) -> bf16 -> shared memory, in the 128B-swizzled layout a TMA
-    //    store expects (the pipeline stages are free once the accumulator barrier has fired).
-    // 2. one thread stores the tile with TMA (coalesced, clipped at the tensor edge, asynchronous).
-    // 3. fprop: per-channel sum / sum-of-squares of the ROUNDED tile, read back from shared memory
-    //    (8-byte column-group loads; no shuffles, no shared-memory atomics).
-    const int q = warp & 3;                    // TMEM lane quarter this warp may access
-    const int row = q * 32 + lane;             // pixel row inside the tile
-    const int t = threadIdx.x - 64;            // 0..127 among the epilogue threads
-    uint8_t* tile = smem;                      // [BN/64][128 rows][128 B]
-    float* red = reinterpret_cast<float*>(smem + 32768);      // [parts][2*BN]
+    // ===================== epilogue warps (2..5) =====================
+    // dgrad with fused BN-backward reduction: fetch this thread's share of the previous block's
+    // "winner" tensor now, so the loads are long complete when the accumulator is
+    if (DGRAD && prm.bn_y != nullptr) {
+      const int t2 = threadIdx.x - 64;
+      const int col = n_tile * BN + ks_rank * (BN / KS) + (t2 % (BN / KS / 8)) * 8;
+#pragma unroll
+      for (int k = 0; k < BN / KS / 8; ++k) {
+        const long long grow = (long long)m_tile * TILE_M + t2 / (BN / KS / 8) + k * (128 / (BN / KS / 8));
+        ywin[k] = grow < prm.total_pixels
+                      ? __ldca(reinterpret_cast<const uint4*>(prm.bn_y + grow * prm.n_out + col))
+                      : make_uint4(0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u);
+      }
+    }
     mbar_wait(accum_bar, 0);
     tc_fence_after();
-    if constexpr (KS == 1) {
-#pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
-      float v[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c, v);
-      tmem_ld_wait();
-      if (!DGRAD) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] += bias_s[c + j];
-      }
-      uint8_t* rbase = tile + (c >> 6) * (TILE_M * 128) + row * 128;
-      const int j0 = (c & 63) >> 3;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint4 pk = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                              pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
-        *reinterpret_cast<uint4*>(rbase + (((j0 + j) ^ (row & 7)) << 4)) = pk;
-      }
-    }
-    fence_async_proxy();                                       // generic-proxy writes -> visible to TMA
-    asm volatile("bar.sync 1, 128;" ::: "memory");             // the four epilogue warps only
-    if (t == 0) {
-#pragma unroll
-      for (int hblk = 0; hblk < BN / 64; ++hblk)
-        tma_store_2d(&tmC, tile + hblk * (TILE_M * 128), n_tile * BN + hblk * 64, m_tile * TILE_M);
-      tma_store_commit();
-    }
-    if (!DGRAD && stats) {
-      constexpr int GROUPS = BN / 4, PARTS = 128 / GROUPS, ROWS = TILE_M / PARTS;
-      const int g = t % GROUPS, part = t / GROUPS;
-      const long long left = prm.total_pixels - (long long)m_tile * TILE_M;
-      const int valid_rows = left < TILE_M ? (int)left : TILE_M;
-      const uint8_t* cbase = tile + ((4 * g) >> 6) * (TILE_M * 128);
-      const int jc = ((4 * g) & 63) >> 3, inner = ((4 * g) & 7) * 2;
-      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
-      const int r_end = min(valid_rows, (part + 1) * ROWS);
-#pragma unroll 4
-      for (int r = part * ROWS; r < r_end; ++r) {
-        const uint2 u = *reinterpret_cast<const uint2*>(cbase + r * 128 + ((jc ^ (r & 7)) << 4) + inner);
-        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
-        s1[0] += a.x; s1[1] += a.y; s1[2] += b.x; s1[3] += b.y;
-        s2[0] = fmaf(a.x, a.x, s2[0]); s2[1] = fmaf(a.y, a.y, s2[1]);
-        s2[2] = fmaf(b.x, b.x, s2[2]); s2[3] = fmaf(b.y, b.y, s2[3]);
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        red[part * 2 * BN + 4 * g + j] = s1[j];
-        red[part * 2 * BN + BN + 4 * g + j] = s2[j];
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      for (int i = t; i < 2 * BN; i += 128) {
-        float acc = 0.f;
-#pragma unroll
-        for (int pz = 0; pz < PARTS; ++pz) acc += red[pz * 2 * BN + i];
-        const int col = i < BN ? i : i - BN;
-        atomicAdd(&stats[(i < BN ? 0 : prm.n_out) + n_tile * BN + col], acc);
-      }
-    }
-    if (t == 0) tma_store_wait_read();        // shared memory must stay valid until TMA has read it
-    }  // KS == 1
   }
+  // Epilogue, common to all variants.  This CTA finishes CW = BN / KS columns of the 128-row tile:
+  //   0. (KS > 1) reduce-scatter of the fp32 partial tiles through distributed shared memory
+  //   1. TMEM (+ partials) (+ bias) -> bf16 -> shared-memory tile (16-byte chunks, XOR-swizzled)
+  //   2. re-mapped threads (CH consecutive threads = one row) store the tile with coalesced 16-byte
+  //      stores and, from the same ROUNDED values, accumulate per-channel sums in registers:
+  //        fprop: BatchNorm statistics (sum, sum of squares) of this layer
+  //        dgrad: the BatchNorm-backward reduction of the PREVIOUS layer (sum dz, sum dz * xhat),
+  //               which would otherwise be a kernel of its own on the critical path
+  //   3. cross-thread reduction through shared memory, one atomicAdd per channel and CTA
+  constexpr int CW = BN / KS;                 // columns this CTA finishes
+  constexpr int CH = CW / 8;                  // 16-byte chunks per tile row
+  constexpr int PARTS = 128 / CH;             // row groups in step 2
+  constexpr int RP = 128;                     // receive buffer: [sender][column][row] fp32 (column-major: conflict-free)
+  float* recv = reinterpret_cast<float*>(smem);
+  uint8_t* tile = smem + (KS - 1) * CW * RP * 4;                        // [128 rows][CW] bf16
+  float* red = reinterpret_cast<float*>(tile + TILE_M * CW * 2);         // [PARTS][2 * CW]
+  const int q = warp & 3, row = q * 32 + lane, t = threadIdx.x - 64;
+  const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
   if constexpr (KS > 1) {
-    constexpr int CW = BN / KS;                 // columns this CTA finishes
-    constexpr int RP = 128;                     // receive buffer: [sender][column][row] fp32 (column-major: conflict-free)
-    float* recv = reinterpret_cast<float*>(smem);
-    float* colbuf = recv + (KS - 1) * CW * RP;  // [CW][129] rounded outputs for the BN statistics
-    float* red = colbuf + CW * 129;             // [128 / CW][2 * CW]
-    const int q = warp & 3, row = q * 32 + lane, t = threadIdx.x - 64;
-    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
     __syncwarp();
     // #0: every CTA's accumulator is complete, i.e. every CTA's pipeline stages are free to be overwritten
     cluster_barrier();
@@ -267,60 +237,87 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     __syncwarp();
     cluster_barrier();                          // #1: all partial column blocks have been delivered
-    if (warp >= 2) {
-      const long long grow = (long long)m_tile * TILE_M + row;
-      const bool valid = grow < prm.total_pixels;
-      bf16* orow = prm.out_raw + grow * prm.n_out + n_tile * BN + ks_rank * CW;
-      const bool want_stats = !DGRAD && stats != nullptr;
+  }
+  if (warp >= 2) {
+    // ---- 1. accumulator -> bf16 tile in shared memory
 #pragma unroll 1
-      for (int c = 0; c < CW; c += 16) {
-        float v[16];
-        tmem_ld_32x32_x16(lane_base + ks_rank * CW + c, v);
-        tmem_ld_wait();
+    for (int c = 0; c < CW; c += 16) {
+      float v[16];
+      tmem_ld_32x32_x16(lane_base + ks_rank * CW + c, v);
+      tmem_ld_wait();
 #pragma unroll
-        for (int sl = 0; sl < KS - 1; ++sl)
+      for (int sl = 0; sl < KS - 1; ++sl)
 #pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] += recv[(sl * CW + c + j) * RP + row];
-        if (!DGRAD) {
+        for (int j = 0; j < 16; ++j) v[j] += recv[(sl * CW + c + j) * RP + row];
+      if (!DGRAD) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] += bias_s[ks_rank * CW + c + j];
-        }
-        uint32_t pk[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-        if (valid) {
-          reinterpret_cast<uint4*>(orow + c)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-          reinterpret_cast<uint4*>(orow + c)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-        }
-        if (want_stats) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float2 f = unpack_bf16x2(pk[j]);      // statistics of the ROUNDED tile, like KS == 1
-            colbuf[(c + 2 * j) * 129 + row] = valid ? f.x : 0.f;
-            colbuf[(c + 2 * j + 1) * 129 + row] = valid ? f.y : 0.f;
-          }
-        }
+        for (int j = 0; j < 16; ++j) v[j] += bias_s[ks_rank * CW + c + j];
       }
-      if (want_stats) {
-        constexpr int PARTS = 128 / CW;           // each part sums CW rows of one column
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        const int col = t % CW, part = t / CW;
-        float s1 = 0.f, s2 = 0.f;
-#pragma unroll 8
-        for (int r = part * CW; r < (part + 1) * CW; ++r) {
-          const float f = colbuf[col * 129 + r];
-          s1 += f; s2 = fmaf(f, f, s2);
-        }
-        red[part * 2 * CW + col] = s1;
-        red[part * 2 * CW + CW + col] = s2;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (t < 2 * CW) {
-          float acc = 0.f;
+      uint8_t* rbase = tile + row * (CW * 2);
+      const int j0 = c >> 3, sw = tile_swizzle<CH>(row);
+      *reinterpret_cast<uint4*>(rbase + ((j0 ^ sw) << 4)) =
+          make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+      *reinterpret_cast<uint4*>(rbase + (((j0 + 1) ^ sw) << 4)) =
+          make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");             // the four epilogue warps only
+    // ---- 2. coalesced store + per-channel sums
+    const int ch = t % CH, part = t / CH;
+    const int col0 = n_tile * BN + ks_rank * CW + ch * 8;      // first of this thread's 8 output channels
+    const long long row0 = (long long)m_tile * TILE_M;
+    const bool want_stats = !DGRAD && stats != nullptr;
+    const bool bn_red = DGRAD && prm.bn_y != nullptr;
+    float s1[8], s2[8], sc[8], sh[8], mu[8], is[8];
 #pragma unroll
-          for (int pz = 0; pz < PARTS; ++pz) acc += red[pz * 2 * CW + t];
-          const int cc = t < CW ? t : t - CW;
-          atomicAdd(&stats[(t < CW ? 0 : prm.n_out) + n_tile * BN + ks_rank * CW + cc], acc);
-        }
+    for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; sc[j] = 0.f; sh[j] = 0.f; mu[j] = 0.f; is[j] = 0.f; }
+    if (bn_red) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        mu[j] = ld_coh(&prm.bn_mean[col0 + j]); is[j] = ld_coh(&prm.bn_invstd[col0 + j]);
+        sc[j] = ld_coh(&prm.bn_gamma[col0 + j]) * is[j];
+        sh[j] = ld_coh(&prm.bn_beta[col0 + j]) - mu[j] * sc[j];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < CH; ++k) {
+      const int r = part + k * PARTS;
+      const long long grow = row0 + r;
+      if (grow >= prm.total_pixels) break;
+      const uint4 u = *reinterpret_cast<const uint4*>(tile + r * (CW * 2) + ((ch ^ tile_swizzle<CH>(r)) << 4));
+      *reinterpret_cast<uint4*>(prm.out_raw + grow * prm.n_out + col0) = u;
+      float d[8];
+      { const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c2 = unpack_bf16x2(u.z), e = unpack_bf16x2(u.w);
+        d[0] = a.x; d[1] = a.y; d[2] = b.x; d[3] = b.y; d[4] = c2.x; d[5] = c2.y; d[6] = e.x; d[7] = e.y; }
+      if (want_stats) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s1[j] += d[j]; s2[j] = fmaf(d[j], d[j], s2[j]); }
+      }
+      if (bn_red) {
+        // yw: the previous block's conv output behind this pixel (NaN: ReLU blocked it -> z > 0 is false)
+        float v[8];
+        { const uint4 w4 = ywin[k];
+          const float2 a = unpack_bf16x2(w4.x), b = unpack_bf16x2(w4.y), c2 = unpack_bf16x2(w4.z), e = unpack_bf16x2(w4.w);
+          v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c2.x; v[5] = c2.y; v[6] = e.x; v[7] = e.y; }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (fmaf(v[j], sc[j], sh[j]) > 0.f) { s1[j] += d[j]; s2[j] = fmaf(d[j], (v[j] - mu[j]) * is[j], s2[j]); }
+      }
+    }
+    // ---- 3. per-channel totals of the CTA
+    if (want_stats || bn_red) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        red[part * 2 * CW + ch * 8 + j] = s1[j];
+        red[part * 2 * CW + CW + ch * 8 + j] = s2[j];
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      float* acc_out = want_stats ? stats : prm.bn_sums;
+      for (int i = t; i < 2 * CW; i += 128) {
+        float acc = 0.f;
+#pragma unroll 4
+        for (int pz = 0; pz < PARTS; ++pz) acc += red[pz * 2 * CW + i];
+        const int cc = i < CW ? i : i - CW;
+        atomicAdd(&acc_out[(i < CW ? 0 : prm.n_out) + n_tile * BN + ks_rank * CW + cc], acc);
       }
     }
   }
@@ -339,6 +336,15 @@ void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn) {
   else { *bw = W; *bh = H; *bn = pixels / (H * W); }
 }
 
+// Arguments of the fused BatchNorm-backward reduction (set by ddpb_conv3x3_dgrad_bnred_tc around its
+// dispatch; a thread-local instead of one more parameter through every tile variant's call).
+struct BnRedArgs {
+  const void* y = nullptr;
+  const float *mean = nullptr, *invstd = nullptr, *gamma = nullptr, *beta = nullptr;
+  float* sums = nullptr;
+};
+static thread_local BnRedArgs g_bnred;
+
 template <int BN, int STAGES, bool DGRAD, int NC = 1, int KS = 1>
 static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, float* stats, int B, int H, int W,
                   int Cin, int Cout, cudaStream_t stream, int taps = 9) {
@@ -355,11 +361,8 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     else DDPB_REQUIRE(false, "conv_tc: cannot cut a %dx%dx%d pixel box into %d multicast slices", bw, bh, bn, NC);
     DDPB_REQUIRE((Nc / BN) % NC == 0, "conv_tc: %d channel tiles are not a multiple of the cluster size %d", Nc / BN, NC);
   }
-  CUtensorMap tmA, tmB, tmC;
+  CUtensorMap tmA, tmB;
   int rc = make_tmap_nhwc_bf16(&tmA, in, B, H, W, Kc, KCHUNK, bw, sbh, sbn);
-  if (rc) return rc;
-  // output matrix [pixels][Nc]; the epilogue stores 64-column x 128-row boxes (clipped at the edge)
-  rc = make_tmap_2d_bf16(&tmC, out, (long long)B * H * W, Nc, 64, TILE_M);
   if (rc) return rc;
   // weight matrix [Cout rows][9*Cin cols]; fprop box = 64 cols x BN rows, dgrad box = 64 cols x 64 rows
   rc = make_tmap_2d_bf16(&tmB, w, Cout, (long long)taps * Cin, KCHUNK, DGRAD ? 64 : BN);
@@ -374,9 +377,17 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   prm.k_total_cols = Cin;
   prm.taps = taps;
   prm.out_raw = out;
+  prm.w_shift = 0; prm.h_shift = 0;
+  while ((1 << prm.w_shift) < W) ++prm.w_shift;
+  while ((1 << prm.h_shift) < H) ++prm.h_shift;
+  // fused BatchNorm-backward reduction requested by ddpb_conv3x3_dgrad_bnred_tc (dgrad only)
+  const BnRedArgs& br = g_bnred;
+  prm.bn_y = DGRAD ? (const bf16*)br.y : nullptr;
+  prm.bn_mean = br.mean; prm.bn_invstd = br.invstd; prm.bn_gamma = br.gamma; prm.bn_beta = br.beta;
+  prm.bn_sums = br.sums;
   static_assert(KS == 1 || NC == 1, "split-K and multicast clusters are separate variants");
-  static_assert(KS == 1 || ((KS - 1) * (BN / KS) * 128 + (BN / KS) * 129 + 256) * 4 <= STAGES * (A_BYTES + BN * KCHUNK * 2),
-                "split-K receive buffers must fit in the pipeline stages");
+  static_assert((KS - 1) * (BN / KS) * 128 * 4 + TILE_M * (BN / KS) * 2 + TILE_M * 2 * 8 * 4 <= STAGES * (A_BYTES + BN * KCHUNK * 2),
+                "epilogue buffers (split-K receive area, bf16 tile, partial sums) must fit in the pipeline stages");
   int m_tiles = prm.tiles_per_img > 0 ? B * prm.tiles_per_img : ceil_div(B, prm.imgs_per_tile);
   dim3 grid(m_tiles, Nc / BN, KS);
   constexpr int smem = conv_tc_smem<BN, STAGES>();
@@ -386,7 +397,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, NC, KS), 1, tmA, tmB, tmC, bias, stats, prm));
+  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, NC, KS), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -507,6 +518,7 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
   if (tile_n == 0) tile_n = auto_tile(B, H, W, Cin, Cout);
   if (tile_n > 2000 && tile_n < 4000) {
     DDPB_REQUIRE(Cin % (tile_n - 2000) == 0, "conv_tc dgrad: Cin %d not a multiple of pair tile %d", Cin, tile_n - 2000);
+    DDPB_REQUIRE(!g_bnred.y, "conv_tc dgrad: pair tiles (DDPB_CONV_2CTA) have no fused BatchNorm reduction");
     return launch_conv_tc2(true, tile_n - 2000, dy, w_bf16, dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
   }
   if (tile_n > 4000) {
@@ -559,4 +571,22 @@ extern "C" int ddpb_conv1x1_fwd_tc(const void* x, const void* w_bf16, const floa
   if (Cout % 128 == 0 && cta_count(B, H, W, Cout, 128) >= 148)
     return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
   return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
+}
+
+// dgrad as above, and in its epilogue the BatchNorm-backward reduction of the block whose OUTPUT dx is the
+// gradient of: sums[0:Cin] += sum dz, sums[Cin:2Cin] += sum dz * xhat, where dz is dx masked by that
+// block's ReLU / 2x2 max-pool.  y_win[B,H,W,Cin] (bf16) holds, per element of dx, the conv output of that
+// block that won the window (ddpb_bn_relu_pool_fwd_winner; the conv output itself for a block without
+// pooling); NaN marks "blocked by ReLU".  Afterwards only ddpb_bn_relu_pool_bwd_apply is needed.
+extern "C" int ddpb_conv3x3_dgrad_bnred_tc(const void* dy, const void* w_bf16, void* dx, int B, int H, int W, int Cin,
+                                           int Cout, int tile_n, const void* y_win, const float* mean,
+                                           const float* invstd, const float* gamma, const float* beta, float* sums,
+                                           cudaStream_t stream) {
+  DDPB_REQUIRE(y_win && mean && invstd && gamma && beta && sums, "dgrad_bnred: null BatchNorm argument");
+  DDPB_REQUIRE(tile_n < 2000 || tile_n > 4000, "dgrad_bnred: pair tiles have no fused reduction");
+  g_bnred.y = y_win; g_bnred.mean = mean; g_bnred.invstd = invstd; g_bnred.gamma = gamma; g_bnred.beta = beta;
+  g_bnred.sums = sums;
+  const int rc = ddpb_conv3x3_dgrad_tc(dy, w_bf16, dx, B, H, W, Cin, Cout, tile_n, stream);
+  g_bnred = BnRedArgs();
+  return rc;
 }

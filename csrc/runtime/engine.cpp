@@ -43,6 +43,7 @@ struct Block {
   long long ch_off;      // offset of this block's [C] in mean / invstd / running stats
   void* y;               // conv output  [B,hw,hw,cout]
   void* act;             // block output [B,ohw,ohw,cout]
+  void* win = nullptr;   // pooling blocks, bf16 tensor-core path: conv output that won each pool window (NaN = none)
 };
 
 struct Bucket { long long off, numel; int last_block; int mode; };   // last_block: -1 = classifier
@@ -70,6 +71,7 @@ struct Engine {
   float *loss = nullptr, *eval_loss = nullptr; int *correct = nullptr; long long* nbt = nullptr;
   size_t scratch_floats = 0;
   void *input = nullptr, *dy_buf2[2] = {nullptr, nullptr}, *dact = nullptr; long long* target = nullptr;
+  bool fuse_bn_reduce = true;                 // DDPB_FUSE_BN_REDUCE=0: keep the separate reduction kernel
   void *x0cols = nullptr, *w0pad = nullptr;   // first layer as a GEMM: patch matrix [B*1024][64], weights [64][64]
   std::vector<Bucket> buckets;
   cudaStream_t comm = nullptr, wg = nullptr;
@@ -238,6 +240,7 @@ static int alloc_all(Engine* e) {
     max_y = std::max(max_y, y); max_act = std::max(max_act, o);
     DDPB_CUDA_CHECK(cudaMalloc(&b.y, B * y * e->esize));
     DDPB_CUDA_CHECK(cudaMalloc(&b.act, B * o * e->esize));
+    if (b.pool && c.dtype == DDPB_BF16 && c.use_tc && e->fuse_bn_reduce) DDPB_CUDA_CHECK(cudaMalloc(&b.win, B * o * e->esize));
   }
   DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf2[0], B * max_y * e->esize));
   DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf2[1], B * max_y * e->esize));
@@ -304,10 +307,10 @@ static int forward(Engine* e, int B, int training, cudaStream_t s) {
       LAUNCH(e, ddpb_conv3x3_fwd_simt(x, e->master + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, dt, s));
       if (st && !(b.cin == 3 && b.cout == 64)) e->counting += 1;       // separate channel_stats launch
     }
-    LAUNCH(e, ddpb_bn_relu_pool_fwd(b.y, st, e->master + b.bn_w.off, e->master + b.bn_b.off, b.act,
-                                    e->mean + b.ch_off, e->invstd + b.ch_off, e->rmean + b.ch_off,
-                                    e->rvar + b.ch_off, e->nbt + i, B, b.hw, b.hw, b.cout, b.pool, training, 1e-5f,
-                                    0.1f, dt, s));
+    LAUNCH(e, ddpb_bn_relu_pool_fwd_winner(b.y, st, e->master + b.bn_w.off, e->master + b.bn_b.off, b.act,
+                                           e->mean + b.ch_off, e->invstd + b.ch_off, e->rmean + b.ch_off,
+                                           e->rvar + b.ch_off, e->nbt + i, training ? b.win : nullptr, B, b.hw, b.hw,
+                                           b.cout, b.pool, training, 1e-5f, 0.1f, dt, s));
     x = b.act;
   }
   return DDPB_OK;
@@ -399,21 +402,39 @@ static int backward(Engine* e, int B, cudaStream_t s) {
                         e->grad + e->fc_b.off, B, dt, s));
   DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[L], s));
   ECHECK(buckets_ready(e, -1, e->ev_dg[L], nullptr));
+  bool reduced_by_dgrad = false;
   for (int i = L - 1; i >= 0; --i) {
     Block& b = e->blocks[i];
     const void* x_in = i == 0 ? e->input : e->blocks[i - 1].act;
     void* dy = e->dy_buf2[i & 1];
     if (i + 2 < L) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[i + 2], 0));   // previous reader of this dY buffer
-    LAUNCH(e, ddpb_bn_relu_pool_bwd(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off, e->master + b.bn_w.off,
-                                    e->master + b.bn_b.off, bsums + b.stat_off, dy, e->grad + b.bn_w.off,
-                                    e->grad + b.bn_b.off, e->grad + b.conv_b.off, B, b.hw, b.hw, b.cout, b.pool,
-                                    dt, s));
-    e->counting += 1;     // the BN backward is two launches (reduce + apply)
+    if (reduced_by_dgrad) {
+      // the reduction pass already ran in the epilogue of dgrad(i + 1)
+      LAUNCH(e, ddpb_bn_relu_pool_bwd_apply(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off,
+                                            e->master + b.bn_w.off, e->master + b.bn_b.off, bsums + b.stat_off, dy,
+                                            e->grad + b.bn_w.off, e->grad + b.bn_b.off, e->grad + b.conv_b.off, B,
+                                            b.hw, b.hw, b.cout, b.pool, dt, s));
+    } else {
+      LAUNCH(e, ddpb_bn_relu_pool_bwd(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off, e->master + b.bn_w.off,
+                                      e->master + b.bn_b.off, bsums + b.stat_off, dy, e->grad + b.bn_w.off,
+                                      e->grad + b.bn_b.off, e->grad + b.conv_b.off, B, b.hw, b.hw, b.cout, b.pool,
+                                      dt, s));
+      e->counting += 1;     // the BN backward is two launches (reduce + apply)
+    }
+    reduced_by_dgrad = false;
     DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dy[i], s));
     // dgrad reads this layer's CURRENT weights; the bucket's fused reduce+SGD rewrites them, so the
     // bucket may only start after dgrad (ev_dg) as well as after wgrad (ev_wg).
     if (i > 0) {
-      if (use_tc(e, b))
+      if (use_tc(e, b) && e->fuse_bn_reduce) {
+        // dgrad(i) also reduces the BN-backward sums of block i - 1 (whose output gradient it produces)
+        const Block& pb = e->blocks[i - 1];
+        LAUNCH(e, ddpb_conv3x3_dgrad_bnred_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0,
+                                              pb.pool ? pb.win : pb.y, e->mean + pb.ch_off, e->invstd + pb.ch_off,
+                                              e->master + pb.bn_w.off, e->master + pb.bn_b.off, bsums + pb.stat_off,
+                                              s));
+        reduced_by_dgrad = true;
+      } else if (use_tc(e, b))
         LAUNCH(e, ddpb_conv3x3_dgrad_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
       else
         LAUNCH(e, ddpb_conv3x3_dgrad_simt(dy, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
@@ -543,6 +564,7 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   DDPB_REQUIRE(cfg->world >= 1 && cfg->world <= DDPB_MAX_RANKS, "engine_create: world size %d unsupported", cfg->world);
   Engine* e = new Engine();
   e->cfg = *cfg;
+  if (const char* fb = getenv("DDPB_FUSE_BN_REDUCE")) e->fuse_bn_reduce = fb[0] != '0';
   int rc = plan_layout(e);
   if (!rc) { plan_buckets(e); rc = alloc_all(e); }
   if (rc) { delete e; return rc; }
@@ -558,7 +580,7 @@ extern "C" int ddpb_engine_destroy(void* handle) {
   for (auto& kv : e->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (int r = 0; r < e->cfg.world; ++r)
     if (r != e->cfg.rank && e->peer_arena[r] && !e->arena_external) cudaIpcCloseMemHandle(e->peer_arena[r]);
-  for (auto& b : e->blocks) { cudaFree(b.y); cudaFree(b.act); }
+  for (auto& b : e->blocks) { cudaFree(b.y); cudaFree(b.act); if (b.win) cudaFree(b.win); }
   void* frees[] = {e->epochs, e->scratch, e->mean, e->invstd, e->nbt, e->logits, e->dlogits, e->eval_loss,
                    e->input, e->target, e->dy_buf2[0], e->dy_buf2[1], e->dact, e->x0cols, e->w0pad,
                    e->arena_external ? nullptr : e->arena};

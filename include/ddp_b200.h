@@ -64,6 +64,12 @@ int ddpb_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma,
                           float* save_mean, float* save_invstd, float* running_mean, float* running_var,
                           long long* num_batches_tracked, int batch, int H, int W, int C, int pool, int training,
                           float eps, float momentum, int dtype, cudaStream_t stream);
+/* Same, and `winner` (nullable, shaped like out) receives the conv output that won each ReLU + max-pool
+ * window (NaN where ReLU blocked the whole window): the input of ddpb_conv3x3_dgrad_bnred_tc. */
+int ddpb_bn_relu_pool_fwd_winner(const void* y, const float* stats, const float* gamma, const float* beta, void* out,
+                                 float* save_mean, float* save_invstd, float* running_mean, float* running_var,
+                                 long long* num_batches_tracked, void* winner, int batch, int H, int W, int C,
+                                 int pool, int training, float eps, float momentum, int dtype, cudaStream_t stream);
 
 /* Backward of the above.  sums: zeroed [2C] scratch.  dgamma/dbeta are written; dbias (gradient of
  * the conv bias that precedes the BN, may be null) is accumulated. */
@@ -71,6 +77,11 @@ int ddpb_bn_relu_pool_bwd(const void* dout, const void* y, const float* save_mea
                           const float* gamma, const float* beta, float* sums, void* dy, float* dgamma,
                           float* dbeta, float* dbias, int batch, int H, int W, int C, int pool, int dtype,
                           cudaStream_t stream);
+/* Second pass of the above only (sums already reduced, e.g. by ddpb_conv3x3_dgrad_bnred_tc). */
+int ddpb_bn_relu_pool_bwd_apply(const void* dout, const void* y, const float* save_mean, const float* save_invstd,
+                                const float* gamma, const float* beta, float* sums, void* dy, float* dgamma,
+                                float* dbeta, float* dbias, int batch, int H, int W, int C, int pool, int dtype,
+                                cudaStream_t stream);
 
 /* Same computation as ddpb_bn_relu_pool_bwd for callers that cannot supply the [2*C] scratch: a
  * host that pre-committed all device memory to its own pool, or a plug-in interface that passes only
@@ -126,6 +137,15 @@ int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const float* bias, vo
                         int W, int Cin, int Cout, int tile_n, cudaStream_t stream);
 int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* dx, int B, int H, int W, int Cin, int Cout,
                           int tile_n, cudaStream_t stream);
+/* dgrad plus, in its epilogue, the BatchNorm-backward reduction of the block that produced this conv's
+ * input: sums[0:Cin] += sum dz, sums[Cin:2*Cin] += sum dz*xhat, where dz is dx masked by that block's
+ * ReLU / max-pool.  y_win (bf16 [B,H,W,Cin]) is the `winner` tensor of ddpb_bn_relu_pool_fwd_winner
+ * for a pooling block, or the block's conv output y itself when it does not pool.
+ * Follow with ddpb_bn_relu_pool_bwd_apply.  Fuses the first BN-backward kernel of every block into the
+ * tensor-core kernel that precedes it (no reference counterpart: autograd runs them separately). */
+int ddpb_conv3x3_dgrad_bnred_tc(const void* dy, const void* w_bf16, void* dx, int B, int H, int W, int Cin, int Cout,
+                                int tile_n, const void* y_win, const float* mean, const float* invstd,
+                                const float* gamma, const float* beta, float* sums, cudaStream_t stream);
 /* dw (fp32 KRSC) accumulates. */
 int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
                           int split_k, cudaStream_t stream);

@@ -212,6 +212,34 @@ def test_conv_tc_dgrad(F, R, b, hw, cin, cout, tile_n):
 
 
 @pytest.mark.parametrize("b", [16, 10])
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
+@pytest.mark.parametrize("tile_n", [0, 64, 128, 1264, 4264, 4464, 4228, 4428])
+def test_conv_tc_dgrad_fused_bn_reduce(F, R, b, hw, cin, cout, tile_n, pool):
+    """dgrad epilogue also produces the previous block's BN-backward sums; the apply pass finishes the job."""
+    if tile_n and not _tile_ok(tile_n, cin, hw):
+        pytest.skip("tile code does not fit this layer")
+    torch.manual_seed(21)
+    dy = torch.randn(b, hw, hw, cout, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(cout, 3, 3, cin, device=DEV) * 0.05).to(torch.bfloat16)
+    hy = hw * 2 if pool else hw                                  # the previous block's conv output
+    y_prev = torch.randn(b, hy, hy, cin, device=DEV).to(torch.bfloat16)
+    gamma, beta = torch.rand(cin, device=DEV) + 0.5, torch.randn(cin, device=DEV) * 0.2
+    rm, rv = torch.zeros(cin, device=DEV), torch.ones(cin, device=DEV)
+    _, mean, invstd, win = F.bn_relu_pool_fwd(y_prev, R.channel_stats(y_prev), gamma, beta, rm, rv, None, pool,
+                                              want_winner=True)
+    dx, sums = F.conv_dgrad_bnred_tc(dy, w, win if pool else y_prev, mean, invstd, gamma, beta, tile_n=tile_n)
+    dyp, dgamma, dbeta = F.bn_relu_pool_bwd_apply(dx, y_prev, mean, invstd, gamma, beta, sums, pool)
+    torch.cuda.synchronize()
+    _report(f"bnred dx hw{hw} {cin}->{cout} b{b} n{tile_n}", dx, R.conv_dgrad(dy, w), 6e-3)
+    dy2, dgamma2, dbeta2 = F.bn_relu_pool_bwd(dx, y_prev, mean, invstd, gamma, beta, pool)      # two-pass path
+    torch.cuda.synchronize()
+    _report("bnred dbeta", dbeta, dbeta2, 1e-4)
+    _report("bnred dgamma", dgamma, dgamma2, 1e-4)
+    _report("bnred dy", dyp, dy2, 2e-3)
+
+
+@pytest.mark.parametrize("b", [16, 10])
 @pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
 @pytest.mark.parametrize("split_k", [0, 1, 3])
 def test_conv_tc_wgrad(F, R, b, hw, cin, cout, split_k):
