@@ -262,7 +262,8 @@ def run_ours(args) -> dict:
 
     cfg = TrainConfig(num_nodes=world, rank=rank, sync="bucketed" if world > 1 else "none", dtype=args.dtype,
                       device="cuda", backend="native", global_batch=PER_GPU_BATCH * world, synthetic=True,
-                      bucket_plan=args.bucket_plan, comm=args.comm, use_cuda_graph=not args.no_graph)
+                      bucket_plan=args.bucket_plan, bucket_cap_mb=args.bucket_cap_mb,
+                      first_bucket_mb=args.first_bucket_mb, comm=args.comm, use_cuda_graph=not args.no_graph)
     be = NativeBackend(cfg, torch.device("cuda", local))
     host = synthetic_host_batches(8, rank, "u8")
     dev = [RawBatch(*[t.cuda() for t in hb]) for hb in host[:4]]
@@ -326,7 +327,8 @@ def run_ours(args) -> dict:
         "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": PER_GPU_BATCH, "seq_len": None,
                    "parallelism": f"dp{world}", "part": "3 (bucketed P2P reduce fused with SGD)" if world > 1
                    else "3 (single GPU)", "comm": be.comm_name(), "cuda_graph": be.uses_graph(),
-                   "bucket_plan": args.bucket_plan, "timeline": timeline,
+                   "bucket_plan": args.bucket_plan if args.bucket_plan != "ddp" else
+                   f"ddp(first {args.first_bucket_mb} MB, cap {args.bucket_cap_mb} MB)", "timeline": timeline,
                    "l2": "working set per step (activations + weights + grads) > 126 MB L2; no explicit flush"},
     }
 
@@ -339,6 +341,8 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--bucket-plan", default="per_layer", choices=["ddp", "per_layer", "single"])
+    ap.add_argument("--bucket-cap-mb", type=float, default=25.0, help="ddp plan: bucket size cap")
+    ap.add_argument("--first-bucket-mb", type=float, default=1.0, help="ddp plan: size of the first bucket")
     ap.add_argument("--comm", default="auto", choices=["auto", "p2p", "nvls", "nccl"])
     ap.add_argument("--no-graph", action="store_true")
     args = ap.parse_args()

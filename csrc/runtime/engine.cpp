@@ -74,7 +74,8 @@ struct Engine {
   bool fuse_bn_reduce = true;                 // DDPB_FUSE_BN_REDUCE=0: keep the separate reduction kernel
   void *x0cols = nullptr, *w0pad = nullptr;   // first layer as a GEMM: patch matrix [B*1024][64], weights [64][64]
   std::vector<Bucket> buckets;
-  cudaStream_t comm = nullptr, wg = nullptr;
+  cudaStream_t comm = nullptr, comm2 = nullptr, wg = nullptr;
+  bool two_comm = true, comm2_used = false;   // multi-GPU: buckets alternate between two streams (DDPB_TWO_COMM=0: one)
   std::vector<cudaEvent_t> bucket_ev, ev_dy, ev_dg, ev_wg;
   cudaEvent_t join_ev = nullptr, fork_ev = nullptr;
   std::map<long long, Graph> graphs;     // key = kind * 1e6 + batch
@@ -252,6 +253,7 @@ static int alloc_all(Engine* e) {
   int prio_lo = 0, prio_hi = 0;
   DDPB_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
   DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->comm, cudaStreamNonBlocking, prio_hi));
+  DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->comm2, cudaStreamNonBlocking, prio_hi));
   DDPB_CUDA_CHECK(cudaStreamCreateWithFlags(&e->wg, cudaStreamNonBlocking));
   e->ev_dy.resize(c.num_blocks + 1); e->ev_dg.resize(c.num_blocks + 1); e->ev_wg.resize(c.num_blocks + 1);
   for (int i = 0; i <= c.num_blocks; ++i) {
@@ -376,11 +378,23 @@ static int buckets_ready(Engine* e, int blk, cudaEvent_t ev_a, cudaEvent_t ev_b)
   if (!overlapped(e)) return DDPB_OK;
   for (size_t i = 0; i < e->buckets.size(); ++i) {
     if (e->buckets[i].last_block != blk) continue;
-    if (ev_a) DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, ev_a, 0));
-    if (ev_b) DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, ev_b, 0));
-    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_ready[i], e->comm));
-    ECHECK(launch_bucket(e, (int)i, e->comm));
-    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_done[i], e->comm));
+    // Multi-GPU: a bucket kernel is mostly NVLink latency (cross-rank barrier, first loads), so two of
+    // them in flight on alternating streams overlap their latencies.  The step's last bucket carries the
+    // closing barrier and therefore has to follow ALL earlier buckets: it runs on `comm` after a join.
+    const bool last = i + 1 == e->buckets.size();
+    const bool multi = e->cfg.world > 1 && e->peers_set && e->two_comm;
+    cudaStream_t cs = (multi && !last && (i & 1)) ? e->comm2 : e->comm;
+    if (ev_a) DDPB_CUDA_CHECK(cudaStreamWaitEvent(cs, ev_a, 0));
+    if (ev_b) DDPB_CUDA_CHECK(cudaStreamWaitEvent(cs, ev_b, 0));
+    if (last && e->comm2_used) {
+      DDPB_CUDA_CHECK(cudaEventRecord(e->fork_ev, e->comm2));
+      DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, e->fork_ev, 0));
+      e->comm2_used = false;
+    }
+    if (cs == e->comm2) e->comm2_used = true;
+    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_ready[i], cs));
+    ECHECK(launch_bucket(e, (int)i, cs));
+    if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_done[i], cs));
   }
   return DDPB_OK;
 }
@@ -457,6 +471,11 @@ static int backward(Engine* e, int B, cudaStream_t s) {
   const bool p2p = c.world > 1 && e->peers_set;
   if (overlapped(e)) {
     // join: the step is complete when every bucket kernel has finished
+    if (e->comm2_used) {       // (the last bucket normally joined it already)
+      DDPB_CUDA_CHECK(cudaEventRecord(e->fork_ev, e->comm2));
+      DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, e->fork_ev, 0));
+      e->comm2_used = false;
+    }
     DDPB_CUDA_CHECK(cudaEventRecord(e->join_ev, e->comm));
     DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->join_ev, 0));
   } else if (!c.external_sync) {
@@ -565,6 +584,7 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   Engine* e = new Engine();
   e->cfg = *cfg;
   if (const char* fb = getenv("DDPB_FUSE_BN_REDUCE")) e->fuse_bn_reduce = fb[0] != '0';
+  if (const char* tc = getenv("DDPB_TWO_COMM")) e->two_comm = tc[0] != '0';
   int rc = plan_layout(e);
   if (!rc) { plan_buckets(e); rc = alloc_all(e); }
   if (rc) { delete e; return rc; }
@@ -592,6 +612,7 @@ extern "C" int ddpb_engine_destroy(void* handle) {
   for (auto& ev : e->ev_dg) cudaEventDestroy(ev);
   for (auto& ev : e->ev_wg) cudaEventDestroy(ev);
   if (e->comm) cudaStreamDestroy(e->comm);
+  if (e->comm2) cudaStreamDestroy(e->comm2);
   if (e->wg) cudaStreamDestroy(e->wg);
   delete e;
   return DDPB_OK;
