@@ -181,6 +181,30 @@ def conv_fwd_tc(x, w_bf16, bias, want_stats: bool = False, tile_n: int = 0):
     return (y, stats) if want_stats else y
 
 
+def conv_fwd_bn_tc(x, w_bf16, bias, gamma, beta, running_mean, running_var, nbt, pool: bool, tile_n: int = 0):
+    """Forward conv with this block's BatchNorm + ReLU + pool fused behind a grid barrier.
+    Returns dict(y, stats, act, winner, save_mean, save_invstd, fused)."""
+    b, h, w_, cin = x.shape
+    cout = w_bf16.shape[0]
+    oh, ow = (h // 2, w_ // 2) if pool else (h, w_)
+    dev = x.device
+    y = torch.empty((b, h, w_, cout), dtype=torch.bfloat16, device=dev)
+    stats = torch.zeros(2 * cout, dtype=torch.float32, device=dev)
+    act = torch.empty((b, oh, ow, cout), dtype=torch.bfloat16, device=dev)
+    winner = torch.empty_like(act)
+    save_mean = torch.empty(cout, dtype=torch.float32, device=dev)
+    save_invstd = torch.empty(cout, dtype=torch.float32, device=dev)
+    barrier = torch.zeros(1, dtype=torch.int32, device=dev)
+    fused = ctypes.c_int(0)
+    check(lib().ddpb_conv3x3_fwd_bn_tc(ptr(x), ptr(w_bf16), ptr(bias), ptr(y), ptr(stats), b, h, w_, cin, cout, tile_n,
+                                       ptr(gamma), ptr(beta), ptr(act), ptr(winner), ptr(save_mean), ptr(save_invstd),
+                                       ptr(running_mean), ptr(running_var), ptr(nbt), int(pool), cf(BN_EPS),
+                                       cf(BN_MOMENTUM), ptr(barrier), ctypes.byref(fused), stream_handle()),
+          "conv_fwd_bn_tc")
+    return dict(y=y, stats=stats, act=act, winner=winner, save_mean=save_mean, save_invstd=save_invstd,
+                fused=bool(fused.value))
+
+
 def conv_dgrad_tc(dy, w_bf16, tile_n: int = 0):
     b, h, w_, cout = dy.shape
     cin = w_bf16.shape[3]

@@ -199,7 +199,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
 // backward pass 2: dy = gamma*invstd * (dz - s1/P - xhat * s2/P); also dgamma, dbeta, conv dbias
 // ------------------------------------------------------------------------------------------
 template <typename T, bool POOL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ sums, T* __restrict__ dy,
@@ -215,15 +215,18 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
   pdl_launch_dependents();
   pdl_wait();
-  float sc[V], sh[V], mu[V], is[V], k1[V], k2[V], ab[V];
+  // dy = sc * (dz - k1 - xhat * k2) with xhat = (y - mu) * is, written as  sc * dz + cb - cy * y:
+  // four per-channel constants instead of seven keep the pooled variant at two blocks per SM
+  float sc[V], sh[V], cb[V], cy[V], ab[V];
   const float invP = 1.f / (float)P;
 #pragma unroll
   for (int j = 0; j < V; ++j) {
-    mu[j] = ld_coh(&mean[c0 + j]); is[j] = ld_coh(&invstd[c0 + j]);
-    sc[j] = ld_coh(&gamma[c0 + j]) * is[j];
-    sh[j] = ld_coh(&beta[c0 + j]) - mu[j] * sc[j];
-    float s1 = ld_coh(&sums[c0 + j]), s2 = ld_coh(&sums[C + c0 + j]);
-    k1[j] = s1 * invP; k2[j] = s2 * invP;
+    const float mu = ld_coh(&mean[c0 + j]), is = ld_coh(&invstd[c0 + j]);
+    sc[j] = ld_coh(&gamma[c0 + j]) * is;
+    sh[j] = ld_coh(&beta[c0 + j]) - mu * sc[j];
+    const float s1 = ld_coh(&sums[c0 + j]), s2 = ld_coh(&sums[C + c0 + j]);
+    cy[j] = sc[j] * is * (s2 * invP);
+    cb[j] = cy[j] * mu - sc[j] * (s1 * invP);
     ab[j] = 0.f;
     if (blockIdx.x == 0 && pl == 0) { dbeta[c0 + j] = s1; dgamma[c0 + j] = s2; }
   }
@@ -252,9 +255,8 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
         float o[V];
 #pragma unroll
         for (int j = 0; j < V; ++j) {
-          float dz = (bq[j] == q) ? d[j] : 0.f;
-          float xhat = (v[q][j] - mu[j]) * is[j];
-          o[j] = sc[j] * (dz - k1[j] - xhat * k2[j]);
+          const float dz = (bq[j] == q) ? d[j] : 0.f;
+          o[j] = fmaf(sc[j], dz, fmaf(-cy[j], v[q][j], cb[j]));
           ab[j] += o[j];
         }
         store_vec<T>(dy + (size_t)in[q] * C + c0, o);

@@ -51,6 +51,17 @@ struct ConvTcParams {
   const bf16* bn_y;
   const float *bn_mean, *bn_invstd, *bn_gamma, *bn_beta;
   float* bn_sums;          // [2 * n_out], accumulated
+  // fprop only: this block's BatchNorm + ReLU (+ 2x2 max-pool) applied in the epilogue after a grid-wide
+  // barrier (bnf_out == null: off).  Needs every CTA of the grid resident at once (checked by the launcher).
+  bf16* bnf_out;           // block output [B, H/(1+pool), W/(1+pool), n_out]
+  bf16* bnf_winner;        // nullable: conv output that won each window (NaN: blocked by ReLU)
+  const float *bnf_gamma, *bnf_beta;
+  float *bnf_save_mean, *bnf_save_invstd, *bnf_running_mean, *bnf_running_var;
+  long long* bnf_nbt;      // nullable
+  unsigned int* bnf_barrier;   // zeroed by the caller before every launch
+  unsigned int bnf_total_ctas;
+  int bnf_pool;
+  float bnf_eps, bnf_momentum;
 };
 
 // XOR swizzle of the 16-byte chunks of the epilogue's bf16 tile ([128 rows][CH chunks]): both the
@@ -320,6 +331,84 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         atomicAdd(&acc_out[(i < CW ? 0 : prm.n_out) + n_tile * BN + ks_rank * CW + cc], acc);
       }
     }
+    // ---- 4. (fprop) fused BatchNorm + ReLU + max-pool of this block
+    if (!DGRAD && prm.bnf_out != nullptr) {
+      // grid-wide barrier: the statistics are complete when every CTA has added its share
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (t == 0) {
+        atomicAdd(prm.bnf_barrier, 1u);
+        const unsigned long long t0 = global_timer_ns();
+        while (ld_acquire_gpu(prm.bnf_barrier) < prm.bnf_total_ctas) {
+          if (global_timer_ns() - t0 > 2000000000ull) {
+            printf("ddpb: conv+BN grid barrier timed out (block %d,%d,%d)\n", blockIdx.x, blockIdx.y, blockIdx.z);
+            __trap();
+          }
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const float inv_p = 1.f / (float)prm.total_pixels;
+      float bsc[8], bsh[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float mean = __ldcg(&stats[col0 + j]) * inv_p;
+        const float var = fmaxf(__ldcg(&stats[prm.n_out + col0 + j]) * inv_p - mean * mean, 0.f);
+        const float invstd = rsqrtf(var + prm.bnf_eps);
+        bsc[j] = __ldcg(&prm.bnf_gamma[col0 + j]) * invstd;
+        bsh[j] = __ldcg(&prm.bnf_beta[col0 + j]) - mean * bsc[j];
+        if (m_tile == 0 && part == 0) {      // one thread per channel in the whole grid
+          prm.bnf_save_mean[col0 + j] = mean;
+          prm.bnf_save_invstd[col0 + j] = invstd;
+          const float n = (float)prm.total_pixels;
+          const float unbiased = prm.total_pixels > 1 ? var * (n / (n - 1.f)) : var;
+          prm.bnf_running_mean[col0 + j] = (1.f - prm.bnf_momentum) * __ldcg(&prm.bnf_running_mean[col0 + j]) + prm.bnf_momentum * mean;
+          prm.bnf_running_var[col0 + j] = (1.f - prm.bnf_momentum) * __ldcg(&prm.bnf_running_var[col0 + j]) + prm.bnf_momentum * unbiased;
+        }
+      }
+      if (m_tile == 0 && n_tile == 0 && ks_rank == 0 && t == 0 && prm.bnf_nbt) *prm.bnf_nbt += 1;
+      // the tile is a box of `rows_per_tile` image rows (H*W >= 128) or of whole images (H*W < 128)
+      const int W = prm.W, H = prm.H;
+      const int pool = prm.bnf_pool;
+      const int ow_n = pool ? W >> 1 : W;                                   // outputs per image row
+      const int img_rows = prm.tiles_per_img > 0 ? prm.rows_per_tile : H;   // image rows per sub-box
+      const int orow_n = pool ? img_rows >> 1 : img_rows;                   // output rows per sub-box
+      const int sub_out = ow_n * orow_n;                                    // outputs per sub-box
+      const int n_sub = prm.tiles_per_img > 0 ? 1 : prm.imgs_per_tile;
+      const int out_per_img = pool ? (H >> 1) * (W >> 1) : H * W;
+      const long long total_imgs = prm.total_pixels / ((long long)H * W);
+      for (int o = part; o < sub_out * n_sub; o += PARTS) {
+        const int sub = o / sub_out, oi = o - sub * sub_out;
+        const int orow = oi / ow_n, ocol = oi - orow * ow_n;
+        const long long img = n0 + sub;
+        if (img >= total_imgs) break;
+        const int r_base = sub * (H * W) + (pool ? (2 * orow) * W + 2 * ocol : orow * W + ocol);
+        float best[8], by[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { best[j] = 0.f; by[j] = __int_as_float(0x7fc00000); }
+        const int nwin = pool ? 4 : 1;
+        for (int wq = 0; wq < nwin; ++wq) {
+          const int r = r_base + (wq & 1) + (wq >> 1) * W;
+          const uint4 u = *reinterpret_cast<const uint4*>(tile + r * (CW * 2) + ((ch ^ tile_swizzle<CH>(r)) << 4));
+          float v[8];
+          { const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c2 = unpack_bf16x2(u.z), e = unpack_bf16x2(u.w);
+            v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c2.x; v[5] = c2.y; v[6] = e.x; v[7] = e.y; }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float z = fmaf(v[j], bsc[j], bsh[j]);
+            if (z > best[j]) { best[j] = z; by[j] = v[j]; }       // strict >: first maximum wins (matches the backward pass)
+          }
+        }
+        const long long opix = img * out_per_img + (long long)((prm.tiles_per_img > 0 ? (pool ? h0 >> 1 : h0) : 0) + orow) * ow_n + ocol;
+        const uint4 ov = make_uint4(pack_bf16x2(best[0], best[1]), pack_bf16x2(best[2], best[3]),
+                                    pack_bf16x2(best[4], best[5]), pack_bf16x2(best[6], best[7]));
+        *reinterpret_cast<uint4*>(prm.bnf_out + opix * prm.n_out + col0) = ov;
+        if (prm.bnf_winner) {
+          const uint4 wv = make_uint4(pack_bf16x2(by[0], by[1]), pack_bf16x2(by[2], by[3]),
+                                      pack_bf16x2(by[4], by[5]), pack_bf16x2(by[6], by[7]));
+          *reinterpret_cast<uint4*>(prm.bnf_winner + opix * prm.n_out + col0) = wv;
+        }
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -344,6 +433,19 @@ struct BnRedArgs {
   float* sums = nullptr;
 };
 static thread_local BnRedArgs g_bnred;
+
+// Arguments of the fused BatchNorm forward (set by ddpb_conv3x3_fwd_bn_tc around its dispatch).
+struct BnFwdArgs {
+  void *out = nullptr, *winner = nullptr;
+  const float *gamma = nullptr, *beta = nullptr;
+  float *save_mean = nullptr, *save_invstd = nullptr, *running_mean = nullptr, *running_var = nullptr;
+  long long* nbt = nullptr;
+  unsigned int* barrier = nullptr;
+  int pool = 0;
+  float eps = 1e-5f, momentum = 0.1f;
+  bool applied = false;      // out: did the launch run with the fusion (all CTAs co-resident)?
+};
+static thread_local BnFwdArgs g_bnfwd;
 
 template <int BN, int STAGES, bool DGRAD, int NC = 1, int KS = 1>
 static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, float* stats, int B, int H, int W,
@@ -385,6 +487,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   prm.bn_y = DGRAD ? (const bf16*)br.y : nullptr;
   prm.bn_mean = br.mean; prm.bn_invstd = br.invstd; prm.bn_gamma = br.gamma; prm.bn_beta = br.beta;
   prm.bn_sums = br.sums;
+  prm.bnf_out = nullptr;
   static_assert(KS == 1 || NC == 1, "split-K and multicast clusters are separate variants");
   static_assert((KS - 1) * (BN / KS) * 128 * 4 + TILE_M * (BN / KS) * 2 + TILE_M * 2 * 8 * 4 <= STAGES * (A_BYTES + BN * KCHUNK * 2),
                 "epilogue buffers (split-K receive area, bf16 tile, partial sums) must fit in the pipeline stages");
@@ -395,7 +498,46 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   static bool configured = false;
   if (!configured) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    // ask for the largest shared-memory carve-out, so that two ~100 KB CTAs share an SM (and the
+    // occupancy query below reports that)
+    DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     configured = true;
+  }
+  if (!DGRAD && g_bnfwd.out && stats) {
+    // the fused BatchNorm needs a grid-wide barrier: only when every CTA is resident at the same time
+    static int capacity = -1;
+    if (capacity < 0) {
+      // CTAs that fit on the GPU at once, from the kernel's actual resource use.  (The runtime's occupancy
+      // query answers 1 CTA per SM for these ~100 KB kernels although two are resident - the TMA probe's
+      // single-wave timing of 296 such CTAs shows it - so the limits are applied by hand.)
+      int dev = 0, sms = 0, smem_sm = 0, regs_sm = 0;
+      DDPB_CUDA_CHECK(cudaGetDevice(&dev));
+      DDPB_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      DDPB_CUDA_CHECK(cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
+      DDPB_CUDA_CHECK(cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev));
+      cudaFuncAttributes fa;
+      DDPB_CUDA_CHECK(cudaFuncGetAttributes(&fa, kern));
+      const int by_smem = smem_sm / (smem + (int)fa.sharedSizeBytes + 1024);
+      const int regs_cta = ((fa.numRegs * 32 + 255) / 256 * 256) * (192 / 32);
+      const int by_regs = regs_sm / (regs_cta > 0 ? regs_cta : 1);
+      const int by_tmem = 512 / BN;
+      int per_sm = by_smem < by_regs ? by_smem : by_regs;
+      if (by_tmem < per_sm) per_sm = by_tmem;
+      capacity = per_sm * sms;
+      // clusters are placed inside one GPC: leave room for SMs a partially filled GPC cannot use
+      if (NC * KS > 1) capacity = capacity / 8 * 7 / (NC * KS) * (NC * KS);
+    }
+    const long long total = (long long)grid.x * grid.y * grid.z;
+    if (getenv("DDPB_DEBUG_OCC")) fprintf(stderr, "[ddpb] conv<%d,%d,NC%d,KS%d> grid %lld capacity %d smem %d\n", BN, STAGES, NC, KS, total, capacity, smem);
+    if (total <= capacity) {
+      prm.bnf_out = (bf16*)g_bnfwd.out; prm.bnf_winner = (bf16*)g_bnfwd.winner;
+      prm.bnf_gamma = g_bnfwd.gamma; prm.bnf_beta = g_bnfwd.beta;
+      prm.bnf_save_mean = g_bnfwd.save_mean; prm.bnf_save_invstd = g_bnfwd.save_invstd;
+      prm.bnf_running_mean = g_bnfwd.running_mean; prm.bnf_running_var = g_bnfwd.running_var;
+      prm.bnf_nbt = g_bnfwd.nbt; prm.bnf_barrier = g_bnfwd.barrier; prm.bnf_total_ctas = (unsigned)total;
+      prm.bnf_pool = g_bnfwd.pool; prm.bnf_eps = g_bnfwd.eps; prm.bnf_momentum = g_bnfwd.momentum;
+      g_bnfwd.applied = true;
+    }
   }
   DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, NC, KS), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
@@ -588,5 +730,34 @@ extern "C" int ddpb_conv3x3_dgrad_bnred_tc(const void* dy, const void* w_bf16, v
   g_bnred.sums = sums;
   const int rc = ddpb_conv3x3_dgrad_tc(dy, w_bf16, dx, B, H, W, Cin, Cout, tile_n, stream);
   g_bnred = BnRedArgs();
+  return rc;
+}
+
+// Forward conv as above and, when the whole grid fits on the GPU at once, this block's BatchNorm (batch
+// statistics) + ReLU + optional 2x2 max-pool in the same kernel: after a grid-wide barrier every CTA
+// normalises the tile it still holds in shared memory and writes `act` (and `winner`, nullable).
+// *fused = 1 when that happened; 0 means only y and stats were produced and the caller must run
+// ddpb_bn_relu_pool_fwd(_winner) itself.  `barrier` is one zeroed uint32 per launch; stats must be zeroed.
+extern "C" int ddpb_conv3x3_fwd_bn_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats,
+                                      int B, int H, int W, int Cin, int Cout, int tile_n, const float* gamma,
+                                      const float* beta, void* act, void* winner, float* save_mean,
+                                      float* save_invstd, float* running_mean, float* running_var,
+                                      long long* num_batches_tracked, int pool, float eps, float momentum,
+                                      unsigned int* barrier, int* fused, cudaStream_t stream) {
+  DDPB_REQUIRE(stats && gamma && beta && act && save_mean && save_invstd && running_mean && running_var && barrier &&
+                   fused, "conv_fwd_bn: null argument");
+  DDPB_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "conv_fwd_bn: pooling needs even H, W");
+  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cout, Cin);
+  *fused = 0;
+  if (tile_n > 2000 && tile_n < 4000)       // pair tiles have their own epilogue: no fusion
+    return ddpb_conv3x3_fwd_tc(x, w_bf16, bias, y, stats, B, H, W, Cin, Cout, tile_n, stream);
+  g_bnfwd = BnFwdArgs();
+  g_bnfwd.out = act; g_bnfwd.winner = winner; g_bnfwd.gamma = gamma; g_bnfwd.beta = beta;
+  g_bnfwd.save_mean = save_mean; g_bnfwd.save_invstd = save_invstd;
+  g_bnfwd.running_mean = running_mean; g_bnfwd.running_var = running_var; g_bnfwd.nbt = num_batches_tracked;
+  g_bnfwd.barrier = barrier; g_bnfwd.pool = pool ? 1 : 0; g_bnfwd.eps = eps; g_bnfwd.momentum = momentum;
+  const int rc = ddpb_conv3x3_fwd_tc(x, w_bf16, bias, y, stats, B, H, W, Cin, Cout, tile_n, stream);
+  *fused = g_bnfwd.applied ? 1 : 0;
+  g_bnfwd = BnFwdArgs();
   return rc;
 }

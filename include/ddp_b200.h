@@ -137,6 +137,15 @@ int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const float* bias, vo
                         int W, int Cin, int Cout, int tile_n, cudaStream_t stream);
 int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* dx, int B, int H, int W, int Cin, int Cout,
                           int tile_n, cudaStream_t stream);
+/* Forward conv and, when the whole grid is resident at once (*fused = 1), this block's training-mode
+ * BatchNorm + ReLU + optional 2x2 max-pool in the same kernel (grid-wide barrier after the statistics).
+ * *fused = 0: only y / stats were produced, run ddpb_bn_relu_pool_fwd(_winner) next.
+ * `barrier`: one zeroed uint32 per launch.  No reference counterpart (cuDNN runs conv and BN separately). */
+int ddpb_conv3x3_fwd_bn_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats, int B, int H,
+                           int W, int Cin, int Cout, int tile_n, const float* gamma, const float* beta, void* act,
+                           void* winner, float* save_mean, float* save_invstd, float* running_mean,
+                           float* running_var, long long* num_batches_tracked, int pool, float eps, float momentum,
+                           unsigned int* barrier, int* fused, cudaStream_t stream);
 /* dgrad plus, in its epilogue, the BatchNorm-backward reduction of the block that produced this conv's
  * input: sums[0:Cin] += sum dz, sums[Cin:2*Cin] += sum dz*xhat, where dz is dx masked by that block's
  * ReLU / max-pool.  y_win (bf16 [B,H,W,Cin]) is the `winner` tensor of ddpb_bn_relu_pool_fwd_winner

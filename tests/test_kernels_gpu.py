@@ -215,6 +215,41 @@ def test_conv_tc_dgrad(F, R, b, hw, cin, cout, tile_n):
 @pytest.mark.parametrize("pool", [False, True])
 @pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
 @pytest.mark.parametrize("tile_n", [0, 64, 128, 1264, 4264, 4464, 4228, 4428])
+def test_conv_tc_forward_fused_bn(F, R, b, hw, cin, cout, tile_n, pool):
+    """conv + grid barrier + BatchNorm/ReLU/pool in one kernel == the two separate kernels."""
+    if tile_n and not _tile_ok(tile_n, cout, hw):
+        pytest.skip("tile code does not fit this layer")
+    torch.manual_seed(22)
+    x = torch.randn(b, hw, hw, cin, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(cout, 3, 3, cin, device=DEV) * 0.05).to(torch.bfloat16)
+    bias = torch.randn(cout, device=DEV) * 0.1
+    gamma, beta = torch.rand(cout, device=DEV) + 0.5, torch.randn(cout, device=DEV) * 0.2
+    rm1, rv1 = torch.zeros(cout, device=DEV), torch.ones(cout, device=DEV)
+    rm2, rv2 = rm1.clone(), rv1.clone()
+    nbt1 = torch.zeros(1, dtype=torch.int64, device=DEV)
+    nbt2 = nbt1.clone()
+    got = F.conv_fwd_bn_tc(x, w, bias, gamma, beta, rm1, rv1, nbt1, pool, tile_n=tile_n)
+    if not got["fused"]:
+        pytest.skip("grid does not fit on the GPU at once: the launcher kept the kernels separate")
+    y, stats = F.conv_fwd_tc(x, w, bias, want_stats=True, tile_n=tile_n)
+    act, mean, invstd, win = F.bn_relu_pool_fwd(y, stats, gamma, beta, rm2, rv2, nbt2, pool, want_winner=True)
+    torch.cuda.synchronize()
+    assert torch.equal(got["y"], y)
+    _report(f"fusedbn stats hw{hw} {cin}->{cout} b{b} n{tile_n}", got["stats"], stats, 1e-5)
+    _report("fusedbn mean", got["save_mean"], mean, 1e-4)
+    _report("fusedbn invstd", got["save_invstd"], invstd, 1e-4)
+    _report("fusedbn act", got["act"], act, 4e-3)
+    same = torch.isnan(got["winner"].float()) == torch.isnan(win.float())
+    assert same.float().mean().item() > 0.999       # ReLU decisions can flip on values that round to zero
+    _report("fusedbn running_mean", rm1, rm2, 1e-4)
+    _report("fusedbn running_var", rv1, rv2, 1e-4)
+    assert int(nbt1) == int(nbt2) == 1
+
+
+@pytest.mark.parametrize("b", [16, 10])
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
+@pytest.mark.parametrize("tile_n", [0, 64, 128, 1264, 4264, 4464, 4228, 4428])
 def test_conv_tc_dgrad_fused_bn_reduce(F, R, b, hw, cin, cout, tile_n, pool):
     """dgrad epilogue also produces the previous block's BN-backward sums; the apply pass finishes the job."""
     if tile_n and not _tile_ok(tile_n, cin, hw):
