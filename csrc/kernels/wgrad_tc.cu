@@ -15,6 +15,8 @@
 // (split-K).  Partial results are added to the fp32 gradient with TMA reduce-add
 // (cp.reduce.async.bulk.tensor ... .add) straight into the gradient arena in KRSC order, i.e. the
 // buffer the peer-to-peer reduce kernels and the fused SGD read - there is no staging copy.
+#include <stdlib.h>
+
 #include "../common.cuh"
 #include "../../include/ddp_b200.h"
 #include "../runtime/tensormap.h"
@@ -51,7 +53,10 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
   constexpr int WG_TMEM_COLS = TAPS == 3 ? 256 : 64;        // TAPS x 64 used
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * WG_STAGE);
+  // barriers sit behind whichever is larger: the pipeline stages or the epilogue's fp32 staging tile
+  constexpr int EPI_BYTES = M == 128 ? TAPS * 2 * M * 128 : 0;
+  constexpr int DATA_BYTES = STAGES * WG_STAGE > EPI_BYTES ? STAGES * WG_STAGE : EPI_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + DATA_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* accum_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
@@ -211,30 +216,50 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
   prm.total_chunks = prm.chunks_per_img > 0 ? B * prm.chunks_per_img : ceil_div(B, prm.imgs_per_chunk);
   prm.Cin = Cin; prm.Cout = Cout;
   int base_ctas = (Cout / WG_M) * (Cin / WG_N) * 3;
+  // Pipeline depth: a CTA gets only about one stage's worth of TMA loads in flight whatever the depth
+  // (tools/tma_probe.py), so two stages lose nothing against four - and at ~98 KB (the epilogue's fp32
+  // staging tile sets the floor) two CTAs, or one of these and one dgrad CTA, share an SM instead of
+  // this kernel evicting the critical path's kernels from every SM it touches.
+  static int stages = 0;
+  if (!stages) {
+    const char* e = getenv("DDPB_WGRAD_STAGES");
+    stages = e ? atoi(e) : 2;
+    if (stages != 2 && stages != 3 && stages != 4) stages = 2;
+  }
+  const int per_sm = stages == 2 ? 2 : 1;
   if (split_k <= 0) {
-    // one CTA per SM: pick the split that minimises (waves) x (k-iterations per CTA + fixed cost);
-    // 150 CTAs on 148 SMs would cost a whole second wave
+    // pick the split that minimises (waves) x (k-iterations per CTA + fixed cost)
     long long best_cost = -1;
     const int max_split = prm.total_chunks < 64 ? prm.total_chunks : 64;
-    for (int s = 1; s <= max_split; ++s) {
-      long long waves = ((long long)base_ctas * s + 147) / 148;
-      long long iters = (prm.total_chunks + s - 1) / s;
-      long long cost = waves * (iters + 6);
-      if (best_cost < 0 || cost < best_cost) { best_cost = cost; split_k = s; }
+    for (int sp = 1; sp <= max_split; ++sp) {
+      long long waves = ((long long)base_ctas * sp + 148 * per_sm - 1) / (148 * per_sm);
+      long long iters = (prm.total_chunks + sp - 1) / sp;
+      long long cost = waves * (iters * per_sm + 6);        // CTAs sharing an SM share its load bandwidth
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; split_k = sp; }
     }
   }
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
   prm.dw_raw = nullptr; prm.ld_raw = 0; prm.cols_raw = 0;
-  constexpr int STAGES = 4;
-  constexpr int smem = STAGES * (WG_M / 64 + WG_TAPS) * WG_BOX + (2 * STAGES + 1) * 8 + 16 + 1024;
-  auto kern = wgrad_tc_kernel<STAGES, WG_M, WG_TAPS>;
-  static bool configured = false;
-  if (!configured) {
-    DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
   dim3 grid(base_ctas / 3, 3, split_k);
-  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmW, prm));
+  constexpr int EPI_BYTES = WG_TAPS * 2 * WG_M * 128;       // fp32 staging of the epilogue (96 KB)
+#define DDPB_WGRAD_LAUNCH(ST)                                                                                  \
+  do {                                                                                                         \
+    constexpr int pipe = ST * (WG_M / 64 + WG_TAPS) * WG_BOX;                                                  \
+    constexpr int smem = (pipe > EPI_BYTES ? pipe : EPI_BYTES) + (2 * ST + 1) * 8 + 16 + 1024;                 \
+    auto kern = wgrad_tc_kernel<ST, WG_M, WG_TAPS>;                                                            \
+    static bool configured = false;                                                                            \
+    if (!configured) {                                                                                         \
+      DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));          \
+      DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,               \
+                                           cudaSharedmemCarveoutMaxShared));                                   \
+      configured = true;                                                                                       \
+    }                                                                                                          \
+    DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmW, prm));   \
+  } while (0)
+  if (stages == 2) DDPB_WGRAD_LAUNCH(2);
+  else if (stages == 3) DDPB_WGRAD_LAUNCH(3);
+  else DDPB_WGRAD_LAUNCH(4);
+#undef DDPB_WGRAD_LAUNCH
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -262,15 +287,24 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   prm.Cin = 64; prm.Cout = Cout;
   prm.dw_raw = dw; prm.ld_raw = ld; prm.cols_raw = cols;
   const int base_ctas = Cout / 64;
-  if (split_k <= 0) split_k = 148 / base_ctas;
+  // CTA count: more CTAs per SM put more loads in flight (both operands stream from HBM), but every CTA
+  // ends with 64 x 27 atomic adds on the same addresses; measured best around one CTA per SM
+  static int ctas = 0;
+  if (!ctas) {
+    const char* e = getenv("DDPB_WGRAD0_CTAS");
+    ctas = e ? atoi(e) : 148;
+    if (ctas < 1 || ctas > 1024) ctas = 148;
+  }
+  if (split_k <= 0) split_k = ctas / base_ctas;
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
   if (split_k < 1) split_k = 1;
-  constexpr int STAGES = 8;
+  constexpr int STAGES = 2;
   constexpr int smem = STAGES * 2 * WG_BOX + (2 * STAGES + 1) * 8 + 16 + 1024;
   auto kern = wgrad_tc_kernel<STAGES, 64, 1>;
   static bool configured = false;
   if (!configured) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     configured = true;
   }
   dim3 grid(base_ctas, 1, split_k);
