@@ -140,6 +140,50 @@ im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16
   reinterpret_cast<uint4*>(cols)[i] = pk;
 }
 
+// W == 32 fast path: one block = one image row.  The three input rows it needs are staged in shared
+// memory with coalesced loads (the generic kernel's eight scattered 2-byte global loads per thread made
+// it LSU-bound: 23 us for a 33 MB write), then every thread assembles its 16-byte segment from there.
+__global__ void __launch_bounds__(256)
+im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
+                          bf16* __restrict__ w_pad, int H, int h_shift, int Cout) {
+  pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
+  __shared__ unsigned short rows[3][34 * 3];       // pixels -1..32 of rows h-1..h+1, zero outside the image
+  const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
+  const int tid = threadIdx.x;
+  const long long gi = (long long)blockIdx.x * 256 + tid;
+  if (gi < (long long)Cout * 8) {
+    const int co = (int)(gi >> 3), seg = (int)(gi & 7);
+    const unsigned short* ws = reinterpret_cast<const unsigned short*>(w) + co * 27;
+    unsigned short v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { const int k = seg * 8 + j; v[j] = k < 27 ? ws[k] : (unsigned short)0; }
+    reinterpret_cast<uint4*>(w_pad)[gi] = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+  }
+  const unsigned row = blockIdx.x;                 // (n, h)
+  const int h = (int)(row & (unsigned)(H - 1));
+  for (int i = tid; i < 3 * 96; i += 256) {
+    const int r = i / 96, e = i - r * 96;
+    const int yy = h + r - 1;
+    rows[r][3 + e] = (yy >= 0 && yy < H) ? xs[((size_t)(row + r - 1) * 32) * 3 + e] : (unsigned short)0;
+  }
+  if (tid < 18) { const int r = tid / 6, e = tid - r * 6; rows[r][e < 3 ? e : 96 + e] = 0; }
+  __syncthreads();
+  const int wx = tid >> 3, seg = tid & 7;
+  uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+  if (seg < 4) {
+    unsigned short v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = seg * 8 + j;
+      const int tap = k / 3, c = k - tap * 3;
+      const int r = tap / 3, s2 = tap - r * 3;
+      v[j] = k < 27 ? rows[r][(wx + s2) * 3 + c] : (unsigned short)0;
+    }
+    pk = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+  }
+  reinterpret_cast<uint4*>(cols)[(size_t)row * 256 + tid] = pk;
+}
+
 static int grid_for(long long n, int block, int cap = 148 * 16) {
   long long g = (n + block - 1) / block;
   if (g < 1) g = 1;
@@ -219,6 +263,12 @@ extern "C" int ddpb_im2col3x3_c3(const void* x, const void* w_bf16, void* cols, 
   while ((1 << w_shift) < W) ++w_shift;
   DDPB_REQUIRE(n_seg >= (long long)Cout * 8, "im2col3x3_c3: fewer pixels than output channels");
   const long long blocks = (n_seg + 255) / 256;
+  if (W == 32) {
+    im2col3x3_c3_row32_kernel<<<(unsigned)((long long)B * H), 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
+                                                                               (bf16*)w_pad, H, h_shift, Cout);
+    DDPB_LAUNCH_CHECK();
+    return DDPB_OK;
+  }
   im2col3x3_c3_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
                                                             (bf16*)w_pad, n_seg, H, W, h_shift, w_shift, Cout);
   DDPB_LAUNCH_CHECK();
