@@ -238,7 +238,7 @@ def conv_wgrad_tc(dy, x, split_k: int = 0, out: Optional[torch.Tensor] = None):
     return dw
 
 
-def first_layer_fwd_tc(x, w_bf16, bias, want_stats: bool = False):
+def first_layer_fwd_tc(x, w_bf16, bias, want_stats: bool = False, generic_kernel: bool = False):
     """conv3x3(3 -> Cout) on the tensor cores: im2col to [pixels][64], then a 1x1 convolution.
     Returns (y, stats | None, cols) - ``cols`` is what the weight gradient needs later."""
     b, h, w_, cin = x.shape
@@ -250,8 +250,12 @@ def first_layer_fwd_tc(x, w_bf16, bias, want_stats: bool = False):
     stats = torch.zeros(2 * cout, dtype=torch.float32, device=x.device) if want_stats else None
     check(lib().ddpb_im2col3x3_c3(ptr(x), ptr(w_bf16), ptr(cols), ptr(w_pad), b, h, w_, cout, stream_handle()),
           "im2col3x3_c3")
-    check(lib().ddpb_conv1x1_fwd_tc(ptr(cols), ptr(w_pad), ptr(bias), ptr(y), ptr(stats), b, h, w_, 64, cout,
-                                    stream_handle()), "conv1x1_fwd_tc")
+    if generic_kernel:       # the conv kernel with a single tap (one CTA per 128-pixel tile)
+        check(lib().ddpb_conv1x1_fwd_tc(ptr(cols), ptr(w_pad), ptr(bias), ptr(y), ptr(stats), b, h, w_, 64, cout,
+                                        stream_handle()), "conv1x1_fwd_tc")
+    else:                    # the multi-tile GEMM kernel the engine uses
+        check(lib().ddpb_gemm_rows_fwd_tc(ptr(cols), ptr(w_pad), ptr(bias), ptr(y), ptr(stats),
+                                          ctypes.c_longlong(b * h * w_), cout, stream_handle()), "gemm_rows_fwd_tc")
     return y, stats, cols
 
 

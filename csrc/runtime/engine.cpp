@@ -314,7 +314,7 @@ static int forward(Engine* e, int B, int training, cudaStream_t s) {
       LAUNCH(e, ddpb_conv3x3_fwd_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0, s));
     else if (use_tc_first(e, b)) {
       LAUNCH(e, ddpb_im2col3x3_c3(x, e->shadow + b.conv_w.off, e->x0cols, e->w0pad, B, b.hw, b.hw, b.cout, s));
-      LAUNCH(e, ddpb_conv1x1_fwd_tc(e->x0cols, e->w0pad, bias, b.y, st, B, b.hw, b.hw, 64, b.cout, s));
+      LAUNCH(e, ddpb_gemm_rows_fwd_tc(e->x0cols, e->w0pad, bias, b.y, st, (long long)B * b.hw * b.hw, b.cout, s));
     } else {
       LAUNCH(e, ddpb_conv3x3_fwd_simt(x, e->master + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, dt, s));
       if (st && !(b.cin == 3 && b.cout == 64)) e->counting += 1;       // separate channel_stats launch

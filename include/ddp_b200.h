@@ -166,6 +166,10 @@ int ddpb_im2col3x3_c3(const void* x_nhwc3, const void* w_bf16, void* cols, void*
                       cudaStream_t stream);
 int ddpb_conv1x1_fwd_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats, int B, int H,
                         int W, int Cin, int Cout, cudaStream_t stream);
+/* y[P][Cout] = x[P][64] * w[Cout][64]^T + bias (+ BN statistics): the first layer's forward over its patch
+ * matrix; one CTA walks several 128-row tiles with double-buffered TMEM accumulators. */
+int ddpb_gemm_rows_fwd_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats, long long P,
+                          int Cout, cudaStream_t stream);
 /* dw (fp32 [Cout][ld], columns < cols) accumulates dy^T * x_cols. */
 int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw, int B, int H, int W, int Cout, int ld, int cols,
                         int split_k, cudaStream_t stream);

@@ -286,15 +286,16 @@ def test_conv_tc_wgrad(F, R, b, hw, cin, cout, split_k):
     _report(f"tc_wgrad hw{hw} {cin}->{cout} b{b} s{split_k}", dw, R.conv_wgrad(dy, x), 2e-3)
 
 
-@pytest.mark.parametrize("b", [16, 5])
+@pytest.mark.parametrize("b", [16, 5, 37])
 @pytest.mark.parametrize("cout", [64, 128])
-def test_first_layer_tc(F, R, b, cout):
+@pytest.mark.parametrize("generic", [False, True])
+def test_first_layer_tc(F, R, b, cout, generic):
     """3-channel first layer as im2col + tensor-core GEMM: forward, BN statistics and weight gradient."""
     torch.manual_seed(15)
     x = torch.randn(b, 32, 32, 3, device=DEV).to(torch.bfloat16)
     w = (torch.randn(cout, 3, 3, 3, device=DEV) * 0.2).to(torch.bfloat16)
     bias = torch.randn(cout, device=DEV) * 0.1
-    y, stats, cols = F.first_layer_fwd_tc(x, w, bias, want_stats=True)
+    y, stats, cols = F.first_layer_fwd_tc(x, w, bias, want_stats=True, generic_kernel=generic)
     torch.cuda.synchronize()
     assert cols[..., 27:].abs().max().item() == 0
     _report(f"first_tc_fwd b{b} c{cout}", y, R.conv_fwd(x, w, bias), 6e-3)

@@ -81,7 +81,8 @@ def main():
         if cin == 3:
             line(f"first_layer_fwd (simt) {tag}", timeit(lambda: F.conv_fwd_simt(x, w32, bias, True)), flops)
             line(f"first_layer_wgrad (simt) {tag}", timeit(lambda: F.conv_wgrad_simt(dy, x)), flops)
-            total["fwd"] += line(f"first_layer_fwd im2col+tc {tag}", timeit(lambda: F.first_layer_fwd_tc(x, w16, bias, True)), flops)
+            line(f"first_layer_fwd im2col+conv1x1 {tag}", timeit(lambda: F.first_layer_fwd_tc(x, w16, bias, True, True)), flops)
+            total["fwd"] += line(f"first_layer_fwd im2col+gemm_rows {tag}", timeit(lambda: F.first_layer_fwd_tc(x, w16, bias, True)), flops)
             cols = F.first_layer_fwd_tc(x, w16, bias, True)[2]
             total["wgrad"] += line(f"first_layer_wgrad tc {tag}", timeit(lambda: F.first_layer_wgrad_tc(dy, cols)), flops)
         else:
