@@ -174,6 +174,10 @@ int ddpb_gemm_rows_fwd_tc(const void* x, const void* w_bf16, const float* bias, 
 int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw, int B, int H, int W, int Cout, int ld, int cols,
                         int split_k, cudaStream_t stream);
 
+/* Allow (1) / forbid (0) programmatic dependent launches (default: on unless DDPB_PDL=0); returns the
+ * previous setting.  They are only ever used while the launching stream is being captured. */
+int ddpb_set_pdl(int on);
+
 /* Diagnostic (csrc/kernels/tma_probe.cu, tools/tma_probe.py): per-CTA L2 -> shared-memory ingest rate of
  * the conv load patterns.  No reference counterpart. */
 int ddpb_probe_tma(int mode, int stages, int iters, int ctas, int smem_pad_kb, int cols, const void* act, const void* wgt,
