@@ -73,6 +73,10 @@ def test_fp32_engine_matches_torch_training(no_tf32, graph):
         # training is chaotic: rounding-level differences grow step by step (torch itself is not
         # run-to-run reproducible at the 1e-3 level by step 3)
         tol = 2e-3 if step < 2 else 3e-2
+        if step == 0:       # diagnostic: which tensors differ most after the first update
+            sd_t, sd_n = tb.state_dict(), nb.state_dict()
+            worst = sorted(((_rel(sd_n[k], sd_t[k]), k) for k in sd_t if "num_batches" not in k), reverse=True)[:3]
+            print("[eng] fp32 after step 0, largest relative differences: " + ", ".join(f"{k} {r:.2e}" for r, k in worst))
         assert abs(float(lt) - float(ln)) < tol * max(1.0, abs(float(lt))), step
     sd_t, sd_n = tb.state_dict(), nb.state_dict()
     assert list(sd_t.keys()) == list(sd_n.keys())
