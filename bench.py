@@ -278,15 +278,26 @@ def run_ours(args) -> dict:
 
     def steps(n, e2e):
         last = None
+        if e2e:
+            # The public pipeline a training loop uses: every step copies ITS batch from pinned host memory
+            # (stage -> copy stream, overlapping the previous step), runs the augmentation kernel and the
+            # step, and copies ITS loss to pinned host memory; the host reads loss i after it has queued
+            # step i + 1, so the GPU never waits for Python.
+            staged = be.stage(RawBatch(*host[0]))
+            pending = None
+            for i in range(n):
+                data, target = be.prepare(staged)
+                handle = be.loss_to_host(be.train_step(data, target, timer))   # D2H of this step's loss
+                if i + 1 < n:
+                    staged = be.stage(RawBatch(*host[(i + 1) % len(host)]))      # H2D of the next step's batch
+                if pending is not None:
+                    last = pending.item()
+                pending = handle
+            last = pending.item()
+            return last
         for i in range(n):
-            if e2e:
-                hb = host[i % len(host)]
-                raw = RawBatch(*[t.cuda(non_blocking=True) for t in hb])
-                data, target = be.prepare(raw)
-                last = float(be.train_step(data, target, timer))          # D2H read of the loss, every step
-            else:
-                data, target = prepared[i % len(prepared)]
-                last = be.train_step(data, target, timer)
+            data, target = prepared[i % len(prepared)]
+            last = be.train_step(data, target, timer)
         return last
 
     def timed(e2e):

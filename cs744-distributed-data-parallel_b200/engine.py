@@ -78,6 +78,19 @@ def _view(address: int, numel: int, dtype: torch.dtype, device: torch.device) ->
     return nv.DeviceBuffer(address, nbytes).as_tensor(device).view(dtype)
 
 
+class HostScalar:
+    """A scalar on its way to pinned host memory (``NativeBackend.loss_to_host``)."""
+
+    def __init__(self, buf: torch.Tensor, index: int, event: "torch.cuda.Event") -> None:
+        self._buf, self._index, self._event = buf, index, event
+
+    def item(self) -> float:
+        self._event.synchronize()
+        return float(self._buf[self._index])
+
+    __float__ = item
+
+
 class NativeBackend:
     name = "native"
 
@@ -243,10 +256,70 @@ class NativeBackend:
         cur.wait_stream(self.stream)
 
     # ---- data --------------------------------------------------------------------------------------
+    def stage(self, batch: RawBatch) -> RawBatch:
+        """Start the host -> device copy of a (pinned) host batch on the backend's copy stream and return
+        the device batch; ``prepare`` orders itself after the copy.  Two staging slots alternate, so the
+        copy of batch i+1 runs while step i computes (the loader's prefetch; the reference gets the
+        same effect from ``DataLoader`` workers, ref ``Part 1/main.py:53-58``)."""
+        n = batch.size
+        if n > self.max_batch:
+            raise nv.NativeError(f"batch {n} exceeds the engine's max batch {self.max_batch}")
+        if not hasattr(self, "_stage_slots"):
+            dev, mb = self.device, self.max_batch
+            self._copy_stream = torch.cuda.Stream(dev)
+            self._stage_slots = [dict(images=torch.empty((mb, 32, 32, 3), dtype=torch.uint8, device=dev),
+                                labels=torch.empty(mb, dtype=torch.int64, device=dev),
+                                crop=torch.empty((mb, 2), dtype=torch.int32, device=dev),
+                                flip=torch.empty(mb, dtype=torch.uint8, device=dev),
+                                ready=torch.cuda.Event(), consumed=None) for _ in range(2)]
+            self._slot_next = 0
+        slot = self._stage_slots[self._slot_next]
+        self._slot_next ^= 1
+        cs = self._copy_stream
+        if slot["consumed"] is not None:
+            cs.wait_event(slot["consumed"])           # the augmentation kernel that read this slot has run
+        with torch.cuda.stream(cs):
+            slot["images"][:n].copy_(batch.images, non_blocking=True)
+            slot["labels"][:n].copy_(batch.labels, non_blocking=True)
+            if batch.crop_xy is not None:
+                slot["crop"][:n].copy_(batch.crop_xy, non_blocking=True)
+            if batch.flip is not None:
+                slot["flip"][:n].copy_(batch.flip, non_blocking=True)
+            slot["ready"].record(cs)
+        out = RawBatch(slot["images"][:n], slot["labels"][:n],
+                       None if batch.crop_xy is None else slot["crop"][:n],
+                       None if batch.flip is None else slot["flip"][:n])
+        out._slot = slot                                # prepare() waits for `ready` and marks `consumed`
+        return out
+
+    def loss_to_host(self, loss: torch.Tensor) -> "HostScalar":
+        """Queue a device -> host copy of a step's loss into pinned memory; ``.item()`` on the result
+        waits for that copy only, so the host can queue the next step before it reads this one."""
+        if not hasattr(self, "_loss_host"):
+            self._loss_host = torch.empty(4, dtype=torch.float32).pin_memory()
+            self._loss_ev = [torch.cuda.Event() for _ in range(4)]
+            self._loss_next = 0
+        k = self._loss_next
+        self._loss_next = (k + 1) % 4
+        with self.on_stream():
+            self._loss_host[k:k + 1].copy_(loss.reshape(1), non_blocking=True)
+            self._loss_ev[k].record(torch.cuda.current_stream(self.device))
+        return HostScalar(self._loss_host, k, self._loss_ev[k])
+
     def prepare(self, batch: RawBatch) -> Tuple[torch.Tensor, torch.Tensor]:
         n = batch.size
         if n > self.max_batch:
             raise nv.NativeError(f"batch {n} exceeds the engine's max batch {self.max_batch}")
+        slot = getattr(batch, "_slot", None)
+        if slot is not None:                            # staged batch: order after its copy, release the slot after use
+            with self.on_stream():
+                cur = torch.cuda.current_stream(self.device)
+                cur.wait_event(slot["ready"])
+                F.augment(batch.images, None, batch.crop_xy, batch.flip, self.dtype, out=self.input, batch=n)
+                self.target[:n].copy_(batch.labels, non_blocking=True)
+                slot["consumed"] = torch.cuda.Event()
+                slot["consumed"].record(cur)
+            return self.input[:n], self.target[:n]
         with self.on_stream():
             b = batch.to(self.device)
             F.augment(b.images, None, b.crop_xy, b.flip, self.dtype, out=self.input, batch=n)

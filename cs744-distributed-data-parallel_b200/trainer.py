@@ -115,6 +115,22 @@ class Trainer:
         with self._stream_ctx():
             return self._evaluate()
 
+    def _prefetched(self, loader):
+        """One batch ahead: with a backend that can ``stage`` (the native engine on a GPU), the host ->
+        device copy of batch i+1 is queued on its copy stream before step i is, and overlaps it."""
+        stage = getattr(self.backend, "stage", None)
+        if stage is None or self.device.type != "cuda":
+            yield from loader
+            return
+        ahead = None
+        for raw in loader:
+            cur = stage(raw) if raw.images.device.type == "cpu" else raw
+            if ahead is not None:
+                yield ahead
+            ahead = cur
+        if ahead is not None:
+            yield ahead
+
     def _train_epoch(self, epoch: int = 0) -> List[Dict]:
         cfg, be, timer, log = self.cfg, self.backend, self.timer, self.logger
         if not (cfg.reproduce_eval_mode_quirk and epoch > 0):
@@ -123,7 +139,7 @@ class Trainer:
         loss_acc = None
         host_times: List[Tuple[float, float, float]] = []
         iter_number = 1
-        for raw in self.train_loader:
+        for raw in self._prefetched(self.train_loader):
             data, target = be.prepare(raw)
             loss = be.train_step(data, target, timer)
             loss_acc = loss if loss_acc is None else loss_acc + loss
