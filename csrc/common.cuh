@@ -45,10 +45,23 @@ static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) 
 // while its predecessor on the stream is still running, so its prologue (barrier init, TMEM
 // allocation, descriptor prefetch, index math) and the launch latency overlap the predecessor's tail
 // (applied while a CUDA graph is being captured only, see launch_ex).
-// Such a kernel MUST execute pdl_wait() before its first access to global memory; every kernel calls
-// pdl_launch_dependents() early so that ITS successor can be scheduled.  DDPB_PDL=0 disables it.
+// Such a kernel MUST execute pdl_wait() before its first access to global memory; while capturing, every
+// kernel calls pdl_launch_dependents() early so that ITS successor can be scheduled.  DDPB_PDL=0 disables it.
 bool pdl_enabled();
 int pdl_mask();         // DDPB_PDL_MASK: bit per kernel family (debugging aid), default all ones
+
+// Is programmatic dependent launch in effect for a kernel of `family` launched on `stream` right now?
+// Only inside a stream capture: there every dependency (events between the engine's streams included)
+// becomes an explicit graph edge.  In plain stream order a kernel that executes
+// griddepcontrol.launch_dependents releases the NEXT kernel of the stream early even when that kernel
+// was launched normally and never waits (measured: the SIMT dgrad read a half-written dY and the
+// gradients of every earlier layer were ~1 % off in most runs), so eager runs neither set the launch
+// attribute nor execute the trigger: kernels take the answer as a parameter (`if (pdl) pdl_launch_dependents()`).
+static inline int pdl_active(cudaStream_t stream, int family) {
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  return family && pdl_enabled() && (pdl_mask() & family) && cudaStreamIsCapturing(stream, &cap) == cudaSuccess &&
+         cap == cudaStreamCaptureStatusActive;
+}
 
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
@@ -63,13 +76,7 @@ static inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 bloc
     attr[n].val.clusterDim.x = cluster.x; attr[n].val.clusterDim.y = cluster.y; attr[n].val.clusterDim.z = cluster.z;
     ++n;
   }
-  // Only inside a stream capture: there every dependency (events between the engine's streams included)
-  // becomes an explicit graph edge.  In plain stream order, mixing programmatic launches with the
-  // event waits of the three-stream backward gave slightly wrong gradients (measured), so eager runs
-  // keep ordinary launches.
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (pdl && pdl_enabled() && (pdl_mask() & pdl) && cudaStreamIsCapturing(stream, &cap) == cudaSuccess &&
-      cap == cudaStreamCaptureStatusActive) {
+  if (pdl_active(stream, pdl)) {
     attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[n].val.programmaticStreamSerializationAllowed = 1;
     ++n;
@@ -131,6 +138,16 @@ template <> __device__ __forceinline__ void load_vec_coh<bf16>(const bf16* p, fl
   out[4] = c.x; out[5] = c.y; out[6] = d.x; out[7] = d.y;
 }
 __device__ __forceinline__ float ld_coh(const float* p) { return __ldca(p); }
+// N (multiple of 4) consecutive floats with 16-byte loads: per-channel parameters of a thread's channel
+// group (scalar loads made the BatchNorm kernels load-instruction bound: 32-48 of them per thread)
+template <int N>
+__device__ __forceinline__ void ld_coh_vec(const float* p, float* out) {
+#pragma unroll
+  for (int i = 0; i < N; i += 4) {
+    const float4 v = __ldca(reinterpret_cast<const float4*>(p + i));
+    out[i] = v.x; out[i + 1] = v.y; out[i + 2] = v.z; out[i + 3] = v.w;
+  }
+}
 __device__ __forceinline__ float ld_coh_any(const float* p) { return __ldca(p); }
 __device__ __forceinline__ bf16 ld_coh_any(const bf16* p) {
   unsigned short u = __ldca(reinterpret_cast<const unsigned short*>(p));

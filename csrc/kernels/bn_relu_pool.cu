@@ -77,7 +77,7 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
               const float* __restrict__ beta, T* __restrict__ out, float* __restrict__ save_mean,
               float* __restrict__ save_invstd, float* __restrict__ running_mean,
               float* __restrict__ running_var, long long* __restrict__ nbt, T* __restrict__ winner,
-              long long P, long long Pout, int C, int H, int W, float eps, float momentum, int training) {
+              long long P, long long Pout, int C, int H, int W, float eps, float momentum, int training, int pdl) {
   constexpr int V = VecOf<T>::N;
   const int groups = C / V;
   const int g = threadIdx.x % groups;
@@ -85,29 +85,36 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
-  pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
 
   float sc[V], sh[V];
+  {
+    float a[V], b[V], ga[V], be[V];
+    if (training) { ld_coh_vec<V>(stats + c0, a); ld_coh_vec<V>(stats + C + c0, b); }
+    else { ld_coh_vec<V>(running_mean + c0, a); ld_coh_vec<V>(running_var + c0, b); }
+    ld_coh_vec<V>(gamma + c0, ga);
+    ld_coh_vec<V>(beta + c0, be);
 #pragma unroll
-  for (int j = 0; j < V; ++j) {
-    float mean, var;
-    if (training) {
-      mean = ld_coh(&stats[c0 + j]) / (float)P;
-      var = fmaxf(ld_coh(&stats[C + c0 + j]) / (float)P - mean * mean, 0.f);
-    } else {
-      mean = ld_coh(&running_mean[c0 + j]);
-      var = ld_coh(&running_var[c0 + j]);
-    }
-    float invstd = rsqrtf(var + eps);
-    sc[j] = ld_coh(&gamma[c0 + j]) * invstd;
-    sh[j] = ld_coh(&beta[c0 + j]) - mean * sc[j];
-    if (training && blockIdx.x == 0 && pl == 0) {
-      save_mean[c0 + j] = mean;
-      save_invstd[c0 + j] = invstd;
-      float unbiased = P > 1 ? var * ((float)P / (float)(P - 1)) : var;
-      running_mean[c0 + j] = (1.f - momentum) * ld_coh(&running_mean[c0 + j]) + momentum * mean;
-      running_var[c0 + j] = (1.f - momentum) * ld_coh(&running_var[c0 + j]) + momentum * unbiased;
+    for (int j = 0; j < V; ++j) {
+      float mean, var;
+      if (training) {
+        mean = a[j] / (float)P;
+        var = fmaxf(b[j] / (float)P - mean * mean, 0.f);
+      } else {
+        mean = a[j];
+        var = b[j];
+      }
+      float invstd = rsqrtf(var + eps);
+      sc[j] = ga[j] * invstd;
+      sh[j] = be[j] - mean * sc[j];
+      if (training && blockIdx.x == 0 && pl == 0) {
+        save_mean[c0 + j] = mean;
+        save_invstd[c0 + j] = invstd;
+        float unbiased = P > 1 ? var * ((float)P / (float)(P - 1)) : var;
+        running_mean[c0 + j] = (1.f - momentum) * ld_coh(&running_mean[c0 + j]) + momentum * mean;
+        running_var[c0 + j] = (1.f - momentum) * ld_coh(&running_var[c0 + j]) + momentum * unbiased;
+      }
     }
   }
   if (training && blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
@@ -144,7 +151,7 @@ __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const float* __restrict__ mean,
                      const float* __restrict__ invstd, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float* __restrict__ sums, long long Pout, int C, int H,
-                     int W) {
+                     int W, int pdl) {
   constexpr int V = VecOf<T>::N;
   extern __shared__ float sm[];      // [ppb*C]
   const int groups = C / V;
@@ -153,14 +160,17 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
-  pdl_launch_dependents();
+  if (pdl) pdl_launch_dependents();
   pdl_wait();
   float sc[V], sh[V], mu[V], is[V], a1[V], a2[V];
+  ld_coh_vec<V>(mean + c0, mu);
+  ld_coh_vec<V>(invstd + c0, is);
+  ld_coh_vec<V>(gamma + c0, sc);
+  ld_coh_vec<V>(beta + c0, sh);
 #pragma unroll
   for (int j = 0; j < V; ++j) {
-    mu[j] = ld_coh(&mean[c0 + j]); is[j] = ld_coh(&invstd[c0 + j]);
-    sc[j] = ld_coh(&gamma[c0 + j]) * is[j];
-    sh[j] = ld_coh(&beta[c0 + j]) - mu[j] * sc[j];
+    sc[j] *= is[j];
+    sh[j] -= mu[j] * sc[j];
     a1[j] = 0.f; a2[j] = 0.f;
   }
   if (pl < ppb) {
@@ -204,7 +214,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ sums, T* __restrict__ dy,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
-                    long long P, long long Pout, int C, int H, int W) {
+                    long long P, long long Pout, int C, int H, int W, int pdl) {
   constexpr int V = VecOf<T>::N;
   extern __shared__ float sm[];      // [ppb*C]
   const int groups = C / V;
@@ -213,18 +223,25 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
-  pdl_launch_dependents();
+  if (pdl) pdl_launch_dependents();
   pdl_wait();
   // dy = sc * (dz - k1 - xhat * k2) with xhat = (y - mu) * is, written as  sc * dz + cb - cy * y:
   // four per-channel constants instead of seven keep the pooled variant at two blocks per SM
   float sc[V], sh[V], cb[V], cy[V], ab[V];
   const float invP = 1.f / (float)P;
+  ld_coh_vec<V>(gamma + c0, sc);
+  ld_coh_vec<V>(beta + c0, sh);
+  ld_coh_vec<V>(mean + c0, cb);          // cb / cy / ab double as staging for mean / invstd / sums
+  ld_coh_vec<V>(invstd + c0, cy);
+  float s1v[V], s2v[V];
+  ld_coh_vec<V>(sums + c0, s1v);
+  ld_coh_vec<V>(sums + C + c0, s2v);
 #pragma unroll
   for (int j = 0; j < V; ++j) {
-    const float mu = ld_coh(&mean[c0 + j]), is = ld_coh(&invstd[c0 + j]);
-    sc[j] = ld_coh(&gamma[c0 + j]) * is;
-    sh[j] = ld_coh(&beta[c0 + j]) - mu * sc[j];
-    const float s1 = ld_coh(&sums[c0 + j]), s2 = ld_coh(&sums[C + c0 + j]);
+    const float mu = cb[j], is = cy[j];
+    sc[j] *= is;
+    sh[j] -= mu * sc[j];
+    const float s1 = s1v[j], s2 = s2v[j];
     cy[j] = sc[j] * is * (s2 * invP);
     cb[j] = cy[j] * mu - sc[j] * (s1 * invP);
     ab[j] = 0.f;
@@ -365,7 +382,8 @@ int fwd_launch(const void* y, const float* stats, const float* gamma, const floa
   int ppb = 256 / (C / VecOf<T>::N);
   DDPB_CUDA_CHECK(launch_ex(bn_fwd_kernel<T, POOL>, dim3(bn_grid(bn_fwd_kernel<T, POOL>, Pout, ppb, 0)), dim3(256), 0,
                             stream, dim3(1, 1, 1), 4, (const T*)y, stats, gamma, beta, (T*)out, save_mean,
-                            save_invstd, rm, rv, nbt, (T*)winner, P, Pout, C, H, W, eps, momentum, training));
+                            save_invstd, rm, rv, nbt, (T*)winner, P, Pout, C, H, W, eps, momentum, training,
+                            pdl_active(stream, 4)));
   return DDPB_OK;
 }
 
@@ -381,10 +399,11 @@ int bwd_launch(const void* dout, const void* y, const float* mean, const float* 
   if (reduce)
     DDPB_CUDA_CHECK(launch_ex(bn_bwd_reduce_kernel<T, POOL>, dim3(bn_grid(bn_bwd_reduce_kernel<T, POOL>, Pout, ppb, smem)),
                               dim3(256), smem, stream, dim3(1, 1, 1), 8, (const T*)dout, (const T*)y, mean, invstd,
-                              gamma, beta, sums, Pout, C, H, W));
+                              gamma, beta, sums, Pout, C, H, W, pdl_active(stream, 8)));
   DDPB_CUDA_CHECK(launch_ex(bn_bwd_apply_kernel<T, POOL>, dim3(bn_grid(bn_bwd_apply_kernel<T, POOL>, Pout, ppb, smem)),
                             dim3(256), smem, stream, dim3(1, 1, 1), 16, (const T*)dout, (const T*)y, mean, invstd,
-                            gamma, beta, (const float*)sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C, H, W));
+                            gamma, beta, (const float*)sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C, H, W,
+                            pdl_active(stream, 16)));
   return DDPB_OK;
 }
 

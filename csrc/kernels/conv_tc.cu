@@ -42,6 +42,7 @@ struct ConvTcParams {
   int k_total_cols;        // fprop: Cin (column stride between taps in the weight matrix)
   int slice_dim;           // NC > 1: tensor dimension (2 = h, 3 = n) along which the A box is cut into NC slices
   int slice_extent;        // NC > 1: extent of one slice along slice_dim
+  int pdl;                 // 1: execute griddepcontrol.launch_dependents (captured launches only, see common.cuh)
   int taps;                // 9 = 3x3 filter, 1 = 1x1 (plain GEMM over the pixel rows; first-layer patch matrix)
   bf16* out_raw;           // output matrix [total_pixels][n_out]
   int w_shift, h_shift;    // log2(W), log2(H)
@@ -121,7 +122,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 1) tmem_alloc<BN>(tmem_slot);
   // everything above is private to this CTA and overlaps the previous kernel's tail (programmatic
   // dependent launch); global memory may only be touched after pdl_wait()
-  pdl_launch_dependents();
+  if (prm.pdl) pdl_launch_dependents();
   pdl_wait();
   if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? ld_coh(&bias[n_tile * BN + i]) : 0.f;
   tc_fence_before();
@@ -282,12 +283,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; sc[j] = 0.f; sh[j] = 0.f; mu[j] = 0.f; is[j] = 0.f; }
     if (bn_red) {
+      ld_coh_vec<8>(prm.bn_mean + col0, mu);
+      ld_coh_vec<8>(prm.bn_invstd + col0, is);
+      ld_coh_vec<8>(prm.bn_gamma + col0, sc);
+      ld_coh_vec<8>(prm.bn_beta + col0, sh);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        mu[j] = ld_coh(&prm.bn_mean[col0 + j]); is[j] = ld_coh(&prm.bn_invstd[col0 + j]);
-        sc[j] = ld_coh(&prm.bn_gamma[col0 + j]) * is[j];
-        sh[j] = ld_coh(&prm.bn_beta[col0 + j]) - mu[j] * sc[j];
-      }
+      for (int j = 0; j < 8; ++j) { sc[j] *= is[j]; sh[j] -= mu[j] * sc[j]; }
     }
 #pragma unroll
     for (int k = 0; k < CH; ++k) {
@@ -539,6 +540,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
       g_bnfwd.applied = true;
     }
   }
+  prm.pdl = pdl_active(stream, 1);
   DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, NC, KS), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;

@@ -103,8 +103,8 @@ __global__ void nchw_to_nhwc_kernel(const TI* __restrict__ src, TO* __restrict__
 // Cout*8 threads also lay the [Cout][27] bf16 weights out as [Cout][64] (zero padded).
 __global__ void __launch_bounds__(256)
 im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
-                    bf16* __restrict__ w_pad, long long n_seg, int H, int W, int h_shift, int w_shift, int Cout) {
-  pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
+                    bf16* __restrict__ w_pad, long long n_seg, int H, int W, int h_shift, int w_shift, int Cout, int pdl) {
+  if (pdl) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
   if (i < (long long)Cout * 8) {
@@ -145,8 +145,8 @@ im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16
 // it LSU-bound: 23 us for a 33 MB write), then every thread assembles its 16-byte segment from there.
 __global__ void __launch_bounds__(256)
 im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
-                          bf16* __restrict__ w_pad, int H, int h_shift, int Cout) {
-  pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
+                          bf16* __restrict__ w_pad, int H, int h_shift, int Cout, int pdl) {
+  if (pdl) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
   __shared__ unsigned short rows[3][34 * 3];       // pixels -1..32 of rows h-1..h+1, zero outside the image
   const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
   const int tid = threadIdx.x;
@@ -265,12 +265,12 @@ extern "C" int ddpb_im2col3x3_c3(const void* x, const void* w_bf16, void* cols, 
   const long long blocks = (n_seg + 255) / 256;
   if (W == 32) {
     im2col3x3_c3_row32_kernel<<<(unsigned)((long long)B * H), 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
-                                                                               (bf16*)w_pad, H, h_shift, Cout);
+                                                                               (bf16*)w_pad, H, h_shift, Cout, pdl_active(stream, 64));
     DDPB_LAUNCH_CHECK();
     return DDPB_OK;
   }
   im2col3x3_c3_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
-                                                            (bf16*)w_pad, n_seg, H, W, h_shift, w_shift, Cout);
+                                                            (bf16*)w_pad, n_seg, H, W, h_shift, w_shift, Cout, pdl_active(stream, 64));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

@@ -19,9 +19,9 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ bias,
                  const int64_t* __restrict__ target, float* __restrict__ logits, float* __restrict__ dlogits,
-                 float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch) {
+                 float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch, int pdl) {
   __shared__ float ws[NCLS * FEAT];
-  pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
   for (int i = threadIdx.x; i < NCLS * FEAT; i += blockDim.x) ws[i] = ld_coh(&w[i]);   // ld.global.cg: see load_vec_coh in common.cuh
   __syncthreads();
@@ -68,8 +68,8 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
 template <typename T>
 __global__ void __launch_bounds__(256)
 fc_bwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ dlogits,
-              T* __restrict__ dact, float* __restrict__ dw, float* __restrict__ db, int batch, int blocks_da) {
-  pdl_launch_dependents();     // launched normally itself (it follows the gradient memset)
+              T* __restrict__ dact, float* __restrict__ dw, float* __restrict__ db, int batch, int blocks_da, int pdl) {
+  if (pdl) pdl_launch_dependents();     // launched normally itself (it follows the gradient memset)
   if ((int)blockIdx.x < blocks_da) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= batch * FEAT) return;
@@ -114,11 +114,11 @@ extern "C" int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias
   if (dtype == DDPB_BF16)
     DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<bf16>, dim3(blocks), dim3(256), 0, stream, dim3(1, 1, 1), 32,
                               (const bf16*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
-                              batch, inv));
+                              batch, inv, pdl_active(stream, 32)));
   else
     DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<float>, dim3(blocks), dim3(256), 0, stream, dim3(1, 1, 1), 32,
                               (const float*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
-                              batch, inv));
+                              batch, inv, pdl_active(stream, 32)));
   return DDPB_OK;
 }
 
@@ -129,10 +129,10 @@ extern "C" int ddpb_fc_bwd(const void* act, const float* w, const float* dlogits
   int blocks_dw = ceil_div(NCLS * FEAT + NCLS, 256) * ceil_div(batch, FC_SLICE);
   if (dtype == DDPB_BF16)
     fc_bwd_kernel<bf16><<<blocks_da + blocks_dw, 256, 0, stream>>>((const bf16*)act, w, dlogits, (bf16*)dact, dw,
-                                                                  db, batch, blocks_da);
+                                                                  db, batch, blocks_da, pdl_active(stream, 64));
   else
     fc_bwd_kernel<float><<<blocks_da + blocks_dw, 256, 0, stream>>>((const float*)act, w, dlogits, (float*)dact,
-                                                                   dw, db, batch, blocks_da);
+                                                                   dw, db, batch, blocks_da, pdl_active(stream, 64));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

@@ -28,6 +28,7 @@ struct GemmRowsParams {
   int n_out;               // Cout (row pitch of y)
   int tiles;               // ceil(P / 128)
   int mt;                  // row tiles per CTA
+  int pdl;                 // 1: execute griddepcontrol.launch_dependents (captured launches only)
   bf16* y;
 };
 
@@ -61,7 +62,7 @@ gemm_rows_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<2 * GR_N>(tmem_slot);
-  pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (prm.pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
   for (int i = threadIdx.x; i < GR_N; i += blockDim.x) bias_s[i] = bias ? ld_coh(&bias[n_tile * GR_N + i]) : 0.f;
   tc_fence_before();
@@ -195,6 +196,7 @@ extern "C" int ddpb_gemm_rows_fwd_tc(const void* x, const void* w_bf16, const fl
                                          cudaSharedmemCarveoutMaxShared));
     configured = true;
   }
+  prm.pdl = pdl_active(stream, 1);
   DDPB_CUDA_CHECK(launch_ex(gemm_rows_tc_kernel, grid, dim3(192), smem, stream, dim3(1, 1, 1), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;

@@ -38,6 +38,7 @@ struct WgradParams {
   int Cin, Cout;
   float* dw_raw;        // M == 64 variant: gradient matrix [64][ld_raw], columns < cols_raw are accumulated
   int ld_raw, cols_raw;
+  int pdl;              // 1: execute griddepcontrol.launch_dependents (captured launches only)
 };
 
 void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn);   // conv_tc.cu
@@ -78,7 +79,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<WG_TMEM_COLS>(tmem_slot);
-  pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (prm.pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
   tc_fence_before();
   __syncthreads();
@@ -240,6 +241,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
   }
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
   prm.dw_raw = nullptr; prm.ld_raw = 0; prm.cols_raw = 0;
+  prm.pdl = pdl_active(stream, 2);
   dim3 grid(base_ctas / 3, 3, split_k);
   constexpr int EPI_BYTES = WG_TAPS * 2 * WG_M * 128;       // fp32 staging of the epilogue (96 KB)
 #define DDPB_WGRAD_LAUNCH(ST)                                                                                  \
@@ -286,6 +288,7 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   prm.total_chunks = B * prm.chunks_per_img;
   prm.Cin = 64; prm.Cout = Cout;
   prm.dw_raw = dw; prm.ld_raw = ld; prm.cols_raw = cols;
+  prm.pdl = pdl_active(stream, 2);
   const int base_ctas = Cout / 64;
   // CTA count: more CTAs per SM put more loads in flight (both operands stream from HBM), but every CTA
   // ends with 64 x 27 atomic adds on the same addresses; measured best around one CTA per SM

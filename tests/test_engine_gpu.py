@@ -275,3 +275,31 @@ def test_staged_batches_and_async_loss_match_the_direct_path():
         # bf16 + atomics: two runs of the same training drift apart step by step (see the bf16 test above)
         tol = 5e-3 if step == 0 else (3e-2 if step == 1 else 0.15)
         assert abs(a - b) < tol * max(1.0, abs(a)), (step, a, b)
+
+
+def test_first_update_is_reproducible_across_fresh_engines(no_tf32):
+    """Regression test for a stream-order race: kernels that executed griddepcontrol.launch_dependents
+    released the next, normally launched kernel early, and in ~80 % of eager fp32 runs the SIMT dgrad read a
+    half-written dY (every earlier layer's gradient ~1 % off).  Same weights + same batch must give the
+    same first update every time, up to the order of the floating-point atomics."""
+    from cs744_ddp_b200.backends import TorchBackend
+    from cs744_ddp_b200.engine import NativeBackend
+    torch.manual_seed(0)
+    tb = TorchBackend(_cfg(backend="torch", dtype="fp32", global_batch=16), DEV)
+    init = {k: v.clone() for k, v in tb.state_dict().items()}
+    raw = _batches(1, 16)[0]
+    ref = None
+    for it in range(8):
+        nb = NativeBackend(_cfg(backend="native", dtype="fp32", use_cuda_graph=False, global_batch=16), DEV,
+                           init_state=init)
+        nb.train_step(*nb.prepare(raw), _T())
+        torch.cuda.synchronize()
+        # BatchNorm biases start at zero, so their value after one step IS the (scaled) gradient
+        cur = {k: v.float().clone() for k, v in nb.state_dict().items() if k.endswith(".bias") and "layers" in k
+               and int(k.split(".")[1]) in (1, 5, 9, 12, 16, 19, 23, 26)}
+        if ref is None:
+            ref = cur
+        else:
+            worst = max((_rel(cur[k], ref[k]), k) for k in cur)
+            assert worst[0] < 1e-4, (it, worst)
+        del nb
