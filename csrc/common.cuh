@@ -51,12 +51,9 @@ bool pdl_enabled();
 int pdl_mask();         // DDPB_PDL_MASK: bit per kernel family (debugging aid), default all ones
 
 // Is programmatic dependent launch in effect for a kernel of `family` launched on `stream` right now?
-// Only inside a stream capture: there every dependency (events between the engine's streams included)
-// becomes an explicit graph edge.  In plain stream order a kernel that executes
-// griddepcontrol.launch_dependents releases the NEXT kernel of the stream early even when that kernel
-// was launched normally and never waits (measured: the SIMT dgrad read a half-written dY and the
-// gradients of every earlier layer were ~1 % off in most runs), so eager runs neither set the launch
-// attribute nor execute the trigger: kernels take the answer as a parameter (`if (pdl) pdl_launch_dependents()`).
+// Only inside a stream capture (the product path), where every dependency - the events between the
+// engine's streams included - is an explicit graph edge.  Eager runs keep ordinary launches and do not
+// execute the trigger either: kernels take the answer as a parameter (`if (pdl) pdl_launch_dependents()`).
 static inline int pdl_active(cudaStream_t stream, int family) {
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   return family && pdl_enabled() && (pdl_mask() & family) && cudaStreamIsCapturing(stream, &cap) == cudaSuccess &&
@@ -86,6 +83,11 @@ static inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 bloc
 }
 
 typedef __nv_bfloat16 bf16;
+
+// cache operator of the "coherent" loads (see load_vec_coh): ld.global.ca; ld.global.cg was measured slower and no more correct
+#ifndef DDPB_LD_COH
+#define DDPB_LD_COH __ldca
+#endif
 
 // ------------------------------------------------------------------------------------------
 // scalar / vector conversion helpers
@@ -128,29 +130,29 @@ template <> __device__ __forceinline__ void load_vec<bf16>(const bf16* p, float*
 // compiles to LDG.STRONG.GPU, which made the BatchNorm kernels ~2x slower.
 template <typename T> __device__ __forceinline__ void load_vec_coh(const T* p, float* out);
 template <> __device__ __forceinline__ void load_vec_coh<float>(const float* p, float* out) {
-  float4 v = __ldca(reinterpret_cast<const float4*>(p));
+  float4 v = DDPB_LD_COH(reinterpret_cast<const float4*>(p));
   out[0] = v.x; out[1] = v.y; out[2] = v.z; out[3] = v.w;
 }
 template <> __device__ __forceinline__ void load_vec_coh<bf16>(const bf16* p, float* out) {
-  uint4 v = __ldca(reinterpret_cast<const uint4*>(p));
+  uint4 v = DDPB_LD_COH(reinterpret_cast<const uint4*>(p));
   float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z), d = unpack_bf16x2(v.w);
   out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
   out[4] = c.x; out[5] = c.y; out[6] = d.x; out[7] = d.y;
 }
-__device__ __forceinline__ float ld_coh(const float* p) { return __ldca(p); }
+__device__ __forceinline__ float ld_coh(const float* p) { return DDPB_LD_COH(p); }
 // N (multiple of 4) consecutive floats with 16-byte loads: per-channel parameters of a thread's channel
 // group (scalar loads made the BatchNorm kernels load-instruction bound: 32-48 of them per thread)
 template <int N>
 __device__ __forceinline__ void ld_coh_vec(const float* p, float* out) {
 #pragma unroll
   for (int i = 0; i < N; i += 4) {
-    const float4 v = __ldca(reinterpret_cast<const float4*>(p + i));
+    const float4 v = DDPB_LD_COH(reinterpret_cast<const float4*>(p + i));
     out[i] = v.x; out[i + 1] = v.y; out[i + 2] = v.z; out[i + 3] = v.w;
   }
 }
-__device__ __forceinline__ float ld_coh_any(const float* p) { return __ldca(p); }
+__device__ __forceinline__ float ld_coh_any(const float* p) { return DDPB_LD_COH(p); }
 __device__ __forceinline__ bf16 ld_coh_any(const bf16* p) {
-  unsigned short u = __ldca(reinterpret_cast<const unsigned short*>(p));
+  unsigned short u = DDPB_LD_COH(reinterpret_cast<const unsigned short*>(p));
   return *reinterpret_cast<bf16*>(&u);
 }
 template <typename T> __device__ __forceinline__ void store_vec(T* p, const float* in);

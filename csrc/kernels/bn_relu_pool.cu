@@ -17,6 +17,23 @@ namespace ddpb {
 
 template <typename T> struct VecOf { static constexpr int N = 16 / sizeof(T); };
 
+// 16 raw bytes (8 bf16 or 4 fp32) fetched with a coherent load; unpacked to floats when used.  Keeping the
+// packed form lets the kernels issue the NEXT iteration's loads (and the first iteration's, before the
+// per-channel constants are even read) without doubling their register count.
+struct Raw16 { uint4 u; };
+template <typename T> __device__ __forceinline__ Raw16 ld_raw(const T* p) {
+  Raw16 r; r.u = DDPB_LD_COH(reinterpret_cast<const uint4*>(p)); return r;
+}
+template <typename T> __device__ __forceinline__ void unpack_raw(const Raw16& r, float* out);
+template <> __device__ __forceinline__ void unpack_raw<float>(const Raw16& r, float* out) {
+  out[0] = __uint_as_float(r.u.x); out[1] = __uint_as_float(r.u.y);
+  out[2] = __uint_as_float(r.u.z); out[3] = __uint_as_float(r.u.w);
+}
+template <> __device__ __forceinline__ void unpack_raw<bf16>(const Raw16& r, float* out) {
+  const float2 a = unpack_bf16x2(r.u.x), b = unpack_bf16x2(r.u.y), c = unpack_bf16x2(r.u.z), d = unpack_bf16x2(r.u.w);
+  out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y; out[4] = c.x; out[5] = c.y; out[6] = d.x; out[7] = d.y;
+}
+
 // decode output pixel -> the (up to) four input pixel indices.  32-bit arithmetic on purpose: the
 // 64-bit divisions this replaced cost more instructions than the rest of the loop body.  H and W
 // are powers of two for every layer of the VGG family (shift path); other sizes take the divide.
@@ -88,6 +105,19 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   if (pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
 
+  // software pipeline: the first window is requested before the per-channel constants, every later one
+  // while the previous window is being processed (small layers are one dependent-latency chain long)
+  constexpr int NQ = POOL ? 4 : 1;
+  const int stride = gridDim.x * ppb;
+  int op = blockIdx.x * ppb + pl;
+  Raw16 nxt[NQ];
+  if (pl < ppb && op < (int)Pout) {
+    int in[4];
+    window<POOL>(op, gm, in);
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) nxt[q] = ld_raw<T>(y + (size_t)in[q] * C + c0);
+  }
+
   float sc[V], sh[V];
   {
     float a[V], b[V], ga[V], be[V];
@@ -120,16 +150,23 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   if (training && blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
   if (pl >= ppb) return;
 
-  for (int op = blockIdx.x * ppb + pl; op < (int)Pout; op += gridDim.x * ppb) {
-    int in[4];
-    window<POOL>(op, gm, in);
+  for (; op < (int)Pout; op += stride) {
+    Raw16 cur[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) cur[q] = nxt[q];
+    if (op + stride < (int)Pout) {
+      int in[4];
+      window<POOL>(op + stride, gm, in);
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) nxt[q] = ld_raw<T>(y + (size_t)in[q] * C + c0);
+    }
     float best[V], by[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) { best[j] = 0.f; by[j] = __int_as_float(0x7fc00000); }   // ReLU floor; NaN = "no winner"
 #pragma unroll
-    for (int q = 0; q < (POOL ? 4 : 1); ++q) {
+    for (int q = 0; q < NQ; ++q) {
       float v[V];
-      load_vec_coh<T>(y + (size_t)in[q] * C + c0, v);
+      unpack_raw<T>(cur[q], v);
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         const float z = fmaf(v[j], sc[j], sh[j]);
@@ -225,6 +262,18 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
   if (pdl) pdl_launch_dependents();
   pdl_wait();
+  // software pipeline as in the forward kernel: first window before the constants, next one during the current
+  constexpr int NQ = POOL ? 4 : 1;
+  const int stride = gridDim.x * ppb;
+  int op = blockIdx.x * ppb + pl;
+  Raw16 nd, nv[NQ];
+  if (pl < ppb && op < (int)Pout) {
+    int in[4];
+    window<POOL>(op, gm, in);
+    nd = ld_raw<T>(dout + (size_t)op * C + c0);
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) nv[q] = ld_raw<T>(y + (size_t)in[q] * C + c0);
+  }
   // dy = sc * (dz - k1 - xhat * k2) with xhat = (y - mu) * is, written as  sc * dz + cb - cy * y:
   // four per-channel constants instead of seven keep the pooled variant at two blocks per SM
   float sc[V], sh[V], cb[V], cy[V], ab[V];
@@ -248,32 +297,43 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
     if (blockIdx.x == 0 && pl == 0) { dbeta[c0 + j] = s1; dgamma[c0 + j] = s2; }
   }
   if (pl < ppb) {
-    for (int op = blockIdx.x * ppb + pl; op < (int)Pout; op += gridDim.x * ppb) {
+    for (; op < (int)Pout; op += stride) {
       int in[4];
       window<POOL>(op, gm, in);
       float d[V];
-      load_vec_coh<T>(dout + (size_t)op * C + c0, d);
-      float v[POOL ? 4 : 1][V];
+      unpack_raw<T>(nd, d);
+      Raw16 cv[NQ];
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) cv[q] = nv[q];
+      if (op + stride < (int)Pout) {
+        int in2[4];
+        window<POOL>(op + stride, gm, in2);
+        nd = ld_raw<T>(dout + (size_t)(op + stride) * C + c0);
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) nv[q] = ld_raw<T>(y + (size_t)in2[q] * C + c0);
+      }
       float bz[V];
       int bq[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) { bz[j] = 0.f; bq[j] = -1; }
 #pragma unroll
-      for (int q = 0; q < (POOL ? 4 : 1); ++q) {
-        load_vec_coh<T>(y + (size_t)in[q] * C + c0, v[q]);
+      for (int q = 0; q < NQ; ++q) {
+        float v[V];
+        unpack_raw<T>(cv[q], v);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
-          float z = fmaf(v[q][j], sc[j], sh[j]);
+          float z = fmaf(v[j], sc[j], sh[j]);
           if (z > bz[j]) { bz[j] = z; bq[j] = q; }
         }
       }
 #pragma unroll
-      for (int q = 0; q < (POOL ? 4 : 1); ++q) {
-        float o[V];
+      for (int q = 0; q < NQ; ++q) {
+        float v[V], o[V];
+        unpack_raw<T>(cv[q], v);
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           const float dz = (bq[j] == q) ? d[j] : 0.f;
-          o[j] = fmaf(sc[j], dz, fmaf(-cy[j], v[q][j], cb[j]));
+          o[j] = fmaf(sc[j], dz, fmaf(-cy[j], v[j], cb[j]));
           ab[j] += o[j];
         }
         store_vec<T>(dy + (size_t)in[q] * C + c0, o);

@@ -132,6 +132,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint16_t MC_MASK = (uint16_t)((1u << NC) - 1);
   uint4 ywin[BN / KS / 8];               // dgrad + fused BN reduction only (epilogue warps)
+  float bn_mu[8], bn_is[8], bn_sc[8], bn_sh[8];   // its per-channel BatchNorm constants, fetched up front as well
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -198,11 +199,15 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (DGRAD && prm.bn_y != nullptr) {
       const int t2 = threadIdx.x - 64;
       const int col = n_tile * BN + ks_rank * (BN / KS) + (t2 % (BN / KS / 8)) * 8;
+      ld_coh_vec<8>(prm.bn_mean + col, bn_mu);
+      ld_coh_vec<8>(prm.bn_invstd + col, bn_is);
+      ld_coh_vec<8>(prm.bn_gamma + col, bn_sc);
+      ld_coh_vec<8>(prm.bn_beta + col, bn_sh);
 #pragma unroll
       for (int k = 0; k < BN / KS / 8; ++k) {
         const long long grow = (long long)m_tile * TILE_M + t2 / (BN / KS / 8) + k * (128 / (BN / KS / 8));
         ywin[k] = grow < prm.total_pixels
-                      ? __ldca(reinterpret_cast<const uint4*>(prm.bn_y + grow * prm.n_out + col))
+                      ? DDPB_LD_COH(reinterpret_cast<const uint4*>(prm.bn_y + grow * prm.n_out + col))
                       : make_uint4(0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u);
       }
     }
@@ -283,12 +288,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; sc[j] = 0.f; sh[j] = 0.f; mu[j] = 0.f; is[j] = 0.f; }
     if (bn_red) {
-      ld_coh_vec<8>(prm.bn_mean + col0, mu);
-      ld_coh_vec<8>(prm.bn_invstd + col0, is);
-      ld_coh_vec<8>(prm.bn_gamma + col0, sc);
-      ld_coh_vec<8>(prm.bn_beta + col0, sh);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { sc[j] *= is[j]; sh[j] -= mu[j] * sc[j]; }
+      for (int j = 0; j < 8; ++j) {
+        mu[j] = bn_mu[j]; is[j] = bn_is[j];
+        sc[j] = bn_sc[j] * is[j];
+        sh[j] = bn_sh[j] - mu[j] * sc[j];
+      }
     }
 #pragma unroll
     for (int k = 0; k < CH; ++k) {

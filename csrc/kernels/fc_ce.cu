@@ -49,7 +49,7 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
 #pragma unroll
   for (int j = 0; j < NCLS; ++j) se += expf(acc[j] - mx);
   float lse = mx + logf(se);
-  int t = (int)__ldca(reinterpret_cast<const long long*>(&target[b]));
+  int t = (int)DDPB_LD_COH(reinterpret_cast<const long long*>(&target[b]));
   if (lane == 0) {
     float lt = 0.f;
 #pragma unroll

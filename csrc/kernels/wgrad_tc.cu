@@ -301,17 +301,32 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   if (split_k <= 0) split_k = ctas / base_ctas;
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
   if (split_k < 1) split_k = 1;
-  constexpr int STAGES = 2;
-  constexpr int smem = STAGES * 2 * WG_BOX + (2 * STAGES + 1) * 8 + 16 + 1024;
-  auto kern = wgrad_tc_kernel<STAGES, 64, 1>;
-  static bool configured = false;
-  if (!configured) {
-    DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    configured = true;
-  }
   dim3 grid(base_ctas, 1, split_k);
-  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmDY /* unused */, prm));
+  static int stages = 0;
+  if (!stages) {
+    const char* e = getenv("DDPB_WGRAD0_STAGES");
+    stages = e ? atoi(e) : 8;
+    if (stages != 2 && stages != 4 && stages != 8 && stages != 12) stages = 8;
+  }
+#define DDPB_WGRAD0_LAUNCH(ST)                                                                                 \
+  do {                                                                                                         \
+    constexpr int smem = ST * 2 * WG_BOX + (2 * ST + 1) * 8 + 16 + 1024;                                       \
+    auto kern = wgrad_tc_kernel<ST, 64, 1>;                                                                    \
+    static bool configured = false;                                                                            \
+    if (!configured) {                                                                                         \
+      DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));          \
+      DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,               \
+                                           cudaSharedmemCarveoutMaxShared));                                   \
+      configured = true;                                                                                       \
+    }                                                                                                          \
+    DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmDY, prm));  \
+  } while (0)
+  // both operands stream from HBM (~1 us latency): here a deep ring does pay (8 stages 27 us, 2 stages 35 us)
+  if (stages == 2) DDPB_WGRAD0_LAUNCH(2);
+  else if (stages == 4) DDPB_WGRAD0_LAUNCH(4);
+  else if (stages == 12) DDPB_WGRAD0_LAUNCH(12);
+  else DDPB_WGRAD0_LAUNCH(8);
+#undef DDPB_WGRAD0_LAUNCH
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

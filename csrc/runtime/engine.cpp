@@ -248,6 +248,24 @@ static int alloc_all(Engine* e) {
   DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf2[0], B * max_y * e->esize));
   DDPB_CUDA_CHECK(cudaMalloc(&e->dy_buf2[1], B * max_y * e->esize));
   DDPB_CUDA_CHECK(cudaMalloc(&e->dact, B * max_act * e->esize));
+  if (getenv("DDPB_POISON")) {
+    // debugging aid: every buffer that is meant to be fully written before it is read starts as NaN
+    // (0xFF bytes), so a kernel that reads what nobody wrote shows up as NaN instead of as leftovers
+    for (auto& b : e->blocks) {
+      long long y = (long long)b.hw * b.hw * b.cout, o = b.pool ? y / 4 : y;
+      DDPB_CUDA_CHECK(cudaMemset(b.y, 0xFF, B * y * e->esize));
+      DDPB_CUDA_CHECK(cudaMemset(b.act, 0xFF, B * o * e->esize));
+      if (b.win) DDPB_CUDA_CHECK(cudaMemset(b.win, 0xFF, B * o * e->esize));
+    }
+    DDPB_CUDA_CHECK(cudaMemset(e->dy_buf2[0], 0xFF, B * max_y * e->esize));
+    DDPB_CUDA_CHECK(cudaMemset(e->dy_buf2[1], 0xFF, B * max_y * e->esize));
+    DDPB_CUDA_CHECK(cudaMemset(e->dact, 0xFF, B * max_act * e->esize));
+    DDPB_CUDA_CHECK(cudaMemset(e->logits, 0xFF, B * 10 * 4));
+    DDPB_CUDA_CHECK(cudaMemset(e->dlogits, 0xFF, B * 10 * 4));
+    DDPB_CUDA_CHECK(cudaMemset(e->input, 0xFF, B * 32 * 32 * 3 * e->esize));
+    if (e->x0cols) DDPB_CUDA_CHECK(cudaMemset(e->x0cols, 0xFF, B * 32 * 32 * 64 * 2));
+    if (e->w0pad) DDPB_CUDA_CHECK(cudaMemset(e->w0pad, 0xFF, (size_t)e->blocks[0].cout * 64 * 2));
+  }
   // BN defaults: gamma 1, running_var 1 (weights are loaded by the caller afterwards)
   DDPB_CUDA_CHECK(cudaMemset(e->mean, 0, e->total_c * 4));
   DDPB_CUDA_CHECK(cudaMemset(e->invstd, 0, e->total_c * 4));
