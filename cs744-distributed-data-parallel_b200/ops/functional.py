@@ -248,7 +248,7 @@ def first_layer_fwd_tc(x, w_bf16, bias, want_stats: bool = False, generic_kernel
     w_pad = torch.empty((cout, 64), dtype=torch.bfloat16, device=x.device)
     y = torch.empty((b, h, w_, cout), dtype=torch.bfloat16, device=x.device)
     stats = torch.zeros(2 * cout, dtype=torch.float32, device=x.device) if want_stats else None
-    check(lib().ddpb_im2col3x3_c3(ptr(x), ptr(w_bf16), ptr(cols), ptr(w_pad), b, h, w_, cout, stream_handle()),
+    check(lib().ddpb_im2col3x3_c3(ptr(x), ptr(w_bf16), ptr(cols), ptr(w_pad), b, h, w_, cout, 1, stream_handle()),
           "im2col3x3_c3")
     if generic_kernel:       # the conv kernel with a single tap (one CTA per 128-pixel tile)
         check(lib().ddpb_conv1x1_fwd_tc(ptr(cols), ptr(w_pad), ptr(bias), ptr(y), ptr(stats), b, h, w_, 64, cout,

@@ -145,7 +145,7 @@ im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16
 // it LSU-bound: 23 us for a 33 MB write), then every thread assembles its 16-byte segment from there.
 __global__ void __launch_bounds__(256)
 im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
-                          bf16* __restrict__ w_pad, int H, int h_shift, int Cout, int pdl) {
+                          bf16* __restrict__ w_pad, int H, int h_shift, int Cout, int zero_pad, int pdl) {
   if (pdl) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
   __shared__ unsigned short rows[3][34 * 3];       // pixels -1..32 of rows h-1..h+1, zero outside the image
   const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
@@ -170,6 +170,7 @@ im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w
   __syncthreads();
   const int wx = tid >> 3, seg = tid & 7;
   uint4 pk = make_uint4(0u, 0u, 0u, 0u);
+  if (seg >= 4 && !zero_pad) return;        // columns 32..63 are zero for good: the caller cleared them once
   if (seg < 4) {
     unsigned short v[8];
 #pragma unroll
@@ -252,8 +253,9 @@ extern "C" int ddpb_nchw_to_nhwc(const void* src, void* dst, int n, int c, int h
 }
 
 // x bf16 [B,H,W,3] -> cols bf16 [B*H*W][64] (3x3 patches, zero padded), w bf16 [Cout][27] -> w_pad [Cout][64].
+// zero_pad = 0: columns 32..63 of `cols` are not touched (the caller zeroed them once; they never change).
 extern "C" int ddpb_im2col3x3_c3(const void* x, const void* w_bf16, void* cols, void* w_pad, int B, int H, int W,
-                                 int Cout, cudaStream_t stream) {
+                                 int Cout, int zero_pad, cudaStream_t stream) {
   DDPB_REQUIRE(B > 0 && H > 0 && W > 0 && Cout > 0 && (H & (H - 1)) == 0 && (W & (W - 1)) == 0,
                "im2col3x3_c3: H and W must be powers of two");
   const long long n_seg = (long long)B * H * W * 8;
@@ -265,7 +267,7 @@ extern "C" int ddpb_im2col3x3_c3(const void* x, const void* w_bf16, void* cols, 
   const long long blocks = (n_seg + 255) / 256;
   if (W == 32) {
     im2col3x3_c3_row32_kernel<<<(unsigned)((long long)B * H), 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
-                                                                               (bf16*)w_pad, H, h_shift, Cout, pdl_active(stream, 64));
+                                                                               (bf16*)w_pad, H, h_shift, Cout, zero_pad, pdl_active(stream, 64));
     DDPB_LAUNCH_CHECK();
     return DDPB_OK;
   }

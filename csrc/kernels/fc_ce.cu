@@ -15,27 +15,32 @@ constexpr int NCLS = 10;
 constexpr int FEAT = 512;
 constexpr int FC_SLICE = 16;
 
+// One warp per sample, no shared memory: lane l owns features [16 l, 16 l + 16) (two 16-byte activation
+// loads) and reads the matching 16 weights of every class with 16-byte loads (the 20 KB weight matrix
+// stays in L1/L2); the ten partial dot products are then reduced across the warp.
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ bias,
                  const int64_t* __restrict__ target, float* __restrict__ logits, float* __restrict__ dlogits,
                  float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch, int pdl) {
-  __shared__ float ws[NCLS * FEAT];
   if (pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
-  for (int i = threadIdx.x; i < NCLS * FEAT; i += blockDim.x) ws[i] = ld_coh(&w[i]);   // ld.global.cg: see load_vec_coh in common.cuh
-  __syncthreads();
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int b = blockIdx.x * (blockDim.x >> 5) + warp;
   if (b >= batch) return;
+  constexpr int V = Vec16<T>::N;
+  float av[16];
+#pragma unroll
+  for (int i = 0; i < 16; i += V) load_vec_coh<T>(act + (size_t)b * FEAT + lane * 16 + i, av + i);
   float acc[NCLS];
 #pragma unroll
-  for (int j = 0; j < NCLS; ++j) acc[j] = 0.f;
-  const T* a = act + (size_t)b * FEAT;
-  for (int k = lane; k < FEAT; k += 32) {
-    float av = to_f32(ld_coh_any(&a[k]));
+  for (int j = 0; j < NCLS; ++j) {
+    float wv[16];
+    ld_coh_vec<16>(w + j * FEAT + lane * 16, wv);
+    float a = 0.f;
 #pragma unroll
-    for (int j = 0; j < NCLS; ++j) acc[j] = fmaf(av, ws[j * FEAT + k], acc[j]);
+    for (int i = 0; i < 16; ++i) a = fmaf(av[i], wv[i], a);
+    acc[j] = a;
   }
 #pragma unroll
   for (int j = 0; j < NCLS; ++j) acc[j] = warp_sum(acc[j]) + ld_coh(&bias[j]);
@@ -109,14 +114,14 @@ extern "C" int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias
                               float* logits, float* dlogits, float* loss, int* correct, int batch,
                               int loss_divisor, int dtype, cudaStream_t stream) {
   DDPB_REQUIRE(batch > 0 && loss_divisor > 0, "fc_ce_fwd: bad batch");
-  int blocks = ceil_div(batch, 8);
+  int blocks = ceil_div(batch, 4);
   float inv = 1.f / (float)loss_divisor;
   if (dtype == DDPB_BF16)
-    DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<bf16>, dim3(blocks), dim3(256), 0, stream, dim3(1, 1, 1), 32,
+    DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<bf16>, dim3(blocks), dim3(128), 0, stream, dim3(1, 1, 1), 32,
                               (const bf16*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
                               batch, inv, pdl_active(stream, 32)));
   else
-    DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<float>, dim3(blocks), dim3(256), 0, stream, dim3(1, 1, 1), 32,
+    DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<float>, dim3(blocks), dim3(128), 0, stream, dim3(1, 1, 1), 32,
                               (const float*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
                               batch, inv, pdl_active(stream, 32)));
   return DDPB_OK;

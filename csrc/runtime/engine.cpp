@@ -234,6 +234,7 @@ static int alloc_all(Engine* e) {
   DDPB_CUDA_CHECK(cudaMalloc(&e->target, B * 8));
   if (c.dtype == DDPB_BF16 && c.use_tc && e->blocks[0].cin == 3 && e->blocks[0].cout % 64 == 0) {
     DDPB_CUDA_CHECK(cudaMalloc(&e->x0cols, B * 32 * 32 * 64 * 2));
+    DDPB_CUDA_CHECK(cudaMemset(e->x0cols, 0, B * 32 * 32 * 64 * 2));     // columns 32..63 stay zero for good
     DDPB_CUDA_CHECK(cudaMalloc(&e->w0pad, (size_t)e->blocks[0].cout * 64 * 2));
   }
   long long max_y = 0, max_act = 512;
@@ -263,7 +264,6 @@ static int alloc_all(Engine* e) {
     DDPB_CUDA_CHECK(cudaMemset(e->logits, 0xFF, B * 10 * 4));
     DDPB_CUDA_CHECK(cudaMemset(e->dlogits, 0xFF, B * 10 * 4));
     DDPB_CUDA_CHECK(cudaMemset(e->input, 0xFF, B * 32 * 32 * 3 * e->esize));
-    if (e->x0cols) DDPB_CUDA_CHECK(cudaMemset(e->x0cols, 0xFF, B * 32 * 32 * 64 * 2));
     if (e->w0pad) DDPB_CUDA_CHECK(cudaMemset(e->w0pad, 0xFF, (size_t)e->blocks[0].cout * 64 * 2));
   }
   // BN defaults: gamma 1, running_var 1 (weights are loaded by the caller afterwards)
@@ -331,7 +331,7 @@ static int forward(Engine* e, int B, int training, cudaStream_t s) {
     } else if (use_tc(e, b))
       LAUNCH(e, ddpb_conv3x3_fwd_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0, s));
     else if (use_tc_first(e, b)) {
-      LAUNCH(e, ddpb_im2col3x3_c3(x, e->shadow + b.conv_w.off, e->x0cols, e->w0pad, B, b.hw, b.hw, b.cout, s));
+      LAUNCH(e, ddpb_im2col3x3_c3(x, e->shadow + b.conv_w.off, e->x0cols, e->w0pad, B, b.hw, b.hw, b.cout, 0, s));
       LAUNCH(e, ddpb_gemm_rows_fwd_tc(e->x0cols, e->w0pad, bias, b.y, st, (long long)B * b.hw * b.hw, b.cout, s));
     } else {
       LAUNCH(e, ddpb_conv3x3_fwd_simt(x, e->master + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, dt, s));

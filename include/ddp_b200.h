@@ -163,6 +163,7 @@ int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H
  * matrix (27 real columns), after which forward is a 1x1 convolution and the weight gradient a plain
  * split-K GEMM.  im2col also pads the bf16 weights [Cout][27] -> [Cout][64]. */
 int ddpb_im2col3x3_c3(const void* x_nhwc3, const void* w_bf16, void* cols, void* w_pad, int B, int H, int W, int Cout,
+                      int zero_pad /* 0: columns 32..63 of cols were zeroed by the caller and are left alone */,
                       cudaStream_t stream);
 int ddpb_conv1x1_fwd_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats, int B, int H,
                         int W, int Cin, int Cout, cudaStream_t stream);
