@@ -12,9 +12,10 @@ Two numbers per run, both timed on the device with CUDA events bracketed by barr
 synchronize, max over ranks:
 
 * ``value``      – the training step on device-resident inputs (kernel-only view);
-* ``e2e.value``  – the same steps through the public API (``Trainer``-level ``prepare`` +
-  ``train_step``) including, every step, the host->device copy of that step's batch from pinned
-  host memory and a device->host read of the step's loss.
+* ``e2e.value``  – the same steps through the public API (``stage`` + ``prepare`` + ``train_step`` +
+  ``loss_to_host``, what ``Trainer`` uses) including, every step, the host->device copy of that step's
+  batch from pinned host memory (on a copy stream, while the previous step computes) and a
+  device->host copy of that step's loss, which the host reads after queueing the next step.
 
 ``--impl reference`` runs the UNMODIFIED reference (``baseline/_ref/src/Part 3``): its own
 ``mdl.VGG11()``, ``DDP(model)``, ``optim.SGD`` and ``train_model()`` loop, fed by a loader that
