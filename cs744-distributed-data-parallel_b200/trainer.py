@@ -115,6 +115,22 @@ class Trainer:
         with self._stream_ctx():
             return self._evaluate()
 
+    def _train_flops_per_image(self) -> float:
+        from .models.vgg import conv_blocks
+        macs = sum(b.hw * b.hw * b.cout * 9 * b.cin for b in conv_blocks(self.cfg.model)) + 512 * 10
+        return 3.0 * 2.0 * macs
+
+    @staticmethod
+    def _peak_flops() -> float:
+        import json
+        import os
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+        try:
+            with open(path) as f:
+                return float(json.load(f)["bf16_tflops"]) * 1e12
+        except (OSError, KeyError, ValueError):
+            return 1590e12          # cuBLAS bf16 fallback from the profiling recipe
+
     def _prefetched(self, loader):
         """One batch ahead: with a backend that can ``stage`` (the native engine on a GPU), the host ->
         device copy of batch i+1 is queued on its copy stream before step i is, and overlaps it."""
@@ -153,7 +169,12 @@ class Trainer:
                 mean_loss = float(loss_acc) / float(n_win)
                 extra = None
                 if cfg.json_log and iter_number != n_win and sums[2] > 0:
-                    extra = {"images_per_s": self.batch_size * self.world / sums[2]}
+                    ips = self.batch_size * self.world / sums[2]
+                    extra = {"images_per_s": ips, "iteration_s_max_over_ranks": sums[2]}
+                    if self.device.type == "cuda":
+                        # achieved model FLOP/s (forward + backward = 3x the forward MACs x 2) against the
+                        # measured dense bf16 peak of the GPUs in use (MEASURED_PEAKS.json, else B200_PROFILING.md)
+                        extra["roofline_frac"] = ips * self._train_flops_per_image() / (self._peak_flops() * self.world)
                 log.window(iter_number, mean_loss, sums[0], sums[1], sums[2], extra)
                 loss_acc, host_times = None, []
             self.global_iteration += 1

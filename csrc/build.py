@@ -74,7 +74,7 @@ def build(verbose: bool = True, force: bool = False) -> pathlib.Path:
     stamp_file = OUT_DIR / "build.stamp"
     if LIB.exists() and stamp_file.exists() and stamp_file.read_text() == stamp and not force:
         return LIB
-    cmd = [_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(LIB), *map(str, objs)]
+    cmd = [_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(LIB), *map(str, objs), "-ldl"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError(f"link failed:\n{res.stderr[-4000:]}")

@@ -25,6 +25,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/ddp_b200.h"
 #include "../common.cuh"
 
@@ -526,9 +528,29 @@ static int backward(Engine* e, int B, cudaStream_t s) {
 
 enum { KIND_FWD = 1, KIND_BWD = 2, KIND_STEP = 3 };
 
+// NVTX ranges around the host-side launch sequences (DDPB_NVTX=1): they show up in nsys / ncu timelines as
+// ddpb.forward / ddpb.backward / ddpb.graph_launch (the reference has only wall-clock prints).
+static bool nvtx_on() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DDPB_NVTX"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+struct NvtxRange {
+  bool on;
+  explicit NvtxRange(const char* name) : on(nvtx_on()) { if (on) nvtxRangePushA(name); }
+  ~NvtxRange() { if (on) nvtxRangePop(); }
+};
+
 static int run_kind(Engine* e, int kind, int B, cudaStream_t s) {
-  if (kind & KIND_FWD) { ECHECK(forward(e, B, 1, s)); ECHECK(loss_fwd(e, B, 1, s)); }
-  if (kind & KIND_BWD) ECHECK(backward(e, B, s));
+  if (kind & KIND_FWD) {
+    NvtxRange r("ddpb.forward");
+    ECHECK(forward(e, B, 1, s));
+    ECHECK(loss_fwd(e, B, 1, s));
+  }
+  if (kind & KIND_BWD) {
+    NvtxRange r("ddpb.backward+sync+sgd");
+    ECHECK(backward(e, B, s));
+  }
   return DDPB_OK;
 }
 
@@ -584,7 +606,10 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
     e->graphs[key] = g;
     return DDPB_OK;
   }
-  DDPB_CUDA_CHECK(cudaGraphLaunch(it->second.exec, s));
+  {
+    NvtxRange r("ddpb.graph_launch");
+    DDPB_CUDA_CHECK(cudaGraphLaunch(it->second.exec, s));
+  }
   e->launches += it->second.launches;
   return DDPB_OK;
 }

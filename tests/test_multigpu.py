@@ -119,3 +119,58 @@ def test_bucketed_bf16_ddp_plan_runs_and_replicas_agree():
             continue
         assert torch.equal(v, out[1]["sd"][k]), k
     assert all(abs(a - b) < 1.0 for a, b in zip(out[0]["losses"], out[1]["losses"]))
+
+
+def _stress_worker(rank, port, outdir):
+    """Many fused reduce+SGD calls in every mode, with random host sleeps and random device-side spins in
+    front of each one so that the ranks reach every cross-GPU barrier in a different order every time."""
+    import random
+    import time
+    import torch.distributed as dist
+    from cs744_ddp_b200.ops import native as nv
+    from cs744_ddp_b200.parallel.p2p import SymmetricArena
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=WORLD, device_id=dev)
+    n = 64 * 1024 + 192
+    arena = SymmetricArena(n, dev, with_shadow=True)
+    rng = random.Random(1234 + rank)            # a different delay schedule on every rank
+    g = torch.Generator(device="cpu").manual_seed(7)
+    lr, mu, wd = 0.05, 0.9, 1e-4
+    bad = 0
+    # one phase per mode (the two-shot and root modes shard / centralise the momentum, so modes do not mix)
+    for phase, mode in enumerate([nv.P2P_ONESHOT, nv.P2P_TWOSHOT, nv.P2P_ROOT]):
+        expect = torch.zeros(arena.numel)
+        mom_ref = torch.zeros(arena.numel)
+        torch.cuda.synchronize(); dist.barrier()
+        arena.master.zero_(); arena.mom.zero_()
+        torch.cuda.synchronize(); dist.barrier()
+        for it in range(20):
+            grads = [torch.randn(arena.numel, generator=g) for _ in range(WORLD)]     # same numbers on all ranks
+            arena.grad.copy_(grads[rank].to(dev))
+            time.sleep(rng.random() * 0.004)                         # host jitter: 0 - 4 ms
+            torch.cuda._sleep(int(rng.random() * 4_000_000))         # device jitter: 0 - ~2 ms of spinning
+            arena.sync(mode, 0, arena.numel, lr=lr, momentum=mu, wd=wd, slot=phase * 4 + it % 4)
+            mean = sum(grads) / WORLD + wd * expect
+            mom_ref = mu * mom_ref + mean
+            expect = expect - lr * mom_ref
+            torch.cuda.synchronize()
+            err = float((arena.master.cpu() - expect).abs().max())
+            if err > 1e-4 * (1.0 + float(expect.abs().max())):
+                bad += 1
+    torch.save({"bad": bad}, os.path.join(outdir, f"stress_{rank}.pt"))
+    dist.barrier()
+    arena.close()
+    dist.destroy_process_group()
+
+
+def test_sync_kernels_survive_random_arrival_order():
+    """racecheck cannot see peer accesses, so the flag/epoch barrier protocol is stressed with
+    randomised host and device delays; every call must still produce the exact averaged SGD update."""
+    import torch.multiprocessing as mp
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_stress_worker, args=(_free_port(), d), nprocs=WORLD, join=True)
+        res = [torch.load(os.path.join(d, f"stress_{r}.pt"), weights_only=False) for r in range(WORLD)]
+    assert all(r["bad"] == 0 for r in res), res
