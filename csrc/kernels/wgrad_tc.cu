@@ -39,6 +39,7 @@ struct WgradParams {
   float* dw_raw;        // M == 64 variant: gradient matrix [64][ld_raw], columns < cols_raw are accumulated
   int ld_raw, cols_raw;
   int pdl;              // 1: execute griddepcontrol.launch_dependents (captured launches only)
+  int cl;               // M == 64 variant: cluster size along the split; ranks > 0 hand their partial tile to rank 0
 };
 
 void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn);   // conv_tc.cu
@@ -61,6 +62,8 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* accum_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  uint64_t* red_bar = reinterpret_cast<uint64_t*>(tmem_slot + 2);          // M == 64, cl > 1: partial tiles have arrived
+  float* recv = reinterpret_cast<float*>(smem + DATA_BYTES + 512);         // [cl - 1][64 rows][32 cols]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int co_blk = blockIdx.x / (prm.Cin / WG_N), ci_blk = blockIdx.x % (prm.Cin / WG_N);
@@ -76,6 +79,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
     tma_prefetch_desc(&tmW);
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     mbar_init(accum_bar, 1);
+    if (M == 64 && prm.cl > 1) mbar_init(red_bar, (prm.cl - 1) * 4);       // one arrival per epilogue warp of every peer
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<WG_TMEM_COLS>(tmem_slot);
@@ -83,6 +87,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
   pdl_wait();
   tc_fence_before();
   __syncthreads();
+  if (M == 64 && prm.cl > 1) cluster_barrier();     // rank 0's red_bar exists before any peer can arrive on it
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -133,19 +138,40 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
       // 64-row accumulator: row i lives in TMEM lane (i % 16) + 32 * (i / 16), i.e. the lower half of
       // each warp's lane quarter.  Only cols_raw (27) of the 64 columns are real.
       const int q = warp & 3;
+      const int crank = prm.cl > 1 ? (int)cluster_rank() : 0;
       mbar_wait(accum_bar, 0);
       tc_fence_after();
+      // cl > 1: the split-K partials of a cluster are summed in rank 0's shared memory first, so only one CTA in
+      // `cl` ends with the 64 x cols atomic adds (they serialise on 1728 addresses and were the tail of this
+      // kernel when more than one CTA per SM was tried)
+      if (prm.cl > 1 && crank == 0) mbar_wait_cluster(red_bar, 0);
 #pragma unroll 1
-      for (int c = 0; c < WG_N; c += 32) {
+      for (int c = 0; c < (prm.cl > 1 ? 32 : WG_N); c += 32) {
         float v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c, v);
         tmem_ld_wait();
         if (lane < 16) {
-          float* dst = prm.dw_raw + (size_t)(co_blk * 64 + q * 16 + lane) * prm.ld_raw;
+          const int row = q * 16 + lane;
+          if (crank != 0) {
+            const uint32_t remote = cluster_map_shared(smem_u32(recv + ((crank - 1) * 64 + row) * 32), 0u);
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c + j < prm.cols_raw) atomicAdd(dst + c + j, v[j]);
+            for (int j = 0; j < 32; ++j) st_cluster_f32(remote + 4u * j, v[j]);
+          } else {
+            for (int sl = 0; sl < prm.cl - 1; ++sl) {
+              const float* rp = recv + (sl * 64 + row) * 32;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] += rp[j];
+            }
+            float* dst = prm.dw_raw + (size_t)(co_blk * 64 + row) * prm.ld_raw;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (c + j < prm.cols_raw) atomicAdd(dst + c + j, v[j]);
+          }
         }
+      }
+      if (crank != 0) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(cluster_map_shared(smem_u32(red_bar), 0u));
       }
     } else {
       // epilogue: TMEM -> registers -> shared memory (128B-swizzled [128 co][32 ci] fp32 boxes), then
@@ -240,7 +266,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
     }
   }
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
-  prm.dw_raw = nullptr; prm.ld_raw = 0; prm.cols_raw = 0;
+  prm.dw_raw = nullptr; prm.ld_raw = 0; prm.cols_raw = 0; prm.cl = 1;
   prm.pdl = pdl_active(stream, 2);
   dim3 grid(base_ctas / 3, 3, split_k);
   constexpr int EPI_BYTES = WG_TAPS * 2 * WG_M * 128;       // fp32 staging of the epilogue (96 KB)
@@ -292,13 +318,20 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   const int base_ctas = Cout / 64;
   // CTA count: more CTAs per SM put more loads in flight (both operands stream from HBM), but every CTA
   // ends with 64 x 27 atomic adds on the same addresses; measured best around one CTA per SM
-  static int ctas = 0;
+  static int ctas = 0, cl = 0;
   if (!ctas) {
     const char* e = getenv("DDPB_WGRAD0_CTAS");
     ctas = e ? atoi(e) : 148;
     if (ctas < 1 || ctas > 1024) ctas = 148;
+    const char* c = getenv("DDPB_WGRAD0_CLUSTER");
+    cl = c ? atoi(c) : 1;
+    if (cl != 1 && cl != 2 && cl != 4) cl = 1;
   }
   if (split_k <= 0) split_k = ctas / base_ctas;
+  int cluster = cols <= 32 ? cl : 1;
+  if (split_k % cluster) split_k = split_k / cluster * cluster;
+  if (split_k < cluster) cluster = 1;
+  prm.cl = cluster;
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
   if (split_k < 1) split_k = 1;
   dim3 grid(base_ctas, 1, split_k);
@@ -310,7 +343,7 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   }
 #define DDPB_WGRAD0_LAUNCH(ST)                                                                                 \
   do {                                                                                                         \
-    constexpr int smem = ST * 2 * WG_BOX + (2 * ST + 1) * 8 + 16 + 1024;                                       \
+    constexpr int smem = ST * 2 * WG_BOX + 512 + 3 * 64 * 32 * 4 + 1024;   /* stages, barriers, receive area */   \
     auto kern = wgrad_tc_kernel<ST, 64, 1>;                                                                    \
     static bool configured = false;                                                                            \
     if (!configured) {                                                                                         \
@@ -319,7 +352,7 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
                                            cudaSharedmemCarveoutMaxShared));                                   \
       configured = true;                                                                                       \
     }                                                                                                          \
-    DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmDY, prm));  \
+    DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, cluster), 2, tmDY, tmX, tmDY, prm)); \
   } while (0)
   // both operands stream from HBM (~1 us latency): here a deep ring does pay (8 stages 27 us, 2 stages 35 us)
   if (stages == 2) DDPB_WGRAD0_LAUNCH(2);
