@@ -25,6 +25,8 @@
 // instead of hanging the GPU.
 //
 // The reduction order is fixed (rank 0..W-1) so every rank computes bit-identical sums.
+#include <stdlib.h>
+
 #include "../common.cuh"
 #include "../../include/ddp_b200.h"
 
@@ -323,9 +325,19 @@ extern "C" int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shado
   DDPB_REQUIRE(off % 4 == 0 && n % 4 == 0, "nvls: range must be float4-aligned");
   DDPB_REQUIRE(slot >= 0 && slot < DDPB_P2P_MAX_SLOTS, "nvls: slot %d out of range", slot);
   DDPB_REQUIRE(mc_grad && mc_master && master_local && mom && flags, "nvls: null pointer");
+  // CTA shape of the NVLS kernel (it runs next to the backward kernels; DDPB_NVLS_THREADS / DDPB_NVLS_MAX_BLOCKS)
+  static int threads = 0, cap = 0;
+  if (!threads) {
+    const char* t = getenv("DDPB_NVLS_THREADS");
+    threads = t ? atoi(t) : 256;        // measured at 2 GPUs: 256 x 32 CTAs 0.575 ms, 512 x 32 0.589, 512 x 64 0.631, 256 x 16 0.624
+    if (threads != 128 && threads != 256 && threads != 512) threads = 256;
+    const char* c = getenv("DDPB_NVLS_MAX_BLOCKS");
+    cap = c ? atoi(c) : 32;
+    if (cap < 1 || cap > P2P_MAX_BLOCKS) cap = 32;
+  }
   if (blocks <= 0) {
-    long long want = (n / 4 / world + 512 * 4 - 1) / (512 * 4);
-    blocks = (int)(want < 1 ? 1 : (want > 32 ? 32 : want));
+    long long want = (n / 4 / world + threads * 4 - 1) / (threads * 4);
+    blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
   }
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "nvls: at most %d blocks", P2P_MAX_BLOCKS);
   NvlsArgs a;
@@ -337,7 +349,7 @@ extern "C" int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shado
   a.base.lr = lr; a.base.momentum = momentum; a.base.wd = wd;
   a.base.skip_exit_barrier = skip_exit_barrier;
   a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
-  p2p_nvls_kernel<<<blocks, 512, 0, stream>>>(a);
+  p2p_nvls_kernel<<<blocks, threads, 0, stream>>>(a);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
