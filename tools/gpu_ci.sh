@@ -64,7 +64,7 @@ ref)
 ncu)
   # launch list of two training steps (only after the same command exited 0 without ncu)
   python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncu_plain.log 2>&1 &&
-  timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --cache-control none -s ${NCU_LIST_SKIP:-153} -c ${NCU_LIST_COUNT:-110} --csv \
+  timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --cache-control none -s ${NCU_LIST_SKIP:-200} -c ${NCU_LIST_COUNT:-60} --csv \
       --log-file $OUT/launches.csv python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncu_run.log 2>&1
   echo "ncu exit=$?" | tee -a $OUT/summary.log ;;
 ncufull)
