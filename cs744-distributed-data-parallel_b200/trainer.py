@@ -82,7 +82,9 @@ class Trainer:
         self.backend = make_backend(cfg, self.device)
         self.timer = (CudaRegionTimer() if self.device.type == "cuda" else HostRegionTimer())
         self.start_epoch = 0
+        self.completed_epochs = 0
         self.global_iteration = 0
+        self._exposed_comm = None      # last measured exposed-communication fraction (--json-log)
         if cfg.resume:
             self.load_checkpoint(cfg.resume)
 
@@ -96,7 +98,10 @@ class Trainer:
             self.logger.epoch_time(epoch + 1, time.time() - t0)
             loss, correct, total = self.evaluate()
             result = {"test_loss": loss, "correct": correct, "total": total}
-        if self.cfg.checkpoint and self.rank == 0:
+            self.completed_epochs = epoch + 1
+        if self.cfg.checkpoint:
+            # every rank takes part (the optimizer state may be sharded across ranks and is gathered
+            # with a collective); only rank 0 writes the file
             self.save_checkpoint(self.cfg.checkpoint)
         return result
 
@@ -157,8 +162,26 @@ class Trainer:
         iter_number = 1
         for raw in self._prefetched(self.train_loader):
             data, target = be.prepare(raw)
-            loss = be.train_step(data, target, timer)
-            loss_acc = loss if loss_acc is None else loss_acc + loss
+            if (cfg.json_log and iter_number == max(1, n_win // 2) and self.world > 1
+                    and hasattr(be, "profile_step") and not getattr(be, "_external_sync", True)):
+                # one step of the warm-up window (whose timings the reference format discards) runs
+                # instrumented: a real training step that also yields the device timeline of the
+                # gradient sync, i.e. how much of it is exposed after the last backward kernel
+                timer.mark(0)
+                tl = be.profile_step(data, target)
+                timer.mark(1)
+                timer.mark(2)
+                self._exposed_comm = max_over_ranks([tl["exposed_comm_frac"]], self.device)[0]
+                loss = be.loss[0]
+            else:
+                loss = be.train_step(data, target, timer)
+            # The native engine returns a VIEW of its device-side loss scalar, which the next step
+            # overwrites: the window sum must live in a tensor this loop owns (ref Part 1/main.py:45
+            # ``epoch_loss += loss``).
+            if loss_acc is None:
+                loss_acc = loss.detach().clone()
+            else:
+                loss_acc.add_(loss)
             if not timer.is_async:
                 host_times.append(timer.collect())
             if iter_number % n_win == 0:
@@ -175,6 +198,8 @@ class Trainer:
                         # achieved model FLOP/s (forward + backward = 3x the forward MACs x 2) against the
                         # measured dense bf16 peak of the GPUs in use (MEASURED_PEAKS.json, else B200_PROFILING.md)
                         extra["roofline_frac"] = ips * self._train_flops_per_image() / (self._peak_flops() * self.world)
+                        if self._exposed_comm is not None:
+                            extra["exposed_comm_frac"] = self._exposed_comm
                 log.window(iter_number, mean_loss, sums[0], sums[1], sums[2], extra)
                 loss_acc, host_times = None, []
             self.global_iteration += 1
@@ -209,12 +234,29 @@ class Trainer:
 
     # ------------------------------------------------------------------------------------
     def save_checkpoint(self, path: str) -> None:
-        ckpt.save_training(path, self.backend.state_dict(), self.backend.optimizer_state_dict(),
-                           self.cfg.epochs, self.global_iteration,
-                           {"model": self.cfg.model, "sync": self.cfg.sync, "dtype": self.cfg.dtype})
+        """Collective: call on EVERY rank.  Reading the optimizer state gathers the momentum shards of
+        the two-shot / NVLS buckets (cross-rank kernels that every rank must launch); rank 0 alone
+        writes the file.  ``epoch`` is the number of COMPLETED epochs, so ``--resume`` continues with
+        the next one (``--epochs`` stays the total)."""
+        with self._stream_ctx():
+            model_sd = self.backend.state_dict()
+            optim_sd = self.backend.optimizer_state_dict()
+            self.backend.synchronize()
+        if self.world > 1:
+            dist.barrier()                  # no rank runs ahead into rank-asymmetric host work
+        if self.rank == 0:
+            ckpt.save_training(path, model_sd, optim_sd, self.completed_epochs, self.global_iteration,
+                               {"model": self.cfg.model, "sync": self.cfg.sync, "dtype": self.cfg.dtype})
+        if self.world > 1:
+            dist.barrier()
 
     def load_checkpoint(self, path: str) -> None:
         blob = ckpt.load(path)
-        self.backend.load_state_dict(blob["model"])
-        self.backend.load_optimizer_state_dict(blob.get("optimizer"))
+        # on the engine's own stream, and finished before the first (captured) step can start
+        with self._stream_ctx():
+            self.backend.load_state_dict(blob["model"])
+            self.backend.load_optimizer_state_dict(blob.get("optimizer"))
+        self.backend.synchronize()
         self.global_iteration = int(blob.get("iteration", 0))
+        self.completed_epochs = int(blob.get("epoch", 0))
+        self.start_epoch = min(self.completed_epochs, self.cfg.epochs)

@@ -39,10 +39,16 @@ def save_training(path: str, model_sd: Dict[str, torch.Tensor], optim_sd: Dict[s
     _atomic_save(blob, path)
 
 
-def load(path: str) -> Dict[str, Any]:
+def load(path: str, allow_pickle: bool = False) -> Dict[str, Any]:
     """Returns ``{"model": sd, "optimizer": sd|None, "epoch": int, "iteration": int}`` for
-    either file flavour (bare model state_dict or full training checkpoint)."""
-    blob = torch.load(path, map_location="cpu", weights_only=False)
+    either file flavour (bare model state_dict or full training checkpoint).
+
+    Files are read with torch's restricted unpickler (``weights_only=True``): a checkpoint holds
+    only tensors, numbers, strings, dicts and lists, and this function is advertised for files
+    produced elsewhere (the reference model, a DDP-wrapped model), so nothing in them may execute
+    code.  ``allow_pickle=True`` is the explicit opt-in for a trusted legacy file that needs the
+    full unpickler."""
+    blob = torch.load(path, map_location="cpu", weights_only=not allow_pickle)
     if isinstance(blob, dict) and "model" in blob and "format_version" in blob:
         blob["model"] = strip_module_prefix(blob["model"])
         return blob

@@ -46,6 +46,20 @@ def test_two_rank_cli_run_prints_reference_lines(part, word):
         assert t0 == t1
 
 
+def test_two_rank_run_writes_one_checkpoint(tmp_path):
+    """Saving is a collective every rank takes part in (sharded optimizer state on the GPU paths);
+    rank 0 alone writes the file, and no rank hangs."""
+    ck = tmp_path / "p3.pt"
+    port = _free_port()
+    procs = [_launch("3", r, 2, port, ("--checkpoint", str(ck))) for r in range(2)]
+    outs = [p.communicate(timeout=600) for p in procs]
+    for p, (out, err) in zip(procs, outs):
+        assert p.returncode == 0, err[-2000:]
+    import torch
+    blob = torch.load(ck, weights_only=True)
+    assert len(blob["model"]) == 58 and blob["epoch"] == 1 and len(blob["optimizer"]["state"]) == 34
+
+
 def test_part1_cli_needs_no_flags_and_checkpoints(tmp_path):
     ck = tmp_path / "p1.pt"
     cmd = [sys.executable, "-m", "cs744_ddp_b200.parts.part1", "--synthetic", "--train-size", "64", "--test-size", "16",

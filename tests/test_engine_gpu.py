@@ -214,6 +214,74 @@ def test_trainer_end_to_end_native():
     assert "libddpb200.so" in open("/proc/self/maps").read()
 
 
+@pytest.mark.parametrize("dtype", ["bf16", "fp32"])
+def test_window_loss_is_the_mean_of_the_step_losses_native(dtype):
+    """ref Part 1/main.py:45-50.  The engine returns a view of its loss scalar that the next step
+    overwrites; the printed window mean must still be the mean of the individual step losses."""
+    from cs744_ddp_b200.trainer import Trainer
+    from cs744_ddp_b200.utils.logger import RunLogger
+    cfg = _cfg(backend="native", dtype=dtype, train_size=16 * 9, test_size=16, max_iters=8)
+    t = Trainer(cfg, RunLogger("1", 4, sink=lambda s: None))
+    be, seen, step = t.backend, [], t.backend.train_step
+
+    def spy(data, target, timer):
+        loss = step(data, target, timer)
+        seen.append(be.loss_to_host(loss))            # this step's own value, copied before the next step runs
+        return loss
+
+    be.train_step = spy
+    t.train_epoch(0)
+    vals = [h.item() for h in seen[4:]] if len(seen) > 4 else []
+    recs = t.logger.records
+    assert len(recs) == 2 and len(seen) == 8
+    want = sum(vals) / 4                                # (only 4 pinned slots: the second window is checkable)
+    assert abs(recs[1]["loss"] - want) <= 1e-6 * max(1.0, abs(want)), (recs[1]["loss"], want)
+    assert len(set(vals)) > 1                           # the steps really had different losses
+
+
+def test_eval_after_training_matches_torch(no_tf32):
+    """Running statistics produced by the engine's own BatchNorm forward (momentum 0.1, unbiased
+    variance, ref Part 1/model.py:24) must evaluate like torch's after the same training steps
+    (ref test_model, Part 1/main.py:61-76)."""
+    tb, nb = _pair("fp32", False, b=32)
+    tb.set_train(True)
+    for raw in _batches(20, 32, seed=5):
+        lt = tb.train_step(*tb.prepare(raw), _T())
+        ln = nb.train_step(*nb.prepare(raw), _T())
+    print(f"[eng] after 20 steps: train loss torch {float(lt):.4f} native {float(ln):.4f}")
+    sd_t, sd_n = tb.state_dict(), nb.state_dict()
+    for k in sd_t:
+        if k.endswith("running_mean") or k.endswith("running_var"):
+            # 20 chaotic steps: weights drift apart at the 1e-2 level, the statistics follow them
+            assert _rel(sd_n[k], sd_t[k]) < 0.1, (k, _rel(sd_n[k], sd_t[k]))
+    # same weights + same statistics in both models: the evaluation itself must agree tightly
+    nb.load_state_dict(sd_t)
+    tb.set_train(False)
+    nb.set_train(False)
+    for raw in _batches(2, 32, seed=8):
+        raw.crop_xy = None
+        raw.flip = None
+        le_t, c_t = tb.eval_step(*tb.prepare(raw))
+        le_n, c_n = nb.eval_step(*nb.prepare(raw))
+        print(f"[eng] eval torch {float(le_t):.5f}/{int(c_t)} native {float(le_n):.5f}/{int(c_n)}")
+        assert abs(float(le_t) - float(le_n)) < 2e-3 * max(1.0, float(le_t))
+        assert abs(int(c_t) - int(c_n)) <= 1
+    # and the engine's OWN trained state evaluates like torch loaded with that state
+    tb2, nb2 = _pair("fp32", False, b=32)
+    for raw in _batches(20, 32, seed=5):
+        nb2.train_step(*nb2.prepare(raw), _T())
+    tb2.load_state_dict(nb2.state_dict())
+    tb2.set_train(False)
+    nb2.set_train(False)
+    raw = _batches(1, 32, seed=8)[0]
+    raw.crop_xy = None
+    raw.flip = None
+    le_t, c_t = tb2.eval_step(*tb2.prepare(raw))
+    le_n, c_n = nb2.eval_step(*nb2.prepare(raw))
+    print(f"[eng] eval of the native-trained state: torch {float(le_t):.5f}/{int(c_t)} native {float(le_n):.5f}/{int(c_n)}")
+    assert abs(float(le_t) - float(le_n)) < 2e-3 * max(1.0, float(le_t))
+
+
 def test_bucket_plans_cover_arena():
     from cs744_ddp_b200.engine import NativeBackend
     for plan, n in (("ddp", 3), ("per_layer", 9), ("single", 1)):

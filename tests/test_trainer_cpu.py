@@ -58,6 +58,60 @@ def test_checkpoint_resume_continues_identically(tmp_path):
     assert b.global_iteration == 4
 
 
+def test_resume_continues_with_the_next_epoch(tmp_path):
+    """The checkpoint stores the number of COMPLETED epochs; --epochs stays the total."""
+    path = str(tmp_path / "ck.pt")
+    lines = []
+    a = Trainer(_cfg(max_iters=2, epochs=1, checkpoint=path), RunLogger("1", 4, sink=lambda s: None))
+    a.fit()
+    b = Trainer(_cfg(max_iters=2, epochs=3, resume=path), RunLogger("1", 4, sink=lines.append))
+    assert b.start_epoch == 1 and b.global_iteration == 2
+    b.fit()
+    done = [l for l in lines if l.startswith("Training time after")]
+    assert [l.split()[3] for l in done] == ["2", "3"]            # epochs 2 and 3 ran, epoch 1 did not
+    assert b.global_iteration == 6
+    c = Trainer(_cfg(max_iters=2, epochs=1, resume=path), RunLogger("1", 4, sink=lambda s: None))
+    assert c.fit() == {}                                           # nothing left to train
+
+
+def test_checkpoint_loader_refuses_pickled_code(tmp_path):
+    """Foreign checkpoints are read with the restricted unpickler: a file that smuggles a callable fails."""
+    import pickle
+
+    import pytest
+
+    from cs744_ddp_b200.utils import checkpoint as ckpt
+
+    class Boom:
+        def __reduce__(self):
+            return (print, ("arbitrary code ran",))
+
+    bad = tmp_path / "bad.pt"
+    torch.save({"layers.0.weight": Boom()}, bad)
+    with pytest.raises(pickle.UnpicklingError):
+        ckpt.load(str(bad))
+
+
+def test_window_loss_is_the_mean_of_the_step_losses():
+    """ref Part 1/main.py:45-50: the printed value is sum(loss of each of the 20 iterations) / 20."""
+    cfg = _cfg(max_iters=8)
+    t = Trainer(cfg, RunLogger("1", cfg.log_every, sink=lambda s: None))
+    seen = []
+    step = t.backend.train_step
+
+    def spy(data, target, timer):
+        loss = step(data, target, timer)
+        seen.append(float(loss))
+        return loss
+
+    t.backend.train_step = spy
+    t.train_epoch(0)
+    recs = t.logger.records
+    for w in range(2):
+        want = sum(seen[4 * w: 4 * w + 4]) / 4
+        assert abs(recs[w]["loss"] - want) <= 1e-6 * max(1.0, abs(want)), (w, recs[w]["loss"], want)
+
+
 def test_eval_mode_quirk_flag():
     quiet = lambda s: None
     t = Trainer(_cfg(epochs=2, max_iters=2, reproduce_eval_mode_quirk=True), RunLogger("1", 4, sink=quiet))
