@@ -139,6 +139,8 @@ class NativeBackend:
         # weights: same construction order and RNG consumption as the reference (seeded by the trainer)
         sd = init_state if init_state is not None else build_model(cfg.model).state_dict()
         self.load_state_dict(sd)
+        if self.world > 1:
+            self.verify_plan_across_ranks()             # DDP checks parameter shapes before it broadcasts
         if cfg.sync == "bucketed" and self.world > 1:
             self.broadcast_from_rank0()                 # DDP init: params + buffers from rank 0
         torch.cuda.synchronize(device)
@@ -407,6 +409,44 @@ class NativeBackend:
             dist.broadcast(self.running_mean, src=0)
             dist.broadcast(self.running_var, src=0)
         dist.broadcast(self.nbt, src=0)
+
+    def plan_signature(self) -> List[int]:
+        """Everything the cross-rank kernels assume to be identical on all ranks: the parameter shapes
+        (in arena order), the arena size and the bucket ranges / modes they will be called with."""
+        sig: List[int] = [int(self.info.arena_elems), int(self.info.total_channels), int(self.info.num_buckets),
+                          1 if self.dtype == torch.bfloat16 else 0, STRATEGY_CODE[self.cfg.sync]]
+        for _, (off, shape, _) in sorted(self._slots().items(), key=lambda kv: kv[1][0]):
+            sig.append(off)
+            sig.extend(int(d) for d in shape)
+        for b in self.buckets():
+            sig.extend(b)
+        return sig
+
+    def verify_plan_across_ranks(self) -> None:
+        """``DDP.__init__`` verifies parameter shapes across processes before its first broadcast
+        (torch ``nn/parallel/distributed.py:881``, which ref ``Part 3/main.py:61`` gets implicitly).
+        Here a mismatch would be worse than a wrong answer: the peer-to-peer kernels index every
+        rank's arena with THIS rank's offsets.  All ranks compare their layout with rank 0's and fail
+        together."""
+        if self.world == 1:
+            return
+        mine = torch.tensor(self.plan_signature(), dtype=torch.int64, device=self.device)
+        n = torch.tensor([mine.numel()], dtype=torch.int64, device=self.device)
+        n0 = n.clone()
+        dist.broadcast(n0, src=0)
+        same = int(n0) == int(n)
+        if same:
+            ref = mine.clone()
+            dist.broadcast(ref, src=0)
+            same = bool(torch.equal(ref, mine))
+        else:
+            dist.broadcast(torch.empty(int(n0), dtype=torch.int64, device=self.device), src=0)
+        ok = torch.tensor([1 if same else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok) == 0:
+            raise RuntimeError(f"rank {self.rank}: model / arena / bucket plan differs across ranks "
+                               f"({'this rank differs from rank 0' if not same else 'another rank differs'}); "
+                               "all ranks must be started with the same --model, --dtype, --sync and bucket options")
 
     def broadcast_from_rank0(self) -> None:
         if self.world == 1:

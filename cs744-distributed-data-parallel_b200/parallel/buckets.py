@@ -15,7 +15,8 @@ Plans available (``--bucket-plan``):
   where per-collective cost is latency, not link count;
 * ``single``    – everything in one bucket (what DDP does in its very first iteration).
 
-The C++ scheduler (``csrc/runtime/bucket_scheduler.cpp``) consumes the plan as arrays of
+The C++ scheduler (``csrc/runtime/engine.cpp``: ``plan_buckets`` / ``buckets_ready`` / ``launch_bucket``) computes
+the same plan natively and consumes the plan as arrays of
 ``(offset, numel)`` ranges over the flat gradient arena, which is laid out in ready order so
 that every bucket is one contiguous range.
 """

@@ -41,6 +41,13 @@ void set_last_error(const char* fmt, ...);
 
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// Number of SMs of the CURRENT device (queried once per device; 148 on B200) - grids are sized from this,
+// never from a literal.
+int sm_count();
+// One-time per-DEVICE setup (cudaFuncSetAttribute is per device, a process may drive several):
+//   static unsigned long long done = 0;  if (first_on_device(&done)) { ...set attributes... }
+bool first_on_device(unsigned long long* mask);
+
 // Programmatic dependent launch: a kernel launched through launch_ex(..., pdl = true) may be scheduled
 // while its predecessor on the stream is still running, so its prologue (barrier init, TMEM
 // allocation, descriptor prefetch, index math) and the launch latency overlap the predecessor's tail

@@ -404,7 +404,7 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ x, const T* __restrict_
   for (int q = 0; q < 4; ++q) dx[(size_t)in[q] * C + c] = (q == bq) ? dout[i] : from_f32<T>(0.f);
 }
 
-// Persistent grid: at most one wave of resident blocks (148 SMs x blocks that fit per SM); the
+// Persistent grid: at most one wave of resident blocks (SM count x blocks that fit per SM); the
 // kernels stride over pixels, so a tail wave of partially filled SMs never happens.
 template <typename K>
 static int bn_grid(K kernel, long long Pout, int ppb, int smem_bytes) {
@@ -414,15 +414,23 @@ static int bn_grid(K kernel, long long Pout, int ppb, int smem_bytes) {
     occ = 2;
   }
   long long g = (Pout + ppb - 1) / ppb;
-  const long long cap = 148LL * occ;
+  const long long cap = (long long)sm_count() * occ;
   return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
+// Channel layout of the BN kernels: a thread owns V = 16 bytes of channels (8 bf16 / 4 fp32), the C / V
+// channel groups of a pixel sit side by side in a 256-thread block.  Hence C / V must divide 256:
+// bf16 C in {8, 16, ..., 2048}, fp32 C in {4, 8, ..., 1024}, C / V a power of two.
 template <typename T>
 static int bn_check(int C, int H, int W, bool pool) {
   constexpr int V = VecOf<T>::N;
-  DDPB_REQUIRE(C % V == 0 && C / V <= 256 && 256 % (C / V) == 0, "bn: unsupported channel count %d", C);
-  DDPB_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "bn: pooling needs even H, W");
+  DDPB_REQUIRE(C > 0 && C % V == 0, "bn: channel count %d is not a multiple of %d (16 bytes of %s)", C, V,
+               sizeof(T) == 2 ? "bf16" : "fp32");
+  DDPB_REQUIRE(C / V <= 256, "bn: channel count %d exceeds the %s limit of %d (one 256-thread block spans a pixel)", C,
+               sizeof(T) == 2 ? "bf16" : "fp32", 256 * V);
+  DDPB_REQUIRE(256 % (C / V) == 0, "bn: channel count %d / %d must be a power of two", C, V);
+  DDPB_REQUIRE(H > 0 && W > 0, "bn: bad spatial size %dx%d", H, W);
+  DDPB_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "bn: pooling needs even H, W (got %dx%d)", H, W);
   return DDPB_OK;
 }
 
@@ -528,7 +536,12 @@ extern "C" int ddpb_bn_relu_pool_bwd_apply(const void* dout, const void* y, cons
 // them the scratch lives inside the library image, as a fixed device array:
 //
 //  * capacity: DDPB_BN_NOALLOC_MAX_C channels (2 * 2048 floats = 16 KB).  Every GPU that loads the
-//    library carries these 16 KB until the process exits, whether or not this entry point is used;
+//    library carries these 16 KB until the process exits, whether or not this entry point is used.
+//    The BN kernels themselves add a tighter bound for fp32 tensors: a thread owns 16 bytes of
+//    channels and one 256-thread block spans a pixel, so bf16 reaches C = 2048 but fp32 only
+//    C = DDPB_BN_NOALLOC_MAX_C_F32 = 1024; in both cases C / (16 bytes' worth) must be a power of
+//    two.  Sizes outside these limits are rejected with a message that names the limit, before the
+//    shared array is touched;
 //  * the array is one per device and shared by all calls: it still holds the previous call's sums,
 //    so each call clears the 2*C floats it is about to use (a memset enqueued on `stream`) before
 //    the kernels run.  Two calls whose work overlaps on the GPU (different streams, or different
@@ -568,12 +581,23 @@ extern "C" int ddpb_bn_relu_pool_bwd_noalloc(const void* dout, const void* y, co
                                              const float* save_invstd, const float* gamma, const float* beta,
                                              void* dy, float* dgamma, float* dbeta, float* dbias, int batch,
                                              int H, int W, int C, int pool, int dtype, cudaStream_t stream) {
+  // Every argument is checked BEFORE the shared array is touched: a rejected call must not clear scratch
+  // that an earlier, correctly serialised call may still be using on another stream.
+  DDPB_REQUIRE(dtype == DDPB_BF16 || dtype == DDPB_F32, "bn_bwd_noalloc: unknown dtype code %d", dtype);
   DDPB_REQUIRE(C > 0 && C <= DDPB_BN_NOALLOC_MAX_C,
                "bn_bwd_noalloc: C = %d exceeds the built-in scratch capacity of %d channels; use "
                "ddpb_bn_relu_pool_bwd with a caller-owned [2*C] buffer instead",
                C, DDPB_BN_NOALLOC_MAX_C);
+  DDPB_REQUIRE(dtype == DDPB_BF16 || C <= DDPB_BN_NOALLOC_MAX_C_F32,
+               "bn_bwd_noalloc: C = %d exceeds the fp32 limit of %d channels (the BN kernels give a thread 16 "
+               "bytes of channels, so fp32 reaches half as far as bf16's %d)",
+               C, DDPB_BN_NOALLOC_MAX_C_F32, DDPB_BN_NOALLOC_MAX_C);
+  DDPB_REQUIRE(batch > 0 && dout && y && save_mean && save_invstd && gamma && beta && dy && dgamma && dbeta,
+               "bn_bwd_noalloc: null pointer or empty batch");
+  int rc = dtype == DDPB_BF16 ? bn_check<bf16>(C, H, W, pool != 0) : bn_check<float>(C, H, W, pool != 0);
+  if (rc) return rc;
   float* sums = nullptr;
-  int rc = static_sums_for_current_device(&sums);
+  rc = static_sums_for_current_device(&sums);
   if (rc) return rc;
   DDPB_CUDA_CHECK(cudaMemsetAsync(sums, 0, sizeof(float) * 2 * (size_t)C, stream));
   return ddpb_bn_relu_pool_bwd(dout, y, save_mean, save_invstd, gamma, beta, sums, dy, dgamma, dbeta, dbias, batch,

@@ -465,13 +465,12 @@ first_layer_wgrad_32(const T* __restrict__ dy, const T* __restrict__ x, float* _
 template <typename T>
 static int launch_first_layer_wgrad_32(const void* dy, const void* x, float* dw, int B, int H, cudaStream_t stream) {
   const int smem = 2 * FL_TILE * 64 * (int)sizeof(T) + 2 * FL_XR * FL_XW * 3 * (int)sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;
+  if (first_on_device(&configured)) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(first_layer_wgrad_32<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
   }
   long long tiles = (long long)B * (H / FL_ROWS);
-  int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
+  int grid = (int)(tiles < sm_count() * 2 ? tiles : sm_count() * 2);
   first_layer_wgrad_32<T><<<grid, 256, smem, stream>>>((const T*)dy, (const T*)x, dw, B, H);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
@@ -489,7 +488,7 @@ extern "C" int ddpb_conv3x3_fwd_simt(const void* x, const float* w, const float*
   long long total = (long long)B * H * W * Cout;
   if (Cin == 3 && Cout == 64 && W == FL_W && H % FL_ROWS == 0) {
     long long tiles = (long long)B * (H / FL_ROWS);
-    int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
+    int grid = (int)(tiles < sm_count() * 2 ? tiles : sm_count() * 2);
     if (dtype == DDPB_BF16)
       first_layer_fwd_32<bf16><<<grid, 256, 0, stream>>>((const bf16*)x, w, bias, (bf16*)y, stats, B, H);
     else
@@ -499,7 +498,7 @@ extern "C" int ddpb_conv3x3_fwd_simt(const void* x, const float* w, const float*
   }
   if (Cin == 3 && Cout == 64) {
     int grid = ceil_div((long long)B * H * W, 64);
-    if (grid > 148 * 8) grid = 148 * 8;
+    if (grid > sm_count() * 8) grid = sm_count() * 8;
     if (dtype == DDPB_BF16)
       first_layer_fwd<bf16><<<grid, 256, 0, stream>>>((const bf16*)x, w, bias, (bf16*)y, stats, B, H, W);
     else
@@ -538,7 +537,7 @@ extern "C" int ddpb_conv3x3_wgrad_simt(const void* dy, const void* x, float* dw,
   }
   if (Cin == 3 && Cout == 64) {
     int grid = ceil_div((long long)B * H * W, 64);
-    if (grid > 148 * 2) grid = 148 * 2;
+    if (grid > sm_count() * 2) grid = sm_count() * 2;
     if (dtype == DDPB_BF16)
       first_layer_wgrad<bf16><<<grid, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, B, H, W);
     else

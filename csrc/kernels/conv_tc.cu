@@ -501,13 +501,12 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   dim3 grid(m_tiles, Nc / BN, KS);
   constexpr int smem = conv_tc_smem<BN, STAGES>();
   auto kern = conv3x3_tc_kernel<BN, STAGES, DGRAD, NC, KS>;
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;
+  if (first_on_device(&configured)) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     // ask for the largest shared-memory carve-out, so that two ~100 KB CTAs share an SM (and the
     // occupancy query below reports that)
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    configured = true;
   }
   if (!DGRAD && g_bnfwd.out && stats) {
     // the fused BatchNorm needs a grid-wide barrier: only when every CTA is resident at the same time
@@ -590,7 +589,7 @@ static int auto_tile(int B, int H, int W, int n_channels, int k_channels) {
   if (t128 >= 256) return 128;
   if (max_ks >= 2 && t128 * 2 >= 256) return 4228;
   if (max_ks >= 4 && t128 * 4 >= 256) return 4428;
-  if (t64 >= 256 || max_ks == 1) return t128 >= 148 ? 128 : 64;
+  if (t64 >= 256 || max_ks == 1) return t128 >= sm_count() ? 128 : 64;
   if (t64 * 2 >= 256 || max_ks == 2) return 4264;
   return 4464;
 }
@@ -623,7 +622,7 @@ extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const floa
     bf16* yo = (bf16*)y;
     DDPB_REQUIRE(Cout % (tile_n % 100 == 28 ? 128 : 64) == 0, "conv_tc fwd: Cout %d does not fit tile code %d", Cout, tile_n);
     switch (tile_n) {
-      case 4264: return cta_count(B, H, W, Cout, 64) * 2 <= 148
+      case 4264: return cta_count(B, H, W, Cout, 64) * 2 <= sm_count()
                             ? launch<64, 8, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
                             : launch<64, 4, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
       case 4464: return launch<64, 4, false, 1, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
@@ -635,7 +634,7 @@ extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const floa
   if (tile_n > 1000) {          // 1<cluster><tile>: activation tile multicast across a cluster of n-tiles
     const bf16 *xi = (const bf16*)x, *wi = (const bf16*)w_bf16;
     bf16* yo = (bf16*)y;
-    const bool deep = cta_count(B, H, W, Cout, 64) <= 148;
+    const bool deep = cta_count(B, H, W, Cout, 64) <= sm_count();
     switch (tile_n) {
       case 1864: return deep ? launch<64, 8, false, 8>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
                              : launch<64, 4, false, 8>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
@@ -652,7 +651,7 @@ extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const floa
     return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
   if (tile_n == 64) {
     // fewer CTAs than SMs: one CTA per SM with a deep pipeline (more bytes in flight per CTA)
-    if (cta_count(B, H, W, Cout, 64) <= 148)
+    if (cta_count(B, H, W, Cout, 64) <= sm_count())
       return launch<64, 8, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
     return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
   }
@@ -675,7 +674,7 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
     bf16* xo = (bf16*)dx;
     DDPB_REQUIRE(Cin % (tile_n % 100 == 28 ? 128 : 64) == 0, "conv_tc dgrad: Cin %d does not fit tile code %d", Cin, tile_n);
     switch (tile_n) {
-      case 4264: return cta_count(B, H, W, Cin, 64) * 2 <= 148
+      case 4264: return cta_count(B, H, W, Cin, 64) * 2 <= sm_count()
                             ? launch<64, 8, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
                             : launch<64, 4, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
       case 4464: return launch<64, 4, true, 1, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
@@ -687,7 +686,7 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
   if (tile_n > 1000) {
     const bf16 *di = (const bf16*)dy, *wi = (const bf16*)w_bf16;
     bf16* xo = (bf16*)dx;
-    const bool deep = cta_count(B, H, W, Cin, 64) <= 148;
+    const bool deep = cta_count(B, H, W, Cin, 64) <= sm_count();
     switch (tile_n) {
       case 1864: return deep ? launch<64, 8, true, 8>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
                              : launch<64, 4, true, 8>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
@@ -703,7 +702,7 @@ extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* d
   if (tile_n == 128)
     return launch<128, 3, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
   if (tile_n == 64) {
-    if (cta_count(B, H, W, Cin, 64) <= 148)
+    if (cta_count(B, H, W, Cin, 64) <= sm_count())
       return launch<64, 8, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
     return launch<64, 4, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
   }
@@ -717,7 +716,7 @@ extern "C" int ddpb_conv1x1_fwd_tc(const void* x, const void* w_bf16, const floa
                                    int B, int H, int W, int Cin, int Cout, cudaStream_t stream) {
   int rc = check_shapes(B, H, W, Cin, Cout);
   if (rc) return rc;
-  if (Cout % 128 == 0 && cta_count(B, H, W, Cout, 128) >= 148)
+  if (Cout % 128 == 0 && cta_count(B, H, W, Cout, 128) >= sm_count())
     return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
   return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
 }

@@ -274,10 +274,9 @@ int launch2(const bf16* in, const bf16* w, bf16* out, const float* bias, float* 
   dim3 grid(m_tiles, Nc / BN);
   constexpr int smem = conv2_smem<BN, STAGES>();
   auto kern = conv3x3_tc2_kernel<BN, STAGES, DGRAD>;
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;
+  if (first_on_device(&configured)) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
   }
   kern<<<grid, 192, smem, stream>>>(tmA, tmB, tmC, bias, stats, prm);
   DDPB_LAUNCH_CHECK();

@@ -185,7 +185,8 @@ im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w
   reinterpret_cast<uint4*>(cols)[(size_t)row * 256 + tid] = pk;
 }
 
-static int grid_for(long long n, int block, int cap = 148 * 16) {
+static int grid_for(long long n, int block, int cap = 0) {
+  if (cap <= 0) cap = sm_count() * 16;
   long long g = (n + block - 1) / block;
   if (g < 1) g = 1;
   return (int)(g > cap ? cap : g);

@@ -184,17 +184,16 @@ extern "C" int ddpb_gemm_rows_fwd_tc(const void* x, const void* w_bf16, const fl
   prm.tiles = (int)((P + 127) / 128);
   // two CTAs per SM: enough row tiles per CTA that the whole grid is one wave
   const int n_tiles = Cout / GR_N;
-  const int slots = 148 * 2 / n_tiles > 0 ? 148 * 2 / n_tiles : 1;
+  const int slots = sm_count() * 2 / n_tiles > 0 ? sm_count() * 2 / n_tiles : 1;
   prm.mt = (prm.tiles + slots - 1) / slots;
   if (prm.mt < 1) prm.mt = 1;
   dim3 grid((prm.tiles + prm.mt - 1) / prm.mt, n_tiles);
   constexpr int smem = GR_STAGES * GR_A + GR_B + 2 * GR_TILE + 16 * 2 * GR_N * 4 + (2 * GR_STAGES + 5) * 8 + 16 + GR_N * 4 + 1024;
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;
+  if (first_on_device(&configured)) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(gemm_rows_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(gemm_rows_tc_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                          cudaSharedmemCarveoutMaxShared));
-    configured = true;
   }
   prm.pdl = pdl_active(stream, 1);
   DDPB_CUDA_CHECK(launch_ex(gemm_rows_tc_kernel, grid, dim3(192), smem, stream, dim3(1, 1, 1), 1, tmA, tmB, bias, stats, prm));

@@ -259,7 +259,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
     long long best_cost = -1;
     const int max_split = prm.total_chunks < 64 ? prm.total_chunks : 64;
     for (int sp = 1; sp <= max_split; ++sp) {
-      long long waves = ((long long)base_ctas * sp + 148 * per_sm - 1) / (148 * per_sm);
+      long long waves = ((long long)base_ctas * sp + sm_count() * per_sm - 1) / (sm_count() * per_sm);
       long long iters = (prm.total_chunks + sp - 1) / sp;
       long long cost = waves * (iters * per_sm + 6);        // CTAs sharing an SM share its load bandwidth
       if (best_cost < 0 || cost < best_cost) { best_cost = cost; split_k = sp; }
@@ -275,12 +275,11 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
     constexpr int pipe = ST * (WG_M / 64 + WG_TAPS) * WG_BOX;                                                  \
     constexpr int smem = (pipe > EPI_BYTES ? pipe : EPI_BYTES) + (2 * ST + 1) * 8 + 16 + 1024;                 \
     auto kern = wgrad_tc_kernel<ST, WG_M, WG_TAPS>;                                                            \
-    static bool configured = false;                                                                            \
-    if (!configured) {                                                                                         \
+    static unsigned long long configured = 0;                                                                            \
+    if (first_on_device(&configured)) {                                                                                         \
       DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));          \
       DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,               \
                                            cudaSharedmemCarveoutMaxShared));                                   \
-      configured = true;                                                                                       \
     }                                                                                                          \
     DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, 1), 2, tmDY, tmX, tmW, prm));   \
   } while (0)
@@ -321,8 +320,8 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   static int ctas = 0, cl = 0;
   if (!ctas) {
     const char* e = getenv("DDPB_WGRAD0_CTAS");
-    ctas = e ? atoi(e) : 148;
-    if (ctas < 1 || ctas > 1024) ctas = 148;
+    ctas = e ? atoi(e) : sm_count();
+    if (ctas < 1 || ctas > 1024) ctas = sm_count();
     const char* c = getenv("DDPB_WGRAD0_CLUSTER");
     cl = c ? atoi(c) : 1;
     if (cl != 1 && cl != 2 && cl != 4) cl = 1;
@@ -345,12 +344,11 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   do {                                                                                                         \
     constexpr int smem = ST * 2 * WG_BOX + 512 + 3 * 64 * 32 * 4 + 1024;   /* stages, barriers, receive area */   \
     auto kern = wgrad_tc_kernel<ST, 64, 1>;                                                                    \
-    static bool configured = false;                                                                            \
-    if (!configured) {                                                                                         \
+    static unsigned long long configured = 0;                                                                            \
+    if (first_on_device(&configured)) {                                                                                         \
       DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));          \
       DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,               \
                                            cudaSharedmemCarveoutMaxShared));                                   \
-      configured = true;                                                                                       \
     }                                                                                                          \
     DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, 1, cluster), 2, tmDY, tmX, tmDY, prm)); \
   } while (0)

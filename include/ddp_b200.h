@@ -86,12 +86,17 @@ int ddpb_bn_relu_pool_bwd_apply(const void* dout, const void* y, const float* sa
 /* Same computation as ddpb_bn_relu_pool_bwd for callers that cannot supply the [2*C] scratch: a
  * host that pre-committed all device memory to its own pool, or a plug-in interface that passes only
  * inputs and outputs.  The scratch is a fixed 16 KB device array inside the library (resident on
- * every GPU that loads it), so this call performs no allocation of any kind.  Limits: C <=
- * DDPB_BN_NOALLOC_MAX_C (larger C is rejected with an error); all calls on a device share the
+ * every GPU that loads it), so this call performs no allocation of any kind.  Limits: bf16 tensors
+ * C <= DDPB_BN_NOALLOC_MAX_C (2048, what the array holds); fp32 tensors C <=
+ * DDPB_BN_NOALLOC_MAX_C_F32 (1024: the BN kernels give each thread 16 bytes of channels and one
+ * 256-thread block spans a pixel, so fp32 reaches half as far); C / 8 (bf16) or C / 4 (fp32) must be
+ * a power of two; H and W even when pool != 0.  A call outside these limits is rejected with an error
+ * that names the limit, before the shared array is touched.  All calls on a device share the
  * array, so calls that overlap on the GPU race - serialise them; the first call on each device
  * resolves the array's device address on the host and should happen before any stream capture.
  * This entry point has no counterpart in the reference. */
 #define DDPB_BN_NOALLOC_MAX_C 2048
+#define DDPB_BN_NOALLOC_MAX_C_F32 1024
 int ddpb_bn_relu_pool_bwd_noalloc(const void* dout, const void* y, const float* save_mean,
                                   const float* save_invstd, const float* gamma, const float* beta, void* dy,
                                   float* dgamma, float* dbeta, float* dbias, int batch, int H, int W, int C,

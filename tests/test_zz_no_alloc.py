@@ -19,7 +19,8 @@ pytestmark = pytest.mark.gpu
 
 LIB = pathlib.Path(__file__).resolve().parent.parent / "cs744-distributed-data-parallel_b200" / "_native" / "libddpb200.so"
 BF16, F32 = 1, 0
-MAX_C = 2048          # DDPB_BN_NOALLOC_MAX_C in include/ddp_b200.h
+MAX_C = 2048          # DDPB_BN_NOALLOC_MAX_C in include/ddp_b200.h (bf16)
+MAX_C_F32 = 1024      # DDPB_BN_NOALLOC_MAX_C_F32: a BN-kernel thread owns 16 bytes of channels
 
 
 def _lib():
@@ -97,3 +98,31 @@ def test_noalloc_rejects_more_channels_than_the_builtin_scratch_holds():
                                            1, 2, 2, c, 0, F32, ctypes.c_void_p(0))
     assert rc != 0
     assert b"exceeds the built-in scratch capacity" in lib.ddpb_last_error()
+
+
+def test_noalloc_names_the_fp32_limit_and_leaves_the_scratch_alone():
+    """fp32 tensors stop at 1024 channels (half of what the array could hold).  The call must say so,
+    and - like every rejected call - must not clear the shared scratch on its way out."""
+    lib = _lib()
+    t = torch.zeros(8, device="cuda")
+    for c, dtype, needle in ((MAX_C, F32, b"exceeds the fp32 limit of 1024"),
+                             (MAX_C_F32 + 4, F32, b"exceeds the fp32 limit of 1024"),
+                             (24, BF16, b"must be a power of two"),
+                             (64, 7, b"unknown dtype")):
+        rc = lib.ddpb_bn_relu_pool_bwd_noalloc(_p(t), _p(t), _p(t), _p(t), _p(t), _p(t), _p(t), _p(t), _p(t), _p(t),
+                                               1, 2, 2, c, 0, dtype, ctypes.c_void_p(0))
+        assert rc != 0, (c, dtype)
+        assert needle in lib.ddpb_last_error(), (c, dtype, lib.ddpb_last_error())
+    # the largest sizes that ARE accepted, checked against torch's own BatchNorm backward (fp32 oracle)
+    for c, dtype in ((MAX_C_F32, torch.float32), (MAX_C, torch.bfloat16)):
+        case = _case(7, c, 2, False, dtype, b=8)
+        y, dout, gamma, beta, mean, invstd = case
+        dy, dgamma, dbeta, _ = _run(lib, lib.ddpb_bn_relu_pool_bwd_noalloc, case, False, dtype, with_scratch=False)
+        yf = y.float().clone().requires_grad_(True)
+        g = gamma.clone().requires_grad_(True)
+        bt = beta.clone().requires_grad_(True)
+        x = yf.permute(0, 3, 1, 2)
+        out = torch.relu(torch.nn.functional.batch_norm(x, None, None, g, bt, True, 0.1, 1e-5))
+        out.backward(dout.float().permute(0, 3, 1, 2))
+        tol = 2e-4 if dtype == torch.float32 else 1.5e-2
+        assert _rel(dy, yf.grad) < tol and _rel(dgamma, g.grad) < tol and _rel(dbeta, bt.grad) < tol
