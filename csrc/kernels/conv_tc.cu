@@ -44,6 +44,7 @@ struct ConvTcParams {
   int slice_extent;        // NC > 1: extent of one slice along slice_dim
   int pdl;                 // 1: execute griddepcontrol.launch_dependents (captured launches only, see common.cuh)
   int taps;                // 9 = 3x3 filter, 1 = 1x1 (plain GEMM over the pixel rows; first-layer patch matrix)
+  unsigned long long* trace;   // nullable: [ctas][8] %globaltimer stamps of this CTA's phases (ddpb_conv3x3_trace)
   bf16* out_raw;           // output matrix [total_pixels][n_out]
   int w_shift, h_shift;    // log2(W), log2(H)
   // dgrad only: BatchNorm-backward reduction of the previous block, fused into the epilogue (bn_y == null: off).
@@ -101,6 +102,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+  unsigned long long* const trc =
+      prm.trace ? prm.trace + 8ull * (blockIdx.x + gridDim.x * (blockIdx.y + (unsigned long long)gridDim.y * blockIdx.z)) : nullptr;
+  if (trc && threadIdx.x == 0) trc[0] = global_timer_ns();            // CTA started
 
   // output tile -> (image, row) origin of the pixel box
   int n0, h0;
@@ -124,6 +128,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   // dependent launch); global memory may only be touched after pdl_wait()
   if (prm.pdl) pdl_launch_dependents();
   pdl_wait();
+  if (trc && threadIdx.x == 0) trc[1] = global_timer_ns();            // prologue done, predecessor finished
   if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? ld_coh(&bias[n_tile * BN + i]) : 0.f;
   tc_fence_before();
   __syncthreads();
@@ -175,6 +180,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int it = 0; it < k_iters; ++it) {
         const int stage = it % STAGES, use = it / STAGES;
         mbar_wait(&full_bar[stage], use & 1);
+        if (trc && it == 0) trc[2] = global_timer_ns();               // first stage landed
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
         const uint32_t sb = sa + A_BYTES;
@@ -191,6 +197,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         if (NC == 1) umma_commit(&empty_bar[stage]); else umma_commit_mc(&empty_bar[stage], MC_MASK);
       }
       umma_commit(accum_bar);                  // accumulator complete
+      if (trc) trc[3] = global_timer_ns();                             // last MMA issued
     }
   } else {
     // ===================== epilogue warps (2..5) =====================
@@ -213,6 +220,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     mbar_wait(accum_bar, 0);
     tc_fence_after();
+    if (trc && threadIdx.x == 64) trc[4] = global_timer_ns();         // accumulator complete
   }
   // Epilogue, common to all variants.  This CTA finishes CW = BN / KS columns of the 128-row tile:
   //   0. (KS > 1) reduce-scatter of the fp32 partial tiles through distributed shared memory
@@ -254,6 +262,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     __syncwarp();
     cluster_barrier();                          // #1: all partial column blocks have been delivered
+    if (trc && threadIdx.x == 64) trc[5] = global_timer_ns();         // split-K partials exchanged
   }
   if (warp >= 2) {
     // ---- 1. accumulator -> bf16 tile in shared memory
@@ -320,6 +329,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           if (fmaf(v[j], sc[j], sh[j]) > 0.f) { s1[j] += d[j]; s2[j] = fmaf(d[j], (v[j] - mu[j]) * is[j], s2[j]); }
       }
     }
+    if (trc && threadIdx.x == 64) trc[6] = global_timer_ns();         // tile stored
     // ---- 3. per-channel totals of the CTA
     if (want_stats || bn_red) {
 #pragma unroll
@@ -420,6 +430,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   if (NC > 1) cluster_barrier();      // peers may still arrive on our barriers: do not exit before them
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
+  if (trc && threadIdx.x == 0) trc[7] = global_timer_ns();            // CTA done
 }
 
 template <int BN, int STAGES>
@@ -431,16 +442,14 @@ void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn) {
   else { *bw = W; *bh = H; *bn = pixels / (H * W); }
 }
 
-// Arguments of the fused BatchNorm-backward reduction (set by ddpb_conv3x3_dgrad_bnred_tc around its
-// dispatch; a thread-local instead of one more parameter through every tile variant's call).
+// Arguments of the fused BatchNorm-backward reduction (ddpb_conv3x3_dgrad_bnred_tc).
 struct BnRedArgs {
   const void* y = nullptr;
   const float *mean = nullptr, *invstd = nullptr, *gamma = nullptr, *beta = nullptr;
   float* sums = nullptr;
 };
-static thread_local BnRedArgs g_bnred;
 
-// Arguments of the fused BatchNorm forward (set by ddpb_conv3x3_fwd_bn_tc around its dispatch).
+// Arguments of the fused BatchNorm forward (ddpb_conv3x3_fwd_bn_tc).
 struct BnFwdArgs {
   void *out = nullptr, *winner = nullptr;
   const float *gamma = nullptr, *beta = nullptr;
@@ -451,11 +460,19 @@ struct BnFwdArgs {
   float eps = 1e-5f, momentum = 0.1f;
   bool applied = false;      // out: did the launch run with the fusion (all CTAs co-resident)?
 };
-static thread_local BnFwdArgs g_bnfwd;
+
+// Everything beyond the plain convolution that an entry point may ask of a launch; handed down the tile
+// dispatch explicitly (it used to travel in thread-local variables around the public API).
+struct ConvExtra {
+  const BnRedArgs* bnred = nullptr;       // dgrad: fuse the previous block's BatchNorm-backward reduction
+  BnFwdArgs* bnfwd = nullptr;             // fprop: fuse this block's BatchNorm forward behind a grid barrier
+  unsigned long long* trace = nullptr;    // per-CTA phase time stamps
+};
+static const ConvExtra kNoExtra;
 
 template <int BN, int STAGES, bool DGRAD, int NC = 1, int KS = 1>
 static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, float* stats, int B, int H, int W,
-                  int Cin, int Cout, cudaStream_t stream, int taps = 9) {
+                  int Cin, int Cout, cudaStream_t stream, const ConvExtra& ex = kNoExtra, int taps = 9) {
   const int Kc = DGRAD ? Cout : Cin;     // reduction channels
   const int Nc = DGRAD ? Cin : Cout;     // output channels
   int bw, bh, bn;
@@ -489,7 +506,9 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   while ((1 << prm.w_shift) < W) ++prm.w_shift;
   while ((1 << prm.h_shift) < H) ++prm.h_shift;
   // fused BatchNorm-backward reduction requested by ddpb_conv3x3_dgrad_bnred_tc (dgrad only)
-  const BnRedArgs& br = g_bnred;
+  static const BnRedArgs no_bnred;
+  const BnRedArgs& br = ex.bnred ? *ex.bnred : no_bnred;
+  prm.trace = ex.trace;
   prm.bn_y = DGRAD ? (const bf16*)br.y : nullptr;
   prm.bn_mean = br.mean; prm.bn_invstd = br.invstd; prm.bn_gamma = br.gamma; prm.bn_beta = br.beta;
   prm.bn_sums = br.sums;
@@ -508,7 +527,8 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     // occupancy query below reports that)
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   }
-  if (!DGRAD && g_bnfwd.out && stats) {
+  if (!DGRAD && ex.bnfwd && ex.bnfwd->out && stats) {
+    BnFwdArgs& g_bnfwd = *ex.bnfwd;
     // the fused BatchNorm needs a grid-wide barrier: only when every CTA is resident at the same time
     static int capacity = -1;
     if (capacity < 0) {
@@ -602,6 +622,55 @@ static int check_shapes(int B, int H, int W, int Cin, int Cout) {
   return DDPB_OK;
 }
 
+// One dispatcher for fprop and dgrad: n_ch is the GEMM N dimension (Cout for fprop, Cin for dgrad).
+template <bool DGRAD>
+static int dispatch(const void* in_v, const void* w_v, void* out_v, const float* bias, float* stats, int B, int H, int W,
+                    int Cin, int Cout, int tile_n, cudaStream_t stream, const ConvExtra& ex) {
+  int rc = check_shapes(B, H, W, Cin, Cout);
+  if (rc) return rc;
+  const char* what = DGRAD ? "conv_tc dgrad" : "conv_tc fwd";
+  const int n_ch = DGRAD ? Cin : Cout, k_ch = DGRAD ? Cout : Cin;
+  if (tile_n == 0) tile_n = auto_tile(B, H, W, n_ch, k_ch);
+  const bf16 *in = (const bf16*)in_v, *w = (const bf16*)w_v;
+  bf16* out = (bf16*)out_v;
+#define DDPB_CONV(BN_, ST_, NC_, KS_) launch<BN_, ST_, DGRAD, NC_, KS_>(in, w, out, bias, stats, B, H, W, Cin, Cout, stream, ex)
+  if (tile_n > 2000 && tile_n < 4000) {
+    DDPB_REQUIRE(n_ch % (tile_n - 2000) == 0, "%s: %d channels are not a multiple of pair tile %d", what, n_ch, tile_n - 2000);
+    DDPB_REQUIRE(!(ex.bnred && ex.bnred->y) && !(ex.bnfwd && ex.bnfwd->out),
+                 "%s: pair tiles (DDPB_CONV_2CTA) have no fused BatchNorm epilogues", what);
+    return launch_conv_tc2(DGRAD, tile_n - 2000, in, w, out, bias, stats, B, H, W, Cin, Cout, stream);
+  }
+  if (tile_n > 4000) {          // 4<splits><tile>: cluster split-K
+    DDPB_REQUIRE(n_ch % (tile_n % 100 == 28 ? 128 : 64) == 0, "%s: %d channels do not fit tile code %d", what, n_ch, tile_n);
+    switch (tile_n) {
+      case 4264: return cta_count(B, H, W, n_ch, 64) * 2 <= sm_count() ? DDPB_CONV(64, 8, 1, 2) : DDPB_CONV(64, 4, 1, 2);
+      case 4464: return DDPB_CONV(64, 4, 1, 4);
+      case 4228: return DDPB_CONV(128, 3, 1, 2);
+      case 4428: return DDPB_CONV(128, 3, 1, 4);
+      default: DDPB_REQUIRE(false, "%s: unknown split-K tile code %d", what, tile_n);
+    }
+  }
+  if (tile_n > 1000) {          // 1<cluster><tile>: activation tile multicast across a cluster of n-tiles
+    const bool deep = cta_count(B, H, W, n_ch, 64) <= sm_count();
+    switch (tile_n) {
+      case 1864: return deep ? DDPB_CONV(64, 8, 8, 1) : DDPB_CONV(64, 4, 8, 1);
+      case 1464: return deep ? DDPB_CONV(64, 8, 4, 1) : DDPB_CONV(64, 4, 4, 1);
+      case 1264: return DDPB_CONV(64, 4, 2, 1);
+      case 1228: return DDPB_CONV(128, 3, 2, 1);
+      case 1428: return DDPB_CONV(128, 3, 4, 1);
+      default: DDPB_REQUIRE(false, "%s: unknown multicast tile code %d", what, tile_n);
+    }
+  }
+  DDPB_REQUIRE(n_ch % tile_n == 0, "%s: %d channels are not a multiple of tile %d", what, n_ch, tile_n);
+  if (tile_n == 128) return DDPB_CONV(128, 3, 1, 1);
+  if (tile_n == 64) {
+    // fewer CTAs than SMs: one CTA per SM with a deep pipeline (more bytes in flight per CTA)
+    return cta_count(B, H, W, n_ch, 64) <= sm_count() ? DDPB_CONV(64, 8, 1, 1) : DDPB_CONV(64, 4, 1, 1);
+  }
+#undef DDPB_CONV
+  DDPB_REQUIRE(false, "%s: tile_n must be 64 or 128", what);
+}
+
 }  // namespace ddpb
 
 using namespace ddpb;
@@ -610,103 +679,26 @@ using namespace ddpb;
 // `stats` (fp32 [2*Cout], may be null) ACCUMULATES per-channel sum and sum of squares of y.
 extern "C" int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const float* bias, void* y, float* stats,
                                    int B, int H, int W, int Cin, int Cout, int tile_n, cudaStream_t stream) {
-  int rc = check_shapes(B, H, W, Cin, Cout);
-  if (rc) return rc;
-  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cout, Cin);
-  if (tile_n > 2000 && tile_n < 4000) {
-    DDPB_REQUIRE(Cout % (tile_n - 2000) == 0, "conv_tc fwd: Cout %d not a multiple of pair tile %d", Cout, tile_n - 2000);
-    return launch_conv_tc2(false, tile_n - 2000, x, w_bf16, y, bias, stats, B, H, W, Cin, Cout, stream);
-  }
-  if (tile_n > 4000) {          // 4<splits><tile>: cluster split-K
-    const bf16 *xi = (const bf16*)x, *wi = (const bf16*)w_bf16;
-    bf16* yo = (bf16*)y;
-    DDPB_REQUIRE(Cout % (tile_n % 100 == 28 ? 128 : 64) == 0, "conv_tc fwd: Cout %d does not fit tile code %d", Cout, tile_n);
-    switch (tile_n) {
-      case 4264: return cta_count(B, H, W, Cout, 64) * 2 <= sm_count()
-                            ? launch<64, 8, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
-                            : launch<64, 4, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      case 4464: return launch<64, 4, false, 1, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      case 4228: return launch<128, 3, false, 1, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      case 4428: return launch<128, 3, false, 1, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      default: DDPB_REQUIRE(false, "conv_tc fwd: unknown split-K tile code %d", tile_n);
-    }
-  }
-  if (tile_n > 1000) {          // 1<cluster><tile>: activation tile multicast across a cluster of n-tiles
-    const bf16 *xi = (const bf16*)x, *wi = (const bf16*)w_bf16;
-    bf16* yo = (bf16*)y;
-    const bool deep = cta_count(B, H, W, Cout, 64) <= sm_count();
-    switch (tile_n) {
-      case 1864: return deep ? launch<64, 8, false, 8>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
-                             : launch<64, 4, false, 8>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      case 1464: return deep ? launch<64, 8, false, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream)
-                             : launch<64, 4, false, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      case 1264: return launch<64, 4, false, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      case 1228: return launch<128, 3, false, 2>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      case 1428: return launch<128, 3, false, 4>(xi, wi, yo, bias, stats, B, H, W, Cin, Cout, stream);
-      default: DDPB_REQUIRE(false, "conv_tc fwd: unknown multicast tile code %d", tile_n);
-    }
-  }
-  DDPB_REQUIRE(Cout % tile_n == 0, "conv_tc fwd: Cout %d not a multiple of tile %d", Cout, tile_n);
-  if (tile_n == 128)
-    return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
-  if (tile_n == 64) {
-    // fewer CTAs than SMs: one CTA per SM with a deep pipeline (more bytes in flight per CTA)
-    if (cta_count(B, H, W, Cout, 64) <= sm_count())
-      return launch<64, 8, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
-    return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream);
-  }
-  DDPB_REQUIRE(false, "conv_tc fwd: tile_n must be 64 or 128");
+  return dispatch<false>(x, w_bf16, y, bias, stats, B, H, W, Cin, Cout, tile_n, stream, kNoExtra);
 }
 
 // dx[B,H,W,Cin] = conv3x3_transpose(dy[B,H,W,Cout], w[Cout,3,3,Cin]); bf16 in/out.
 extern "C" int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* dx, int B, int H, int W, int Cin,
                                      int Cout, int tile_n, cudaStream_t stream) {
-  int rc = check_shapes(B, H, W, Cin, Cout);
-  if (rc) return rc;
-  if (tile_n == 0) tile_n = auto_tile(B, H, W, Cin, Cout);
-  if (tile_n > 2000 && tile_n < 4000) {
-    DDPB_REQUIRE(Cin % (tile_n - 2000) == 0, "conv_tc dgrad: Cin %d not a multiple of pair tile %d", Cin, tile_n - 2000);
-    DDPB_REQUIRE(!g_bnred.y, "conv_tc dgrad: pair tiles (DDPB_CONV_2CTA) have no fused BatchNorm reduction");
-    return launch_conv_tc2(true, tile_n - 2000, dy, w_bf16, dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-  }
-  if (tile_n > 4000) {
-    const bf16 *di = (const bf16*)dy, *wi = (const bf16*)w_bf16;
-    bf16* xo = (bf16*)dx;
-    DDPB_REQUIRE(Cin % (tile_n % 100 == 28 ? 128 : 64) == 0, "conv_tc dgrad: Cin %d does not fit tile code %d", Cin, tile_n);
-    switch (tile_n) {
-      case 4264: return cta_count(B, H, W, Cin, 64) * 2 <= sm_count()
-                            ? launch<64, 8, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
-                            : launch<64, 4, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      case 4464: return launch<64, 4, true, 1, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      case 4228: return launch<128, 3, true, 1, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      case 4428: return launch<128, 3, true, 1, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      default: DDPB_REQUIRE(false, "conv_tc dgrad: unknown split-K tile code %d", tile_n);
-    }
-  }
-  if (tile_n > 1000) {
-    const bf16 *di = (const bf16*)dy, *wi = (const bf16*)w_bf16;
-    bf16* xo = (bf16*)dx;
-    const bool deep = cta_count(B, H, W, Cin, 64) <= sm_count();
-    switch (tile_n) {
-      case 1864: return deep ? launch<64, 8, true, 8>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
-                             : launch<64, 4, true, 8>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      case 1464: return deep ? launch<64, 8, true, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream)
-                             : launch<64, 4, true, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      case 1264: return launch<64, 4, true, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      case 1228: return launch<128, 3, true, 2>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      case 1428: return launch<128, 3, true, 4>(di, wi, xo, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-      default: DDPB_REQUIRE(false, "conv_tc dgrad: unknown multicast tile code %d", tile_n);
-    }
-  }
-  DDPB_REQUIRE(Cin % tile_n == 0, "conv_tc dgrad: Cin %d not a multiple of tile %d", Cin, tile_n);
-  if (tile_n == 128)
-    return launch<128, 3, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-  if (tile_n == 64) {
-    if (cta_count(B, H, W, Cin, 64) <= sm_count())
-      return launch<64, 8, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-    return launch<64, 4, true>((const bf16*)dy, (const bf16*)w_bf16, (bf16*)dx, nullptr, nullptr, B, H, W, Cin, Cout, stream);
-  }
-  DDPB_REQUIRE(false, "conv_tc dgrad: tile_n must be 64 or 128");
+  return dispatch<true>(dy, w_bf16, dx, nullptr, nullptr, B, H, W, Cin, Cout, tile_n, stream, kNoExtra);
+}
+
+// Either of the two with per-CTA phase time stamps (a tuning aid; no reference counterpart):
+// trace[cta][8] = %globaltimer (ns) at CTA start, prologue done (predecessor finished), first stage landed,
+// last MMA issued, accumulator complete, split-K partials exchanged, tile stored, CTA done.  Unused slots
+// keep what the caller put there.
+extern "C" int ddpb_conv3x3_trace(int dgrad, const void* in, const void* w_bf16, const float* bias, void* out,
+                                  float* stats, int B, int H, int W, int Cin, int Cout, int tile_n,
+                                  unsigned long long* trace, cudaStream_t stream) {
+  ConvExtra ex;
+  ex.trace = trace;
+  return dgrad ? dispatch<true>(in, w_bf16, out, nullptr, nullptr, B, H, W, Cin, Cout, tile_n, stream, ex)
+               : dispatch<false>(in, w_bf16, out, bias, stats, B, H, W, Cin, Cout, tile_n, stream, ex);
 }
 
 // y[B,H,W,Cout] = x[B,H,W,Cin] * w[Cout,Cin]^T + bias: the same kernel with a single (centre) tap.
@@ -717,8 +709,8 @@ extern "C" int ddpb_conv1x1_fwd_tc(const void* x, const void* w_bf16, const floa
   int rc = check_shapes(B, H, W, Cin, Cout);
   if (rc) return rc;
   if (Cout % 128 == 0 && cta_count(B, H, W, Cout, 128) >= sm_count())
-    return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
-  return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, 1);
+    return launch<128, 3, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, kNoExtra, 1);
+  return launch<64, 4, false>((const bf16*)x, (const bf16*)w_bf16, (bf16*)y, bias, stats, B, H, W, Cin, Cout, stream, kNoExtra, 1);
 }
 
 // dgrad as above, and in its epilogue the BatchNorm-backward reduction of the block whose OUTPUT dx is the
@@ -732,11 +724,11 @@ extern "C" int ddpb_conv3x3_dgrad_bnred_tc(const void* dy, const void* w_bf16, v
                                            cudaStream_t stream) {
   DDPB_REQUIRE(y_win && mean && invstd && gamma && beta && sums, "dgrad_bnred: null BatchNorm argument");
   DDPB_REQUIRE(tile_n < 2000 || tile_n > 4000, "dgrad_bnred: pair tiles have no fused reduction");
-  g_bnred.y = y_win; g_bnred.mean = mean; g_bnred.invstd = invstd; g_bnred.gamma = gamma; g_bnred.beta = beta;
-  g_bnred.sums = sums;
-  const int rc = ddpb_conv3x3_dgrad_tc(dy, w_bf16, dx, B, H, W, Cin, Cout, tile_n, stream);
-  g_bnred = BnRedArgs();
-  return rc;
+  BnRedArgs br;
+  br.y = y_win; br.mean = mean; br.invstd = invstd; br.gamma = gamma; br.beta = beta; br.sums = sums;
+  ConvExtra ex;
+  ex.bnred = &br;
+  return dispatch<true>(dy, w_bf16, dx, nullptr, nullptr, B, H, W, Cin, Cout, tile_n, stream, ex);
 }
 
 // Forward conv as above and, when the whole grid fits on the GPU at once, this block's BatchNorm (batch
@@ -757,13 +749,14 @@ extern "C" int ddpb_conv3x3_fwd_bn_tc(const void* x, const void* w_bf16, const f
   *fused = 0;
   if (tile_n > 2000 && tile_n < 4000)       // pair tiles have their own epilogue: no fusion
     return ddpb_conv3x3_fwd_tc(x, w_bf16, bias, y, stats, B, H, W, Cin, Cout, tile_n, stream);
-  g_bnfwd = BnFwdArgs();
-  g_bnfwd.out = act; g_bnfwd.winner = winner; g_bnfwd.gamma = gamma; g_bnfwd.beta = beta;
-  g_bnfwd.save_mean = save_mean; g_bnfwd.save_invstd = save_invstd;
-  g_bnfwd.running_mean = running_mean; g_bnfwd.running_var = running_var; g_bnfwd.nbt = num_batches_tracked;
-  g_bnfwd.barrier = barrier; g_bnfwd.pool = pool ? 1 : 0; g_bnfwd.eps = eps; g_bnfwd.momentum = momentum;
-  const int rc = ddpb_conv3x3_fwd_tc(x, w_bf16, bias, y, stats, B, H, W, Cin, Cout, tile_n, stream);
-  *fused = g_bnfwd.applied ? 1 : 0;
-  g_bnfwd = BnFwdArgs();
+  BnFwdArgs bf;
+  bf.out = act; bf.winner = winner; bf.gamma = gamma; bf.beta = beta;
+  bf.save_mean = save_mean; bf.save_invstd = save_invstd;
+  bf.running_mean = running_mean; bf.running_var = running_var; bf.nbt = num_batches_tracked;
+  bf.barrier = barrier; bf.pool = pool ? 1 : 0; bf.eps = eps; bf.momentum = momentum;
+  ConvExtra ex;
+  ex.bnfwd = &bf;
+  const int rc = dispatch<false>(x, w_bf16, y, bias, stats, B, H, W, Cin, Cout, tile_n, stream, ex);
+  *fused = bf.applied ? 1 : 0;
   return rc;
 }

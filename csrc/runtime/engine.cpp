@@ -81,7 +81,7 @@ struct Engine {
   cudaStream_t comm = nullptr, comm2 = nullptr, wg = nullptr;
   bool two_comm = true, comm2_used = false;   // multi-GPU: buckets alternate between two streams (DDPB_TWO_COMM=0: one)
   std::vector<cudaEvent_t> bucket_ev, ev_dy, ev_dg, ev_wg;
-  cudaEvent_t join_ev = nullptr, fork_ev = nullptr;
+  cudaEvent_t join_ev = nullptr, fork_ev = nullptr, zero_ev = nullptr, start_ev = nullptr;
   std::map<long long, Graph> graphs;     // key = kind * 1e6 + batch
   long long launches = 0, counting = 0;
   bool count_only = false;
@@ -89,7 +89,36 @@ struct Engine {
   bool prof_on = false;
   cudaEvent_t prof_start = nullptr, prof_fwd = nullptr, prof_bwd = nullptr, prof_end = nullptr;
   std::vector<cudaEvent_t> prof_ready, prof_done;
+  // per-kernel trace (ddpb_engine_trace_step): one event after every launch, on its stream
+  struct TraceRec { char name[48]; int block; int stream; cudaEvent_t ev; };
+  bool trace_on = false;
+  bool trace_external = false;         // tracing inside a stream capture: event-record NODES (cudaEventRecordExternal)
+  int trace_block = -1;                // conv block the launches belong to (-1: classifier / optimizer)
+  size_t trace_n = 0;
+  std::vector<TraceRec> trace;         // events are created once and reused
+  cudaEvent_t trace_start = nullptr;
+  cudaStream_t trace_main = nullptr;
 };
+
+static int trace_mark(Engine* e, cudaStream_t stream, const char* call_text) {
+  if (e->trace_n == e->trace.size()) {
+    Engine::TraceRec r;
+    memset(&r, 0, sizeof(r));
+    DDPB_CUDA_CHECK(cudaEventCreate(&r.ev));
+    e->trace.push_back(r);
+  }
+  Engine::TraceRec& r = e->trace[e->trace_n++];
+  const char* p = call_text;
+  if (!strncmp(p, "ddpb_", 5)) p += 5;
+  size_t n = 0;
+  while (p[n] && p[n] != '(' && n + 1 < sizeof(r.name)) { r.name[n] = p[n]; ++n; }
+  r.name[n] = 0;
+  r.block = e->trace_block;
+  r.stream = stream == e->trace_main ? 0 : (stream == e->wg ? 1 : (stream == e->comm ? 2 : (stream == e->comm2 ? 3 : 4)));
+  if (e->trace_external) DDPB_CUDA_CHECK(cudaEventRecordWithFlags(r.ev, stream, cudaEventRecordExternal));
+  else DDPB_CUDA_CHECK(cudaEventRecord(r.ev, stream));
+  return DDPB_OK;
+}
 
 #define ECHECK(call)        \
   do {                      \
@@ -287,6 +316,8 @@ static int alloc_all(Engine* e) {
   for (auto& ev : e->bucket_ev) DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->join_ev, cudaEventDisableTiming));
   DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->fork_ev, cudaEventDisableTiming));
+  DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->zero_ev, cudaEventDisableTiming));
+  DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->start_ev, cudaEventDisableTiming));
   return DDPB_OK;
 }
 
@@ -305,53 +336,69 @@ static bool use_tc_first(const Engine* e, const Block& b) {
   return e->cfg.dtype == DDPB_BF16 && e->cfg.use_tc && b.cin == 3 && b.cout % 64 == 0 && b.hw == 32 && e->x0cols;
 }
 
-#define LAUNCH(e, call)   \
-  do {                    \
-    ECHECK(call);         \
-    (e)->counting += 1;   \
+// Every kernel launch of the step goes through here: counted (the launch count bench.py reports) and,
+// while a trace is being taken (ddpb_engine_trace_step), followed by an event on the launching stream.
+#define LAUNCH(e, stream, call)                                   \
+  do {                                                            \
+    ECHECK(call);                                                 \
+    (e)->counting += 1;                                           \
+    if ((e)->trace_on) ECHECK(trace_mark((e), (stream), #call));  \
   } while (0)
 
-static int forward(Engine* e, int B, int training, cudaStream_t s) {
+
+// zero_grads: also clear the gradient arena, on the weight-gradient stream, so that the 37 MB memset
+// overlaps the forward pass instead of opening backward (only when forward and backward are issued as ONE
+// unit - a whole step - because the fork is joined by backward()).
+static int forward(Engine* e, int B, int training, cudaStream_t s, bool zero_grads = false) {
   const int dt = e->cfg.dtype;
   float* fstats = e->scratch;
   if (training) {
     DDPB_CUDA_CHECK(cudaMemsetAsync(e->scratch, 0, e->scratch_floats * 4, s));
   }
+  if (zero_grads) {
+    // everything of the previous step (all streams were joined into s) precedes this point
+    DDPB_CUDA_CHECK(cudaEventRecord(e->start_ev, s));
+    DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->start_ev, 0));
+    DDPB_CUDA_CHECK(cudaMemsetAsync(e->grad, 0, e->arena_elems * 4, e->wg));
+    DDPB_CUDA_CHECK(cudaEventRecord(e->zero_ev, e->wg));
+  }
   const void* x = e->input;
   for (size_t i = 0; i < e->blocks.size(); ++i) {
     Block& b = e->blocks[i];
+    e->trace_block = (int)i;
     float* st = training ? fstats + b.stat_off : nullptr;
     const float* bias = e->master + b.conv_b.off;
     int bn_fused = 0;
     if (use_tc(e, b) && training && e->fuse_bn_fwd) {
       // conv + BatchNorm + ReLU + pool in one kernel when the grid fits on the GPU at once
       unsigned int* barrier = reinterpret_cast<unsigned int*>(e->scratch + e->total_c * 4 + 32) + i;
-      LAUNCH(e, ddpb_conv3x3_fwd_bn_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0,
+      LAUNCH(e, s, ddpb_conv3x3_fwd_bn_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0,
                                        e->master + b.bn_w.off, e->master + b.bn_b.off, b.act, b.win,
                                        e->mean + b.ch_off, e->invstd + b.ch_off, e->rmean + b.ch_off,
                                        e->rvar + b.ch_off, e->nbt + i, b.pool, 1e-5f, 0.1f, barrier, &bn_fused, s));
     } else if (use_tc(e, b))
-      LAUNCH(e, ddpb_conv3x3_fwd_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+      LAUNCH(e, s, ddpb_conv3x3_fwd_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0, s));
     else if (use_tc_first(e, b)) {
-      LAUNCH(e, ddpb_im2col3x3_c3(x, e->shadow + b.conv_w.off, e->x0cols, e->w0pad, B, b.hw, b.hw, b.cout, 0, s));
-      LAUNCH(e, ddpb_gemm_rows_fwd_tc(e->x0cols, e->w0pad, bias, b.y, st, (long long)B * b.hw * b.hw, b.cout, s));
+      LAUNCH(e, s, ddpb_im2col3x3_c3(x, e->shadow + b.conv_w.off, e->x0cols, e->w0pad, B, b.hw, b.hw, b.cout, 0, s));
+      LAUNCH(e, s, ddpb_gemm_rows_fwd_tc(e->x0cols, e->w0pad, bias, b.y, st, (long long)B * b.hw * b.hw, b.cout, s));
     } else {
-      LAUNCH(e, ddpb_conv3x3_fwd_simt(x, e->master + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, dt, s));
+      LAUNCH(e, s, ddpb_conv3x3_fwd_simt(x, e->master + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, dt, s));
       if (st && !(b.cin == 3 && b.cout == 64)) e->counting += 1;       // separate channel_stats launch
     }
     if (!bn_fused)
-    LAUNCH(e, ddpb_bn_relu_pool_fwd_winner(b.y, st, e->master + b.bn_w.off, e->master + b.bn_b.off, b.act,
+    LAUNCH(e, s, ddpb_bn_relu_pool_fwd_winner(b.y, st, e->master + b.bn_w.off, e->master + b.bn_b.off, b.act,
                                            e->mean + b.ch_off, e->invstd + b.ch_off, e->rmean + b.ch_off,
                                            e->rvar + b.ch_off, e->nbt + i, training ? b.win : nullptr, B, b.hw, b.hw,
                                            b.cout, b.pool, training, 1e-5f, 0.1f, dt, s));
     x = b.act;
   }
+  e->trace_block = -1;
   return DDPB_OK;
 }
 
 static int loss_fwd(Engine* e, int B, int training, cudaStream_t s) {
   const Block& last = e->blocks.back();
-  LAUNCH(e, ddpb_fc_ce_fwd(last.act, e->master + e->fc_w.off, e->master + e->fc_b.off, e->target, e->logits,
+  LAUNCH(e, s, ddpb_fc_ce_fwd(last.act, e->master + e->fc_w.off, e->master + e->fc_b.off, e->target, e->logits,
                            training ? e->dlogits : nullptr, training ? e->loss : e->eval_loss,
                            training ? nullptr : e->correct, B, B, e->cfg.dtype, s));
   return DDPB_OK;
@@ -363,7 +410,7 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   if (c.world == 1 || !e->peers_set) {
     // single process (or NCCL fallback driven from Python): plain fused SGD on the bucket
     if (c.external_sync) return DDPB_OK;
-    LAUNCH(e, ddpb_sgd_step(e->master + b.off, e->mom + b.off, e->grad + b.off,
+    LAUNCH(e, s, ddpb_sgd_step(e->master + b.off, e->mom + b.off, e->grad + b.off,
                             c.dtype == DDPB_BF16 ? (void*)(e->shadow + b.off) : nullptr, b.numel, c.lr, c.momentum,
                             c.wd, 1.f, s));
     return DDPB_OK;
@@ -382,13 +429,13 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   if (e->mc_arena && b.mode == DDPB_P2P_TWOSHOT) {
     // NVLS: the switch reduces, one multicast store publishes (sync_p2p.cu, p2p_nvls_kernel)
     char* mc = (char*)e->mc_arena;
-    LAUNCH(e, ddpb_p2p_sync_nvls(mc + e->off_grad, mc + e->off_master,
+    LAUNCH(e, s, ddpb_p2p_sync_nvls(mc + e->off_grad, mc + e->off_master,
                                  c.dtype == DDPB_BF16 ? (void*)(mc + e->off_shadow) : nullptr, e->master, f, e->mom,
                                  e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr, c.momentum, c.wd, 0,
                                  last ? 0 : 1, s));
     return DDPB_OK;
   }
-  LAUNCH(e, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
+  LAUNCH(e, s, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
                           c.momentum, c.wd, blocks, s));
   return DDPB_OK;
 }
@@ -436,31 +483,33 @@ static int buckets_ready(Engine* e, int blk, cudaEvent_t ev_a, cudaEvent_t ev_b)
 //                         layers' BN-bwd / dgrad, which leave most SMs idle on the small layers
 //   comm                  the buckets' fused reduce + SGD kernels
 // dY is double-buffered so that BN-bwd(i-1) does not overwrite what wgrad(i) is still reading.
-static int backward(Engine* e, int B, cudaStream_t s) {
+static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false) {
   const auto& c = e->cfg;
   const int dt = c.dtype;
   const int L = (int)e->blocks.size();
   float* bsums = e->scratch + e->total_c * 2;
-  DDPB_CUDA_CHECK(cudaMemsetAsync(e->grad, 0, e->arena_elems * 4, s));
+  if (grads_zeroed) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->zero_ev, 0));    // cleared during forward(), on wg
+  else DDPB_CUDA_CHECK(cudaMemsetAsync(e->grad, 0, e->arena_elems * 4, s));
   const Block& last = e->blocks.back();
-  LAUNCH(e, ddpb_fc_bwd(last.act, e->master + e->fc_w.off, e->dlogits, e->dact, e->grad + e->fc_w.off,
+  LAUNCH(e, s, ddpb_fc_bwd(last.act, e->master + e->fc_w.off, e->dlogits, e->dact, e->grad + e->fc_w.off,
                         e->grad + e->fc_b.off, B, dt, s));
   DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[L], s));
   ECHECK(buckets_ready(e, -1, e->ev_dg[L], nullptr));
   bool reduced_by_dgrad = false;
   for (int i = L - 1; i >= 0; --i) {
     Block& b = e->blocks[i];
+    e->trace_block = i;
     const void* x_in = i == 0 ? e->input : e->blocks[i - 1].act;
     void* dy = e->dy_buf2[i & 1];
     if (i + 2 < L) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[i + 2], 0));   // previous reader of this dY buffer
     if (reduced_by_dgrad) {
       // the reduction pass already ran in the epilogue of dgrad(i + 1)
-      LAUNCH(e, ddpb_bn_relu_pool_bwd_apply(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off,
+      LAUNCH(e, s, ddpb_bn_relu_pool_bwd_apply(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off,
                                             e->master + b.bn_w.off, e->master + b.bn_b.off, bsums + b.stat_off, dy,
                                             e->grad + b.bn_w.off, e->grad + b.bn_b.off, e->grad + b.conv_b.off, B,
                                             b.hw, b.hw, b.cout, b.pool, dt, s));
     } else {
-      LAUNCH(e, ddpb_bn_relu_pool_bwd(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off, e->master + b.bn_w.off,
+      LAUNCH(e, s, ddpb_bn_relu_pool_bwd(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off, e->master + b.bn_w.off,
                                       e->master + b.bn_b.off, bsums + b.stat_off, dy, e->grad + b.bn_w.off,
                                       e->grad + b.bn_b.off, e->grad + b.conv_b.off, B, b.hw, b.hw, b.cout, b.pool,
                                       dt, s));
@@ -474,27 +523,28 @@ static int backward(Engine* e, int B, cudaStream_t s) {
       if (use_tc(e, b) && e->fuse_bn_reduce) {
         // dgrad(i) also reduces the BN-backward sums of block i - 1 (whose output gradient it produces)
         const Block& pb = e->blocks[i - 1];
-        LAUNCH(e, ddpb_conv3x3_dgrad_bnred_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0,
+        LAUNCH(e, s, ddpb_conv3x3_dgrad_bnred_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0,
                                               pb.pool ? pb.win : pb.y, e->mean + pb.ch_off, e->invstd + pb.ch_off,
                                               e->master + pb.bn_w.off, e->master + pb.bn_b.off, bsums + pb.stat_off,
                                               s));
         reduced_by_dgrad = true;
       } else if (use_tc(e, b))
-        LAUNCH(e, ddpb_conv3x3_dgrad_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+        LAUNCH(e, s, ddpb_conv3x3_dgrad_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
       else
-        LAUNCH(e, ddpb_conv3x3_dgrad_simt(dy, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
+        LAUNCH(e, s, ddpb_conv3x3_dgrad_simt(dy, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
     }
     DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[i], s));
     DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->ev_dy[i], 0));
     if (use_tc_wgrad(e, b))
-      LAUNCH(e, ddpb_conv3x3_wgrad_tc(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, e->wg));
+      LAUNCH(e, e->wg, ddpb_conv3x3_wgrad_tc(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, e->wg));
     else if (use_tc_first(e, b))
-      LAUNCH(e, ddpb_patch_wgrad_tc(dy, e->x0cols, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cout, 27, 27, 0, e->wg));
+      LAUNCH(e, e->wg, ddpb_patch_wgrad_tc(dy, e->x0cols, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cout, 27, 27, 0, e->wg));
     else
-      LAUNCH(e, ddpb_conv3x3_wgrad_simt(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, e->wg));
+      LAUNCH(e, e->wg, ddpb_conv3x3_wgrad_simt(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, dt, e->wg));
     DDPB_CUDA_CHECK(cudaEventRecord(e->ev_wg[i], e->wg));
     ECHECK(buckets_ready(e, i, e->ev_wg[i], e->ev_dg[i]));
   }
+  e->trace_block = -1;
   // join the weight-gradient stream (wgrads of blocks >= 2 were already waited for above)
   DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[0], 0));
   if (L > 1) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[1], 0));
@@ -516,10 +566,10 @@ static int backward(Engine* e, int B, cudaStream_t s) {
       peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
       peer_table(e, e->off_shadow, sh); peer_table(e, e->off_flags, f);
       int mode = c.strategy == 1 ? DDPB_P2P_ROOT : DDPB_P2P_TWOSHOT;
-      LAUNCH(e, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1, 0,
+      LAUNCH(e, s, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1, 0,
                               e->arena_elems, c.lr, c.momentum, c.wd, 0, s));
     } else {
-      LAUNCH(e, ddpb_sgd_step(e->master, e->mom, e->grad, dt == DDPB_BF16 ? (void*)e->shadow : nullptr,
+      LAUNCH(e, s, ddpb_sgd_step(e->master, e->mom, e->grad, dt == DDPB_BF16 ? (void*)e->shadow : nullptr,
                               e->arena_elems, c.lr, c.momentum, c.wd, 1.f, s));
     }
   }
@@ -542,14 +592,15 @@ struct NvtxRange {
 };
 
 static int run_kind(Engine* e, int kind, int B, cudaStream_t s) {
+  const bool whole = kind == KIND_STEP;
   if (kind & KIND_FWD) {
     NvtxRange r("ddpb.forward");
-    ECHECK(forward(e, B, 1, s));
+    ECHECK(forward(e, B, 1, s, whole));
     ECHECK(loss_fwd(e, B, 1, s));
   }
   if (kind & KIND_BWD) {
     NvtxRange r("ddpb.backward+sync+sgd");
-    ECHECK(backward(e, B, s));
+    ECHECK(backward(e, B, s, whole));
   }
   return DDPB_OK;
 }
@@ -663,6 +714,8 @@ extern "C" int ddpb_engine_destroy(void* handle) {
   for (auto& ev : e->bucket_ev) cudaEventDestroy(ev);
   if (e->join_ev) cudaEventDestroy(e->join_ev);
   if (e->fork_ev) cudaEventDestroy(e->fork_ev);
+  if (e->zero_ev) cudaEventDestroy(e->zero_ev);
+  if (e->start_ev) cudaEventDestroy(e->start_ev);
   for (auto& ev : e->ev_dy) cudaEventDestroy(ev);
   for (auto& ev : e->ev_dg) cudaEventDestroy(ev);
   for (auto& ev : e->ev_wg) cudaEventDestroy(ev);
@@ -780,10 +833,10 @@ extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s,
   e->counting = 0;
   int rc = DDPB_OK;
   cudaEventRecord(e->prof_start, s);
-  rc = forward(e, batch, 1, s);
+  rc = forward(e, batch, 1, s, true);
   if (!rc) rc = loss_fwd(e, batch, 1, s);
   cudaEventRecord(e->prof_fwd, s);
-  if (!rc) rc = backward(e, batch, s);
+  if (!rc) rc = backward(e, batch, s, true);
   cudaEventRecord(e->prof_end, s);
   e->prof_on = false;
   e->launches += e->counting;
@@ -803,6 +856,70 @@ extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s,
   }
   (void)cudaGetLastError();
   *n_out = 3 + 2 * nb;
+  return DDPB_OK;
+}
+
+// One eager training step with an event after EVERY kernel launch: the per-kernel timeline of the step
+// as the GPU really runs it (warm caches, all streams concurrent), which an ncu launch list - serialised,
+// cold caches - cannot show.  Row i: names + 48 * i (NUL-terminated entry point name), block[i] (conv block,
+// -1 = classifier / optimizer), stream_id[i] (0 main, 1 weight-gradient, 2 / 3 communication), end_ms[i]
+// (completion time since the start of the step).  graphed = 1 runs the step as a CUDA graph with event-record
+// nodes (no host in the loop, three launches, the last one is read); 0 launches eagerly.  Real steps: weights
+// are updated.  Synchronises.
+extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, int graphed, char* names, int* block,
+                                      int* stream_id, float* end_ms, int max_rows, int* n_rows) {
+  Engine* e = (Engine*)handle;
+  DDPB_REQUIRE(e && names && block && stream_id && end_ms && n_rows, "engine_trace_step: null argument");
+  DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_trace_step: batch %d out of range", batch);
+  if (!e->trace_start) DDPB_CUDA_CHECK(cudaEventCreate(&e->trace_start));
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  if (graphed) {
+    // The step as the product path runs it - one CUDA graph, no host in the loop - with an event-record
+    // node after every kernel.  (Such a node sits between two kernels, so programmatic dependent launch
+    // does not apply across it: the rows are kernel times without prologue overlap.)
+    DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
+    DDPB_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  }
+  e->trace_on = true; e->trace_external = graphed != 0; e->trace_n = 0; e->trace_main = s; e->counting = 0;
+  if (graphed) cudaEventRecordWithFlags(e->trace_start, s, cudaEventRecordExternal);
+  else cudaEventRecord(e->trace_start, s);
+  int rc = forward(e, batch, 1, s, true);
+  if (!rc) rc = loss_fwd(e, batch, 1, s);
+  if (!rc) rc = backward(e, batch, s, true);
+  e->trace_on = false; e->trace_external = false;
+  if (graphed) {
+    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    if (rc || ce != cudaSuccess || !graph) {
+      (void)cudaGetLastError();
+      if (graph) cudaGraphDestroy(graph);
+      if (rc) return rc;
+      DDPB_REQUIRE(false, "engine_trace_step: capture failed (%s)", cudaGetErrorString(ce));
+    }
+    ce = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    DDPB_REQUIRE(ce == cudaSuccess, "engine_trace_step: cudaGraphInstantiate failed (%s)", cudaGetErrorString(ce));
+    for (int rep = 0; rep < 3; ++rep) DDPB_CUDA_CHECK(cudaGraphLaunch(exec, s));     // three real steps; the last one is read
+    e->launches += 3 * e->counting;
+  } else {
+    e->launches += e->counting;
+    if (rc) return rc;
+  }
+  DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
+  DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm));
+  DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm2));
+  DDPB_CUDA_CHECK(cudaStreamSynchronize(e->wg));
+  if (exec) cudaGraphExecDestroy(exec);
+  int n = 0;
+  for (size_t i = 0; i < e->trace_n && n < max_rows; ++i, ++n) {
+    const Engine::TraceRec& r = e->trace[i];
+    memcpy(names + 48 * n, r.name, 48);
+    block[n] = r.block; stream_id[n] = r.stream;
+    float ms = -1.f;
+    if (cudaEventElapsedTime(&ms, e->trace_start, r.ev) != cudaSuccess) { (void)cudaGetLastError(); ms = -1.f; }
+    end_ms[n] = ms;
+  }
+  *n_rows = n;
   return DDPB_OK;
 }
 

@@ -142,6 +142,12 @@ int ddpb_conv3x3_fwd_tc(const void* x, const void* w_bf16, const float* bias, vo
                         int W, int Cin, int Cout, int tile_n, cudaStream_t stream);
 int ddpb_conv3x3_dgrad_tc(const void* dy, const void* w_bf16, void* dx, int B, int H, int W, int Cin, int Cout,
                           int tile_n, cudaStream_t stream);
+/* Either of the two with per-CTA phase time stamps (tuning aid, no reference counterpart): trace[cta][8] =
+ * %globaltimer (ns) at CTA start, prologue done, first stage landed, last MMA issued, accumulator complete,
+ * split-K partials exchanged, tile stored, CTA done.  cta = x + gridDim.x * (y + gridDim.y * z). */
+int ddpb_conv3x3_trace(int dgrad, const void* in, const void* w_bf16, const float* bias, void* out, float* stats,
+                       int B, int H, int W, int Cin, int Cout, int tile_n, unsigned long long* trace,
+                       cudaStream_t stream);
 /* Forward conv and, when the whole grid is resident at once (*fused = 1), this block's training-mode
  * BatchNorm + ReLU + optional 2x2 max-pool in the same kernel (grid-wide barrier after the statistics).
  * *fused = 0: only y / stats were produced, run ddpb_bn_relu_pool_fwd(_winner) next.
@@ -292,6 +298,14 @@ int ddpb_engine_train_step(void* handle, int batch, cudaStream_t stream);
  * compute kernel of backward, out[2] step end, then (ready, done) per bucket; milliseconds since the
  * step start.  Exposed communication = out[2] - out[1].  Synchronises `stream`. */
 int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t stream, float* out, int max_out, int* n_out);
+/* Same idea at kernel granularity: one eager step with an event after every launch on every stream.
+ * Row i: names + 48 * i (entry point name), block[i] (conv block, -1 classifier / optimizer),
+ * stream_id[i] (0 main, 1 weight-gradient, 2 / 3 communication), end_ms[i] (completion time since the
+ * step start).  graphed = 1: the step runs as one CUDA graph with event-record nodes (the product path's
+ * timing, minus programmatic-launch overlap); 0: eager launches (host-bound for the small kernels).
+ * The reference has only three host timers per iteration (ref Part 1/main.py:33-43). */
+int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t stream, int graphed, char* names, int* block,
+                           int* stream_id, float* end_ms, int max_rows, int* n_rows);
 /* ref Part 1/main.py:61-76: eval-mode forward; accumulates info.eval_loss / info.correct. */
 int ddpb_engine_eval_step(void* handle, int batch, cudaStream_t stream);
 int ddpb_engine_eval_reset(void* handle, cudaStream_t stream);

