@@ -485,6 +485,16 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     else if (bn == 1 && bh % NC == 0) { sbh = bh / NC; prm.slice_dim = 2; prm.slice_extent = sbh; }
     else DDPB_REQUIRE(false, "conv_tc: cannot cut a %dx%dx%d pixel box into %d multicast slices", bw, bh, bn, NC);
     DDPB_REQUIRE((Nc / BN) % NC == 0, "conv_tc: %d channel tiles are not a multiple of the cluster size %d", Nc / BN, NC);
+    // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+    // GPU's memory hung the GPU: the multicast variants take nothing but a plain device allocation of the
+    // current device as their activation tensor (no peer / IPC / imported mapping).
+    int cur = -1;
+    cudaPointerAttributes pa;
+    DDPB_CUDA_CHECK(cudaGetDevice(&cur));
+    DDPB_CUDA_CHECK(cudaPointerGetAttributes(&pa, in));
+    DDPB_REQUIRE(pa.type == cudaMemoryTypeDevice && pa.device == cur,
+                 "conv_tc: the multicast tile variants need an activation tensor in the current GPU's own memory "
+                 "(pointer type %d on device %d, current device %d)", (int)pa.type, pa.device, cur);
   }
   CUtensorMap tmA, tmB;
   int rc = make_tmap_nhwc_bf16(&tmA, in, B, H, W, Kc, KCHUNK, bw, sbh, sbn);
