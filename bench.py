@@ -34,6 +34,7 @@ import subprocess
 import sys
 import threading
 import time
+import warnings
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -43,6 +44,22 @@ import torch.distributed as dist
 
 PER_GPU_BATCH = 256
 METRIC = "VGG-11 CIFAR-10 images/sec (Part 3 bucketed DP, max over ranks)"
+# --part: which of the reference's four scripts the run reproduces.  Part 3 is the headline (weak scaling,
+# 256 images per GPU: global batch 2048 at 8 GPUs).  Parts 1 / 2a / 2b keep the reference's own global batch
+# of 256 split as int(256 / world) (ref Part 2a/main.py:22,173): strong scaling.
+PART_SYNC = {"1": "none", "2a": "gather_scatter", "2b": "allreduce", "3": "bucketed"}
+PART_METRIC = {
+    "1": "VGG-11 CIFAR-10 images/sec (Part 1 single process)",
+    "2a": "VGG-11 CIFAR-10 images/sec (Part 2a rank-0 gather/scatter averaging, max over ranks)",
+    "2b": "VGG-11 CIFAR-10 images/sec (Part 2b all_reduce averaging, max over ranks)",
+    "3": METRIC,
+}
+
+
+def per_gpu_batch(part: str, world: int, override: int = 0) -> int:
+    if override:
+        return override
+    return PER_GPU_BATCH if part == "3" else int(256 / float(world))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -129,7 +146,7 @@ def max_over_ranks(ms: float, world: int) -> float:
     return float(t)
 
 
-def synthetic_host_batches(n: int, seed: int, kind: str):
+def synthetic_host_batches(n: int, seed: int, kind: str, PER_GPU_BATCH: int = PER_GPU_BATCH):
     """Pinned host batches. kind='u8' -> (uint8 NHWC images, labels, crop, flip) for our pipeline;
     kind='f32' -> (normalised fp32 NCHW, labels), i.e. what the reference's DataLoader delivers."""
     g = torch.Generator().manual_seed(1234 + seed)
@@ -160,11 +177,11 @@ def ensure_reference() -> str | None:
     return None
 
 
-def load_reference_part3(src: str):
+def load_reference_part(src: str, part_name: str = "3"):
     import importlib.util
-    part = os.path.join(src, "Part 3")
+    part = os.path.join(src, f"Part {part_name}")
     sys.path.insert(0, part)                      # main.py does `import model as mdl`
-    spec = importlib.util.spec_from_file_location("_ref_part3_main", os.path.join(part, "main.py"))
+    spec = importlib.util.spec_from_file_location(f"_ref_part{part_name}_main", os.path.join(part, "main.py"))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod
@@ -179,14 +196,18 @@ def run_reference(args) -> dict:
     except Exception as e:
         return {"impl": "reference", "unavailable": f"torchvision import failed: {e}"}
     rank, world, local = dist_setup(args.gpus)
+    part = args.part
+    if part == "1" and world > 1:
+        return {"impl": "reference", "unavailable": "Part 1 is a single-process script (ref Part 1/main.py:124-125)"}
+    PER_GPU_BATCH = per_gpu_batch(part, world, args.per_gpu_batch)
     with contextlib.redirect_stdout(io.StringIO()):
-        ref = load_reference_part3(src)
+        ref = load_reference_part(src, part)
     torch.set_num_threads(4)
 
     def one_run(autocast: bool, host_batches):
         torch.manual_seed(0)
         model = ref.mdl.VGG11().cuda()
-        if world > 1:
+        if world > 1 and part == "3":
             model = ref.DDP(model, device_ids=[local])
         opt = ref.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
         crit = torch.nn.CrossEntropyLoss().cuda()
@@ -216,14 +237,19 @@ def run_reference(args) -> dict:
 
         ctx = torch.autocast("cuda", dtype=torch.bfloat16) if autocast else contextlib.nullcontext()
         model.train()
-        with contextlib.redirect_stdout(io.StringIO()), ctx:
-            ref.train_model(model, loader(), opt, crit)      # the reference's own loop, unmodified
+        # The reference's own loop and sync function, unmodified.  Part 2a allocates its gather buffers with a
+        # bare torch.empty(...) (ref Part 2a/main.py:120): the default-device context makes that a CUDA tensor
+        # without touching the source.
+        extra = {"1": (0,), "2a": (rank,), "2b": (), "3": ()}[part]
+        with contextlib.redirect_stdout(io.StringIO()), ctx, torch.device("cuda", local), warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ref.train_model(model, loader(), opt, crit, *extra)
         barrier_sync(world)
         clocks = sampler.stop() if sampler else None
         ms = max_over_ranks(ev0.elapsed_time(ev1) / args.steps, world)
         return ms, clocks
 
-    host = synthetic_host_batches(8, rank, "f32")
+    host = synthetic_host_batches(8, rank, "f32", PER_GPU_BATCH)
     results = {}
     for name, ac in (("fp32", False), ("bf16_autocast", True)):
         dev_ms, clocks = one_run(ac, None)
@@ -235,16 +261,19 @@ def run_reference(args) -> dict:
     ms = results[best]["ms_per_step"]
     bytes_in = sum(t.numel() * t.element_size() for t in host[0])
     out = {
-        "impl": "reference", "metric": METRIC, "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world,
+        "impl": "reference", "metric": PART_METRIC[part], "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if best == "bf16_autocast" else "fp32(tf32 conv)",
+        "scaling": "weak" if part == "3" else "strong", "vs_baseline": None, "dtype": "bf16" if best == "bf16_autocast" else "fp32(tf32 conv)",
         "data": "synthetic", "clocks": results[best]["clocks"],
         "e2e": {"value": gb / results[best_e2e]["e2e_ms_per_step"] * 1e3, "unit": "images/s",
                 "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": 0,
                 "note": "reference loop reads the loss on the host only every 20 iterations (its print)"},
         "gpu_launches": 0,
         "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": PER_GPU_BATCH, "seq_len": None,
-                   "parallelism": f"dp{world}", "part": "3 (torch DDP)" if world > 1 else "3 (single GPU, no DDP wrap)",
+                   "parallelism": f"dp{world}",
+                   "part": {"1": "1 (single process)", "2a": "2a (dist.gather / mean / dist.scatter per parameter, NCCL)",
+                            "2b": "2b (dist.all_reduce per parameter, NCCL)",
+                            "3": "3 (torch DDP)" if world > 1 else "3 (single GPU, no DDP wrap)"}[part],
                    "variants": {k: {"images_per_s": gb / v["ms_per_step"] * 1e3,
                                     "e2e_images_per_s": gb / v["e2e_ms_per_step"] * 1e3} for k, v in results.items()},
                    "l2": "working set per step (activations + weights + grads) > 126 MB L2; no explicit flush"},
@@ -261,12 +290,17 @@ def run_ours(args) -> dict:
     from cs744_ddp_b200.engine import NativeBackend
     from cs744_ddp_b200.data.pipeline import RawBatch
 
-    cfg = TrainConfig(num_nodes=world, rank=rank, sync="bucketed" if world > 1 else "none", dtype=args.dtype,
+    part = args.part
+    if part == "1" and world > 1:
+        return {"impl": "ours", "unavailable": "Part 1 is the single-process trainer: run it with --gpus 1"}
+    PER_GPU_BATCH = per_gpu_batch(part, world, args.per_gpu_batch)
+    sync = PART_SYNC[part] if world > 1 else "none"
+    cfg = TrainConfig(num_nodes=world, rank=rank, sync=sync, dtype=args.dtype,
                       device="cuda", backend="native", global_batch=PER_GPU_BATCH * world, synthetic=True,
                       bucket_plan=args.bucket_plan, bucket_cap_mb=args.bucket_cap_mb,
                       first_bucket_mb=args.first_bucket_mb, comm=args.comm, use_cuda_graph=not args.no_graph)
     be = NativeBackend(cfg, torch.device("cuda", local))
-    host = synthetic_host_batches(8, rank, "u8")
+    host = synthetic_host_batches(8, rank, "u8", PER_GPU_BATCH)
     dev = [RawBatch(*[t.cuda() for t in hb]) for hb in host[:4]]
     prepared = [be.prepare(b) for b in dev]
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -307,18 +341,20 @@ def run_ours(args) -> dict:
         sampler = ClockSampler(local) if (rank == 0 and not e2e) else None
         if sampler:
             sampler.start()
-        l0 = be.launch_count()
+        l0, k0 = be.launch_count(), be.launch_counts()
         ev0.record()
         steps(args.steps, e2e)
         ev1.record()
         barrier_sync(world)
         clocks = sampler.stop() if sampler else None
         launches = be.launch_count() - l0
-        return max_over_ranks(ev0.elapsed_time(ev1) / args.steps, world), clocks, launches
+        k1 = be.launch_counts()
+        by_name = {k: k1[k] - k0.get(k, 0) for k in k1 if k1[k] - k0.get(k, 0) > 0}
+        return max_over_ranks(ev0.elapsed_time(ev1) / args.steps, world), clocks, launches, by_name
 
     with torch.cuda.stream(be.stream):          # the engine's own (graph-capturable) stream
-        ms, clocks, launches = timed(False)
-        e2e_ms, _, _ = timed(True)
+        ms, clocks, launches, kernel_launches = timed(False)
+        e2e_ms, _, _, _ = timed(True)
         # device timeline of one (eager) step: how much of the gradient sync is exposed after backward
         barrier_sync(world)
         tl = [be.profile_step(*prepared[0]) for _ in range(3)][-1]
@@ -327,18 +363,36 @@ def run_ours(args) -> dict:
                 "eager_step_ms": round(tl["step_ms"], 4), "exposed_comm_ms": round(tl["exposed_comm_ms"], 4),
                 "exposed_comm_frac": round(tl["exposed_comm_frac"], 4),
                 "buckets_ready_done_ms": [[round(b["ready_ms"], 3), round(b["done_ms"], 3)] for b in tl["buckets"]]}
+    # Self-check of the work the number stands for: after all those steps every replica must hold the same
+    # weights, bit for bit (hash of the fp32 master arena, compared over the control plane), and the weights
+    # must have moved and stayed finite.
+    torch.cuda.synchronize()
+    m = be.master
+    digest = torch.stack([m.view(torch.int32).to(torch.int64).sum(), (m.view(torch.int32).to(torch.int64) * 31 % 1000003).sum(),
+                          torch.isfinite(m).all().to(torch.int64)])
+    replicas_equal, finite = True, bool(digest[2])
+    if world > 1:
+        all_d = [torch.zeros_like(digest) for _ in range(world)]
+        dist.all_gather(all_d, digest)
+        replicas_equal = all(bool(torch.equal(d[:2], all_d[0][:2])) for d in all_d)
+        finite = all(bool(d[2]) for d in all_d)
     gb = PER_GPU_BATCH * world
     bytes_in = sum(t.numel() * t.element_size() for t in host[0])
     return {
-        "impl": "ours", "metric": METRIC, "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world,
+        "impl": "ours", "metric": PART_METRIC[part], "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "clocks": clocks,
+        "scaling": "weak" if part == "3" else "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "clocks": clocks, "replicas_equal": replicas_equal, "weights_finite": finite,
+        "kernel_launches": kernel_launches,
         "e2e": {"value": gb / e2e_ms * 1e3, "unit": "images/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": 4},
         "gpu_launches": launches,
         "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": PER_GPU_BATCH, "seq_len": None,
-                   "parallelism": f"dp{world}", "part": "3 (bucketed P2P reduce fused with SGD)" if world > 1
-                   else "3 (single GPU)", "comm": be.comm_name(), "cuda_graph": be.uses_graph(),
+                   "parallelism": f"dp{world}",
+                   "part": ({"2a": "2a (rank-0 gather / mean / SGD / scatter in one fused P2P kernel after backward)",
+                             "2b": "2b (one fused all-reduce + SGD kernel over the whole arena after backward)",
+                             "3": "3 (bucketed reduce fused with SGD, overlapped with backward)"}[part] if world > 1
+                            else f"{part} (single GPU)"), "comm": be.comm_name(), "cuda_graph": be.uses_graph(),
                    "bucket_plan": args.bucket_plan if args.bucket_plan != "ddp" else
                    f"ddp(first {args.first_bucket_mb} MB, cap {args.bucket_cap_mb} MB)", "timeline": timeline,
                    "l2": "working set per step (activations + weights + grads) > 126 MB L2; no explicit flush"},
@@ -351,6 +405,10 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--part", default="3", choices=["1", "2a", "2b", "3"],
+                    help="which reference script to reproduce; 3 (default) is the headline config, 1/2a/2b keep "
+                         "the reference's global batch of 256 split across the ranks")
+    ap.add_argument("--per-gpu-batch", type=int, default=0, help="override the part's per-GPU batch")
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--bucket-plan", default="per_layer", choices=["ddp", "per_layer", "single"])
     ap.add_argument("--bucket-cap-mb", type=float, default=25.0, help="ddp plan: bucket size cap")

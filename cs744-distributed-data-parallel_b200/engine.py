@@ -454,11 +454,19 @@ class NativeBackend:
         if self._comm in ("p2p", "nvls"):
             torch.cuda.synchronize(self.device)
             dist.barrier()
+            self.gather_master()                    # rank 0 must hold every slice before it is the source
             check(self._lib.ddpb_engine_collective(self._handle, 0, stream_handle()), "bcast weights")
         else:
             dist.broadcast(self.master, src=0)
             check(self._lib.ddpb_engine_refresh_shadow(self._handle, stream_handle()), "refresh_shadow")
         self.sync_buffers()
+
+    def gather_master(self) -> None:
+        """The fp32 master of a conv weight lives, current, only on the rank that owns its slice (peers get
+        the bf16 copy they compute with); bring all slices everywhere before the weights are read in fp32
+        (``state_dict``, a broadcast, a consistency check).  A collective: every rank must call it."""
+        if self.world > 1 and self._comm in ("p2p", "nvls"):
+            check(self._lib.ddpb_engine_collective(self._handle, 3, stream_handle()), "gather master")
 
     def gather_momentum(self) -> None:
         """The two-shot reduce keeps each momentum slice only on the rank that owns it; bring all
@@ -504,6 +512,8 @@ class NativeBackend:
             flat[off: off + t.numel()].copy_(t.reshape(-1))
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
+        """The reference's 58 keys.  On a multi-GPU native run this is a collective (see ``gather_master``)."""
+        self.gather_master()
         params = self._export(self.master)
         sd: Dict[str, torch.Tensor] = {}
         for key in state_dict_keys(self.cfg.model):
@@ -614,6 +624,17 @@ class NativeBackend:
     def launch_count(self) -> int:
         self._refresh_info()
         return int(self.info.launches)
+
+    def launch_counts(self) -> Dict[str, int]:
+        """Kernel launches per C entry point since the engine was created (graph replays included)."""
+        buf = ctypes.create_string_buffer(4096)
+        self._lib.ddpb_engine_launch_counts(self._handle, buf, len(buf))
+        out: Dict[str, int] = {}
+        for item in buf.value.decode().split(";"):
+            if "=" in item:
+                k, v = item.split("=")
+                out[k] = int(v)
+        return out
 
     def comm_name(self) -> str:
         return self._comm

@@ -278,7 +278,12 @@ def _ptr_table(ptrs: Optional[Sequence[int]]):
 def p2p_sync(mode: int, grad_ptrs: Sequence[int], master_ptrs: Optional[Sequence[int]],
              shadow_ptrs: Optional[Sequence[int]], flag_ptrs: Optional[Sequence[int]], mom: Optional[torch.Tensor],
              epochs: Optional[torch.Tensor], rank: int, world: int, slot: int, off: int, n: int, lr: float = 0.0,
-             momentum: float = 0.0, wd: float = 0.0, blocks: int = 0, stream=None) -> None:
-    check(lib().ddpb_p2p_sync(mode, _ptr_table(grad_ptrs), _ptr_table(master_ptrs), _ptr_table(shadow_ptrs),
-                              _ptr_table(flag_ptrs), ptr(mom), ptr(epochs), rank, world, slot, cll(off), cll(n),
-                              cf(lr), cf(momentum), cf(wd), blocks, stream_handle(stream)), "p2p_sync")
+             momentum: float = 0.0, wd: float = 0.0, blocks: int = 0, stream=None,
+             shard: Optional[Sequence[int]] = None) -> None:
+    """``shard``: flat [lo0, hi0, lo1, hi1, ...] element ranges whose fp32 master stays with its owner."""
+    n_sh = len(shard) // 2 if shard else 0
+    tab = (ctypes.c_longlong * (2 * n_sh))(*shard) if n_sh else None
+    check(lib().ddpb_p2p_sync_sharded(mode, _ptr_table(grad_ptrs), _ptr_table(master_ptrs), _ptr_table(shadow_ptrs),
+                                      _ptr_table(flag_ptrs), ptr(mom), ptr(epochs), rank, world, slot, cll(off), cll(n),
+                                      cf(lr), cf(momentum), cf(wd), blocks, tab, n_sh, stream_handle(stream)),
+          "p2p_sync")

@@ -87,25 +87,39 @@ class SymmetricArena:
         return [b + off for b in self.peer_base]
 
     def sync(self, mode: int, off: int = 0, n: Optional[int] = None, lr: float = 0.0, momentum: float = 0.0,
-             wd: float = 0.0, slot: int = 0, blocks: int = 0, stream=None) -> None:
-        """One fused reduce(+SGD) / broadcast / all-gather over ``[off, off+n)`` (see sync_p2p.cu)."""
+             wd: float = 0.0, slot: int = 0, blocks: int = 0, stream=None, shard=None) -> None:
+        """One fused reduce(+SGD) / broadcast / all-gather over ``[off, off+n)`` (see sync_p2p.cu).
+        ``shard``: flat [lo, hi, ...] ranges whose fp32 master is not published (bf16 copy only)."""
         n = self.numel - off if n is None else n
         F.p2p_sync(mode, self._table(self.off_grad), self._table(self.off_master),
                    self._table(self.off_shadow) if self.with_shadow else None, self._table(self.off_flags),
-                   self.mom, self.epochs, self.rank, self.world, slot, off, n, lr, momentum, wd, blocks, stream)
+                   self.mom, self.epochs, self.rank, self.world, slot, off, n, lr, momentum, wd, blocks, stream, shard)
+
+    def allgather_master(self, off: int = 0, n: Optional[int] = None, slot: int = 2) -> None:
+        """Publish this rank's two-shot slice of the fp32 master (after sharded syncs)."""
+        n = self.numel - off if n is None else n
+        F.p2p_sync(nv.P2P_ALLGATHER, self._table(self.off_master), None, None, self._table(self.off_flags), None,
+                   self.epochs, self.rank, self.world, slot, off, n)
 
     def sync_nvls(self, off: int = 0, n: Optional[int] = None, lr: float = 0.0, momentum: float = 0.0,
-                  wd: float = 0.0, slot: int = 1, blocks: int = 0, stream=None) -> None:
-        """Two-shot reduce + SGD with the reduction done inside the NVSwitch (needs ``nvls=True``)."""
+                  wd: float = 0.0, slot: int = 1, blocks: int = 0, stream=None, shard=None,
+                  one_shot: bool = False) -> None:
+        """Reduce + SGD with the reduction done inside the NVSwitch (needs ``nvls=True``): two-shot (the
+        owner of a slice updates it and multicasts the result) or one-shot (every rank pulls the reduced
+        sum of the whole range and updates its own replica)."""
         if not self.mc_base:
             raise RuntimeError("this arena has no multicast mapping")
         n = self.numel - off if n is None else n
         tbl = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(b + self.off_flags) for b in self.peer_base])
-        check(self._lib.ddpb_p2p_sync_nvls(
+        n_sh = len(shard) // 2 if shard else 0
+        tab = (ctypes.c_longlong * (2 * n_sh))(*shard) if n_sh else None
+        check(self._lib.ddpb_p2p_sync_nvls_sharded(
+            nv.P2P_ONESHOT if one_shot else nv.P2P_TWOSHOT,
             ctypes.c_void_p(self.mc_base + self.off_grad), ctypes.c_void_p(self.mc_base + self.off_master),
-            ctypes.c_void_p(self.mc_base + self.off_shadow if self.with_shadow else 0), nv.ptr(self.master), tbl,
+            ctypes.c_void_p(self.mc_base + self.off_shadow if self.with_shadow else 0), nv.ptr(self.master),
+            nv.ptr(self.shadow) if self.with_shadow else None, tbl,
             nv.ptr(self.mom), nv.ptr(self.epochs), self.rank, self.world, slot, nv.cll(off), nv.cll(n), nv.cf(lr),
-            nv.cf(momentum), nv.cf(wd), blocks, 0, nv.stream_handle(stream)), "p2p_sync_nvls")
+            nv.cf(momentum), nv.cf(wd), blocks, 0, tab, n_sh, nv.stream_handle(stream)), "p2p_sync_nvls")
 
     def allreduce_mean_(self, off: int = 0, n: Optional[int] = None, two_shot: Optional[bool] = None,
                         blocks: int = 0) -> torch.Tensor:

@@ -9,23 +9,35 @@
 //   MODE_ONESHOT   K-S1  every rank reads all W copies of the range, reduces in rank order,
 //                        updates its own replica.                     (small ranges: 1 hop)
 //   MODE_TWOSHOT   K-S2  rank r reduces slice r (reduce-scatter), applies SGD to the slice it
-//                        owns (its momentum shard), then writes the new fp32 weights and bf16
-//                        copy into every peer (all-gather).  2(W-1)/W*S bytes per direction.
+//                        owns (its momentum shard), then writes the new weights into every peer
+//                        (all-gather).
 //   MODE_ROOT      K-S4  Part 2a semantics (ref Part 2a/main.py:117-127): rank 0 gathers every
 //                        rank's gradient, takes the mean, updates, scatters the result.
 //   MODE_BCAST     K-S5  every rank copies rank 0's range (DDP's init / BN-buffer broadcast,
 //                        ref Part 3/main.py:61).
-//   MODE_ALLGATHER       rank r publishes its two-shot slice of a buffer (momentum shards at
-//                        checkpoint time).
+//   MODE_ALLGATHER       rank r publishes its two-shot slice of a buffer (momentum / master shards
+//                        at checkpoint time).
+//   NVLS           K-S3  the two-shot (or one-shot) mode with the reduction done inside the NVSwitch.
+//
+// What crosses NVLink in the all-gather half.  The convolution kernels read their weights from the
+// bf16 copy only; the fp32 master of a conv weight is read by nobody but the optimizer.  So for the
+// element ranges the caller marks as "sharded" (the conv weights: 99.85 % of the bytes) the owner
+// keeps the fp32 master to itself, exactly like the momentum, and publishes 2 bytes per element
+// instead of 6.  Everything else (BN scale / shift, biases, the classifier: read as fp32 by the
+// forward kernels) is published in both precisions.  Stale master slices are brought up to date
+// with MODE_ALLGATHER before anyone reads a full state_dict.
 //
 // K-S7 barriers: each CTA b owns flags[slot][b][rank] in every rank's signal pad.  A barrier is
-// "store my epoch into everybody's pad (release.sys), spin until everybody's epoch shows up in
-// mine (acquire.sys)".  Epochs are per-CTA counters kept in device memory, so a captured CUDA
-// graph can replay the kernels unchanged.  Spins are bounded: a dead peer traps the kernel
+// "fence, store my epoch into everybody's pad, spin until everybody's epoch shows up in mine,
+// fence".  Epochs are per-CTA counters kept in device memory, so a captured CUDA graph can replay
+// the kernels unchanged.  Spins are bounded (DDPB_SYNC_TIMEOUT_S, default 120 s): a dead peer leaves
+// a (rank, peer, slot, phase, block, epoch) record in host-mapped memory and traps the kernel
 // instead of hanging the GPU.
 //
-// The reduction order is fixed (rank 0..W-1) so every rank computes bit-identical sums.
+// The reduction order is fixed (rank 0..W-1, or the switch's) so every rank computes identical sums.
 #include <stdlib.h>
+
+#include <mutex>
 
 #include "../common.cuh"
 #include "../../include/ddp_b200.h"
@@ -34,6 +46,7 @@ namespace ddpb {
 
 constexpr int P2P_MAX_RANKS = DDPB_MAX_RANKS;
 constexpr int P2P_MAX_BLOCKS = DDPB_P2P_MAX_BLOCKS;
+constexpr int P2P_MAX_SHARD = DDPB_P2P_MAX_SHARD_RANGES;
 
 struct P2PArgs {
   float* grad[P2P_MAX_RANKS];
@@ -44,18 +57,23 @@ struct P2PArgs {
   uint32_t* epochs;                    // local [slots][P2P_MAX_BLOCKS]
   int rank, world, slot;
   int skip_exit_barrier;               // 1: a later launch of the same step ends with the barrier instead
-  long long off, n;                    // element range, multiples of 4
+  long long off, n;                    // element range, multiples of 8
   float lr, momentum, wd;
+  unsigned long long timeout_ns;
+  unsigned int* err;                   // host-mapped [8] time-out record, or null
+  int n_shard;                         // element ranges whose fp32 master stays with its owner
+  long long shard[2 * P2P_MAX_SHARD];  // [lo, hi) pairs, multiples of 8
 };
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
   uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 // peer data: bypass L1 (each element is read once; never serve it from a stale line)
 __device__ __forceinline__ float4 ld_peer(const float* p) {
   float4 v;
@@ -70,113 +88,155 @@ __device__ __forceinline__ void st_peer(float* p, float4 v) {
                "f"(v.w)
                : "memory");
 }
-__device__ __forceinline__ void st_peer_u2(void* p, uint2 v) {
-  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+__device__ __forceinline__ void st_peer_u4(void* p, uint4 v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
 }
 
 // All threads of the CTA call this.  `phase` 0/1 selects the entry/exit flag set of the slot.
+//   release: bar.sync (the CTA's accesses are done) -> thread 0: fence.sys, then the W flag stores
+//   acquire: thread r polls rank r's flag with relaxed loads, then fence.sys -> bar.sync
+// One fence per side instead of a release store / acquire load per flag and per poll.
 __device__ __forceinline__ void cta_barrier_all_ranks(const P2PArgs& a, int phase) {
   if (a.world == 1 || a.flags[0] == nullptr) return;
   __syncthreads();
   __shared__ uint32_t s_epoch;
   const int idx = (a.slot * 2 + phase) * P2P_MAX_BLOCKS + blockIdx.x;
   if (threadIdx.x == 0) {
-    uint32_t e = a.epochs[idx] + 1;
+    const uint32_t e = a.epochs[idx] + 1;
     a.epochs[idx] = e;
     s_epoch = e;
-    __threadfence_system();          // everything this CTA (and earlier kernels) wrote is visible first
+    fence_sys();                     // everything this CTA (and earlier kernels) wrote is visible first
+    for (int r = 0; r < a.world; ++r) st_relaxed_sys(a.flags[r] + (size_t)idx * P2P_MAX_RANKS + a.rank, e);
   }
   __syncthreads();
   const uint32_t e = s_epoch;
   if ((int)threadIdx.x < a.world) {
     const int r = threadIdx.x;
-    st_release_sys(a.flags[r] + (size_t)idx * P2P_MAX_RANKS + a.rank, e);
     const uint32_t* mine = a.flags[a.rank] + (size_t)idx * P2P_MAX_RANKS + r;
-    const unsigned long long t0 = global_timer_ns();
     // signed distance handles the (theoretical) wrap of the 32-bit epoch
-    while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
-      if (global_timer_ns() - t0 > 20000000000ull) {      // 20 s: a peer died or never launched
-        printf("ddpb: rank %d timed out waiting for rank %d (slot %d phase %d block %d epoch %u)\n", a.rank, r,
-               a.slot, phase, blockIdx.x, e);
-        __trap();
+    if ((int32_t)(ld_relaxed_sys(mine) - e) < 0) {
+      const unsigned long long t0 = global_timer_ns();
+      while ((int32_t)(ld_relaxed_sys(mine) - e) < 0) {
+        if (global_timer_ns() - t0 > a.timeout_ns) {       // a peer died or never launched
+          if (a.err) {
+            a.err[1] = a.rank; a.err[2] = r; a.err[3] = a.slot; a.err[4] = phase; a.err[5] = blockIdx.x; a.err[6] = e;
+            __threadfence_system();
+            a.err[0] = 1;
+            __threadfence_system();
+          }
+          printf("ddpb: rank %d timed out waiting for rank %d (slot %d phase %d block %d epoch %u)\n", a.rank, r,
+                 a.slot, phase, blockIdx.x, e);
+          __trap();
+        }
       }
     }
+    fence_sys();
   }
   __syncthreads();
 }
 
-__device__ __forceinline__ void slice_of(long long n4, int world, int r, long long* lo, long long* hi) {
-  long long per = (n4 + world - 1) / world;
+__device__ __forceinline__ void slice_of(long long units, int world, int r, long long* lo, long long* hi) {
+  long long per = (units + world - 1) / world;
   long long a = per * r;
-  if (a > n4) a = n4;
+  if (a > units) a = units;
   long long b = a + per;
-  if (b > n4) b = n4;
+  if (b > units) b = units;
   *lo = a; *hi = b;
 }
 
-__device__ __forceinline__ float4 sgd_update(float4 g, float4& p, float4& m, float scale, float lr, float mom,
-                                             float wd) {
+// is arena element e inside one of the ranges whose fp32 master is not published?
+__device__ __forceinline__ bool is_sharded(const P2PArgs& a, long long e) {
+  bool in = false;
+  for (int k = 0; k < a.n_shard; ++k) in |= (e >= a.shard[2 * k]) & (e < a.shard[2 * k + 1]);
+  return in;
+}
+
+__device__ __forceinline__ void sgd_update(float4 g, float4& p, float4& m, float scale, float lr, float mom, float wd) {
   g.x = g.x * scale + wd * p.x; g.y = g.y * scale + wd * p.y;
   g.z = g.z * scale + wd * p.z; g.w = g.w * scale + wd * p.w;
   m.x = mom * m.x + g.x; m.y = mom * m.y + g.y; m.z = mom * m.z + g.z; m.w = mom * m.w + g.w;
   p.x -= lr * m.x; p.y -= lr * m.y; p.z -= lr * m.z; p.w -= lr * m.w;
-  return p;
+}
+__device__ __forceinline__ uint4 pack8(const float4& a, const float4& b) {
+  return make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
 }
 
 enum { MODE_ONESHOT = 0, MODE_TWOSHOT = 1, MODE_ROOT = 2, MODE_BCAST = 3, MODE_ALLGATHER = 4 };
 
+// The unit of work is 8 consecutive elements: two 16-byte fp32 accesses and one 16-byte bf16 access.
 template <int MODE>
 __global__ void __launch_bounds__(512)
 p2p_kernel(const P2PArgs a) {
   cta_barrier_all_ranks(a, 0);
-  const long long n4 = a.n / 4;
-  const long long base4 = a.off / 4;
+  const long long n8 = a.n / 8;
+  const long long base8 = a.off / 8;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long nthr = (long long)gridDim.x * blockDim.x;
   const float inv_w = 1.f / (float)a.world;
 
   if (MODE == MODE_ONESHOT || MODE == MODE_TWOSHOT || MODE == MODE_ROOT) {
-    long long lo = 0, hi = n4;
-    if (MODE == MODE_TWOSHOT) slice_of(n4, a.world, a.rank, &lo, &hi);
+    long long lo = 0, hi = n8;
+    if (MODE == MODE_TWOSHOT) slice_of(n8, a.world, a.rank, &lo, &hi);
     if (MODE == MODE_ROOT && a.rank != 0) hi = lo;          // only the root computes
-    // A peer load takes ~2 us over NVLink: each thread keeps U independent 16-byte loads per rank in
-    // flight (U elements `nthr` apart), otherwise the loop is bound by latency, not by the link.
-    constexpr int U = 4;
+    // A peer load takes ~2 us over NVLink: each thread keeps 2U independent 16-byte loads per rank in
+    // flight (U units `nthr` apart), otherwise the loop is bound by latency, not by the link.
+    constexpr int U = 2;
     for (long long i0 = lo + tid; i0 < hi; i0 += nthr * U) {
-      float4 s[U];
+      float4 s[U][2];
 #pragma unroll
-      for (int u = 0; u < U; ++u) s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int u = 0; u < U; ++u) s[u][0] = s[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
       for (int r = 0; r < P2P_MAX_RANKS; ++r) {          // fixed rank order: identical sums on every rank
         if (r < a.world) {
-          float4 g[U];
+          float4 g[U][2];
 #pragma unroll
           for (int u = 0; u < U; ++u) {
             const long long i = i0 + u * nthr;
-            const long long e = (base4 + (i < hi ? i : lo)) * 4;      // clamp: a harmless in-range re-read
-            g[u] = (r == a.rank) ? *reinterpret_cast<const float4*>(a.grad[r] + e) : ld_peer(a.grad[r] + e);
+            const long long e = (base8 + (i < hi ? i : lo)) * 8;      // clamp: a harmless in-range re-read
+            if (r == a.rank) {
+              g[u][0] = *reinterpret_cast<const float4*>(a.grad[r] + e);
+              g[u][1] = *reinterpret_cast<const float4*>(a.grad[r] + e + 4);
+            } else {
+              g[u][0] = ld_peer(a.grad[r] + e);
+              g[u][1] = ld_peer(a.grad[r] + e + 4);
+            }
           }
 #pragma unroll
-          for (int u = 0; u < U; ++u) { s[u].x += g[u].x; s[u].y += g[u].y; s[u].z += g[u].z; s[u].w += g[u].w; }
+          for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              s[u][h].x += g[u][h].x; s[u][h].y += g[u][h].y; s[u][h].z += g[u][h].z; s[u][h].w += g[u][h].w;
+            }
         }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const long long i = i0 + u * nthr;
         if (i >= hi) break;
-        const long long e = (base4 + i) * 4;
-        float4 p = *reinterpret_cast<const float4*>(a.master[a.rank] + e);
-        float4 m = *reinterpret_cast<const float4*>(a.mom + e);
-        sgd_update(s[u], p, m, inv_w, a.lr, a.momentum, a.wd);
-        *reinterpret_cast<float4*>(a.mom + e) = m;
-        uint2 sh = make_uint2(pack_bf16x2(p.x, p.y), pack_bf16x2(p.z, p.w));
+        const long long e = (base8 + i) * 8;
+        float* mp = a.master[a.rank] + e;
+        float4 p0 = *reinterpret_cast<const float4*>(mp), p1 = *reinterpret_cast<const float4*>(mp + 4);
+        float4 m0 = *reinterpret_cast<const float4*>(a.mom + e), m1 = *reinterpret_cast<const float4*>(a.mom + e + 4);
+        sgd_update(s[u][0], p0, m0, inv_w, a.lr, a.momentum, a.wd);
+        sgd_update(s[u][1], p1, m1, inv_w, a.lr, a.momentum, a.wd);
+        *reinterpret_cast<float4*>(a.mom + e) = m0;
+        *reinterpret_cast<float4*>(a.mom + e + 4) = m1;
+        const uint4 sh = pack8(p0, p1);
         if (MODE == MODE_ONESHOT) {
-          *reinterpret_cast<float4*>(a.master[a.rank] + e) = p;
-          if (a.shadow[a.rank]) *reinterpret_cast<uint2*>(a.shadow[a.rank] + e) = sh;
+          *reinterpret_cast<float4*>(mp) = p0;
+          *reinterpret_cast<float4*>(mp + 4) = p1;
+          if (a.shadow[a.rank]) *reinterpret_cast<uint4*>(a.shadow[a.rank] + e) = sh;
         } else {
+          // fp32 master of a sharded range stays here; peers only ever read its bf16 copy
+          const bool keep = a.shadow[a.rank] != nullptr && is_sharded(a, e);
+          if (keep) {
+            *reinterpret_cast<float4*>(mp) = p0;
+            *reinterpret_cast<float4*>(mp + 4) = p1;
+          }
           for (int r = 0; r < a.world; ++r) {
-            st_peer(a.master[r] + e, p);
-            if (a.shadow[r]) st_peer_u2(a.shadow[r] + e, sh);
+            if (!keep) { st_peer(a.master[r] + e, p0); st_peer(a.master[r] + e + 4, p1); }
+            if (a.shadow[r]) st_peer_u4(a.shadow[r] + e, sh);
           }
         }
       }
@@ -184,15 +244,15 @@ p2p_kernel(const P2PArgs a) {
   } else if (MODE == MODE_BCAST) {
     // `grad` holds the buffer being broadcast (any fp32 range of the symmetric arena)
     if (a.rank != 0)
-      for (long long i = tid; i < n4; i += nthr) {
-        const long long e = (base4 + i) * 4;
+      for (long long i = tid; i < n8 * 2; i += nthr) {
+        const long long e = base8 * 8 + i * 4;
         *reinterpret_cast<float4*>(a.grad[a.rank] + e) = ld_peer(a.grad[0] + e);
       }
   } else if (MODE == MODE_ALLGATHER) {
     long long lo, hi;
-    slice_of(n4, a.world, a.rank, &lo, &hi);
-    for (long long i = lo + tid; i < hi; i += nthr) {
-      const long long e = (base4 + i) * 4;
+    slice_of(n8, a.world, a.rank, &lo, &hi);
+    for (long long i = lo * 2 + tid; i < hi * 2; i += nthr) {
+      const long long e = base8 * 8 + i * 4;
       float4 v = *reinterpret_cast<const float4*>(a.grad[a.rank] + e);
       for (int r = 0; r < a.world; ++r)
         if (r != a.rank) st_peer(a.grad[r] + e, v);
@@ -207,8 +267,8 @@ p2p_kernel(const P2PArgs a) {
 // multicast object every rank's arena is bound to (runtime/vmm_arena.cpp): a multimem.ld_reduce on
 // such an address returns the sum of that element over all ranks, a multimem.st writes it to all
 // ranks.  Rank r owns slice r: one switch-reduced load, the SGD update on its momentum shard, one
-// multicast store of the new fp32 weight and one of the bf16 copy - about S bytes per direction per
-// GPU instead of 2(W-1)/W*S for the two-shot kernel, and no per-peer loop at all.
+// multicast store of the bf16 copy (and of the fp32 weight for the few ranges that are not sharded):
+// about S bytes out and S/2 bytes in per GPU for an S-byte gradient, and no per-peer loop at all.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
   float4 v;
@@ -223,8 +283,10 @@ __device__ __forceinline__ void multimem_st(float* mc, float4 v) {
                "f"(v.z), "f"(v.w)
                : "memory");
 }
-__device__ __forceinline__ void multimem_st_bf16x4(void* mc, uint2 v) {
-  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(mc), "r"(v.x), "r"(v.y) : "memory");
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
 }
 
 struct NvlsArgs {
@@ -232,40 +294,112 @@ struct NvlsArgs {
   float* mc_grad;
   float* mc_master;
   bf16* mc_shadow;         // may be null (fp32 compute)
+  int one_shot;            // 1: every rank reduces the WHOLE range through the switch and updates its own replica
 };
 
+template <int U>
 __global__ void __launch_bounds__(512)
 p2p_nvls_kernel(const NvlsArgs n) {
   const P2PArgs& a = n.base;
   cta_barrier_all_ranks(a, 0);
-  const long long n4 = a.n / 4, base4 = a.off / 4;
+  const long long n8 = a.n / 8, base8 = a.off / 8;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long nthr = (long long)gridDim.x * blockDim.x;
   const float inv_w = 1.f / (float)a.world;
-  long long lo, hi;
-  slice_of(n4, a.world, a.rank, &lo, &hi);
-  constexpr int U = 4;
+  long long lo = 0, hi = n8;
+  if (!n.one_shot) slice_of(n8, a.world, a.rank, &lo, &hi);
   for (long long i0 = lo + tid; i0 < hi; i0 += nthr * U) {
-    float4 s[U];
+    float4 s[U][2];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long i = i0 + u * nthr;
-      s[u] = multimem_ld_reduce_add(n.mc_grad + (base4 + (i < hi ? i : lo)) * 4);
+      const float* src = n.mc_grad + (base8 + (i < hi ? i : lo)) * 8;
+      s[u][0] = multimem_ld_reduce_add(src);
+      s[u][1] = multimem_ld_reduce_add(src + 4);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long i = i0 + u * nthr;
       if (i >= hi) break;
-      const long long e = (base4 + i) * 4;
-      float4 p = *reinterpret_cast<const float4*>(a.master[a.rank] + e);
-      float4 m = *reinterpret_cast<const float4*>(a.mom + e);
-      sgd_update(s[u], p, m, inv_w, a.lr, a.momentum, a.wd);
-      *reinterpret_cast<float4*>(a.mom + e) = m;
-      multimem_st(n.mc_master + e, p);
-      if (n.mc_shadow) multimem_st_bf16x4(n.mc_shadow + e, make_uint2(pack_bf16x2(p.x, p.y), pack_bf16x2(p.z, p.w)));
+      const long long e = (base8 + i) * 8;
+      float* mp = a.master[a.rank] + e;
+      float4 p0 = *reinterpret_cast<const float4*>(mp), p1 = *reinterpret_cast<const float4*>(mp + 4);
+      float4 m0 = *reinterpret_cast<const float4*>(a.mom + e), m1 = *reinterpret_cast<const float4*>(a.mom + e + 4);
+      sgd_update(s[u][0], p0, m0, inv_w, a.lr, a.momentum, a.wd);
+      sgd_update(s[u][1], p1, m1, inv_w, a.lr, a.momentum, a.wd);
+      *reinterpret_cast<float4*>(a.mom + e) = m0;
+      *reinterpret_cast<float4*>(a.mom + e + 4) = m1;
+      if (n.one_shot) {
+        // every rank computed the same update from the same switch-reduced sum: purely local stores
+        *reinterpret_cast<float4*>(mp) = p0;
+        *reinterpret_cast<float4*>(mp + 4) = p1;
+        if (a.shadow[a.rank]) *reinterpret_cast<uint4*>(a.shadow[a.rank] + e) = pack8(p0, p1);
+        continue;
+      }
+      if (n.mc_shadow != nullptr && is_sharded(a, e)) {
+        *reinterpret_cast<float4*>(mp) = p0;
+        *reinterpret_cast<float4*>(mp + 4) = p1;
+      } else {
+        multimem_st(n.mc_master + e, p0);
+        multimem_st(n.mc_master + e + 4, p1);
+      }
+      if (n.mc_shadow) multimem_st_bf16x8(n.mc_shadow + e, pack8(p0, p1));
     }
   }
   if (!a.skip_exit_barrier) cta_barrier_all_ranks(a, 1);
+}
+
+// ---- host side -----------------------------------------------------------------------------
+static unsigned int* g_err_host = nullptr;       // pinned, mapped, portable: one record per process
+static std::mutex g_err_mutex;
+
+static unsigned int* err_record() {
+  std::lock_guard<std::mutex> lock(g_err_mutex);
+  if (!g_err_host) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    memset(p, 0, 64);
+    g_err_host = (unsigned int*)p;
+  }
+  return g_err_host;        // unified addressing: the host pointer is valid on the device
+}
+
+static unsigned long long timeout_ns() {
+  static unsigned long long v = 0;
+  if (!v) {
+    const char* e = getenv("DDPB_SYNC_TIMEOUT_S");
+    double s = e ? atof(e) : 120.0;
+    if (!(s > 0.0)) s = 120.0;
+    v = (unsigned long long)(s * 1e9);
+  }
+  return v;
+}
+
+static int fill_common(P2PArgs& a, void* const* flags, float* mom, void* epochs, int rank, int world, int slot,
+                       long long off, long long n, float lr, float momentum, float wd, const long long* shard,
+                       int n_shard) {
+  DDPB_REQUIRE(off % 8 == 0 && n % 8 == 0, "p2p: range must be a multiple of 8 elements (off=%lld n=%lld)", off, n);
+  DDPB_REQUIRE(slot >= 0 && slot < DDPB_P2P_MAX_SLOTS, "p2p: slot %d out of range", slot);
+  DDPB_REQUIRE(n_shard >= 0 && n_shard <= P2P_MAX_SHARD && (n_shard == 0 || shard), "p2p: at most %d sharded ranges",
+               P2P_MAX_SHARD);
+  for (int r = 0; r < world; ++r) a.flags[r] = flags ? (uint32_t*)flags[r] : nullptr;
+  a.mom = mom; a.epochs = (uint32_t*)epochs;
+  a.rank = rank; a.world = world; a.slot = slot; a.off = off; a.n = n;
+  a.lr = lr; a.momentum = momentum; a.wd = wd;
+  a.timeout_ns = timeout_ns();
+  a.err = err_record();
+  a.n_shard = 0;
+  for (int k = 0; k < n_shard; ++k) {
+    const long long lo = shard[2 * k], hi = shard[2 * k + 1];
+    DDPB_REQUIRE(lo % 8 == 0 && hi % 8 == 0 && lo <= hi, "p2p: sharded range [%lld, %lld) must be 8-element aligned", lo, hi);
+    if (hi <= off || lo >= off + n) continue;       // does not touch this launch
+    a.shard[2 * a.n_shard] = lo; a.shard[2 * a.n_shard + 1] = hi;
+    ++a.n_shard;
+  }
+  return DDPB_OK;
 }
 
 }  // namespace ddpb
@@ -275,30 +409,28 @@ using namespace ddpb;
 // One fused synchronisation step over the element range [off, off+n) of the symmetric arenas.
 // Pointer tables have `world` entries (index = rank); flags == null disables the cross-rank
 // barriers (single-GPU emulation in the unit tests).  See include/ddp_b200.h for the modes.
-extern "C" int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, void* const* shadow,
-                             void* const* flags, float* mom, void* epochs, int rank, int world, int slot,
-                             long long off, long long n, float lr, float momentum, float wd, int blocks,
-                             cudaStream_t stream) {
+// shard / n_shard: [lo, hi) element ranges whose fp32 master the owner keeps to itself (two-shot and
+// root modes, only when a bf16 copy exists); n_shard = 0 publishes everything.
+extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* master, void* const* shadow,
+                                     void* const* flags, float* mom, void* epochs, int rank, int world, int slot,
+                                     long long off, long long n, float lr, float momentum, float wd, int blocks,
+                                     const long long* shard, int n_shard, cudaStream_t stream) {
   DDPB_REQUIRE(world >= 1 && world <= P2P_MAX_RANKS && rank >= 0 && rank < world, "p2p: bad rank/world %d/%d",
                rank, world);
-  DDPB_REQUIRE(off % 4 == 0 && n % 4 == 0, "p2p: range must be float4-aligned (off=%lld n=%lld)", off, n);
-  DDPB_REQUIRE(slot >= 0 && slot < DDPB_P2P_MAX_SLOTS, "p2p: slot %d out of range", slot);
+  P2PArgs a;
+  memset(&a, 0, sizeof(a));
+  int rc = fill_common(a, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
+  if (rc) return rc;
   if (blocks <= 0) {
-    long long want = (n / 4 + 512 * 8 - 1) / (512 * 8);
+    long long want = (n / 8 + 512 * 4 - 1) / (512 * 4);
     blocks = (int)(want < 1 ? 1 : (want > 32 ? 32 : want));
   }
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "p2p: at most %d blocks", P2P_MAX_BLOCKS);
-  P2PArgs a;
-  memset(&a, 0, sizeof(a));
   for (int r = 0; r < world; ++r) {
     a.grad[r] = (float*)grad[r];
     a.master[r] = master ? (float*)master[r] : nullptr;
     a.shadow[r] = shadow ? (bf16*)shadow[r] : nullptr;
-    a.flags[r] = flags ? (uint32_t*)flags[r] : nullptr;
   }
-  a.mom = mom; a.epochs = (uint32_t*)epochs;
-  a.rank = rank; a.world = world; a.slot = slot; a.off = off; a.n = n;
-  a.lr = lr; a.momentum = momentum; a.wd = wd;
   a.skip_exit_barrier = (mode & DDPB_P2P_NO_EXIT_BARRIER) ? 1 : 0;
   mode &= ~DDPB_P2P_NO_EXIT_BARRIER;
   switch (mode) {
@@ -313,43 +445,77 @@ extern "C" int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, v
   return DDPB_OK;
 }
 
-// NVLS variant of the two-shot fused reduce+SGD (see p2p_nvls_kernel).  mc_* point into the multicast
-// mapping of the symmetric arena at the same offsets as grad / master / shadow; master_local and mom
-// are this rank's own buffers; `flags` is the usual per-rank table of signal pads.
-extern "C" int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shadow, float* master_local,
-                                  void* const* flags, float* mom, void* epochs, int rank, int world, int slot,
-                                  long long off, long long n, float lr, float momentum, float wd, int blocks,
-                                  int skip_exit_barrier, cudaStream_t stream) {
+extern "C" int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, void* const* shadow,
+                             void* const* flags, float* mom, void* epochs, int rank, int world, int slot,
+                             long long off, long long n, float lr, float momentum, float wd, int blocks,
+                             cudaStream_t stream) {
+  return ddpb_p2p_sync_sharded(mode, grad, master, shadow, flags, mom, epochs, rank, world, slot, off, n, lr, momentum,
+                               wd, blocks, nullptr, 0, stream);
+}
+
+// NVLS variant of the fused reduce+SGD (see p2p_nvls_kernel).  mc_* point into the multicast
+// mapping of the symmetric arena at the same offsets as grad / master / shadow; master_local, shadow_local
+// (nullable) and mom are this rank's own buffers; `flags` is the usual per-rank table of signal pads.
+// mode: DDPB_P2P_TWOSHOT (owner of a slice reduces, updates, multicasts) or DDPB_P2P_ONESHOT (every rank
+// pulls the switch-reduced sum of the whole range and updates its own replica: small ranges, no stores
+// over NVLink at all).  blocks = 0 picks a grid meant to run NEXT TO the backward kernels; a caller that
+// owns the GPU (the bandwidth sweep) passes the grid it wants (up to DDPB_P2P_MAX_BLOCKS).
+extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_master, void* mc_shadow,
+                                          float* master_local, void* shadow_local, void* const* flags, float* mom,
+                                          void* epochs, int rank, int world, int slot, long long off, long long n,
+                                          float lr, float momentum, float wd, int blocks, int skip_exit_barrier,
+                                          const long long* shard, int n_shard, cudaStream_t stream) {
   DDPB_REQUIRE(world >= 2 && world <= P2P_MAX_RANKS && rank >= 0 && rank < world, "nvls: bad rank/world %d/%d", rank,
                world);
-  DDPB_REQUIRE(off % 4 == 0 && n % 4 == 0, "nvls: range must be float4-aligned");
-  DDPB_REQUIRE(slot >= 0 && slot < DDPB_P2P_MAX_SLOTS, "nvls: slot %d out of range", slot);
+  DDPB_REQUIRE(mode == DDPB_P2P_TWOSHOT || mode == DDPB_P2P_ONESHOT, "nvls: mode must be two-shot or one-shot");
   DDPB_REQUIRE(mc_grad && mc_master && master_local && mom && flags, "nvls: null pointer");
-  // CTA shape of the NVLS kernel (it runs next to the backward kernels; DDPB_NVLS_THREADS / DDPB_NVLS_MAX_BLOCKS)
+  NvlsArgs a;
+  memset(&a, 0, sizeof(a));
+  int rc = fill_common(a.base, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
+  if (rc) return rc;
+  // CTA shape of the NVLS kernel when it runs next to the backward kernels (DDPB_NVLS_THREADS / DDPB_NVLS_MAX_BLOCKS)
   static int threads = 0, cap = 0;
   if (!threads) {
     const char* t = getenv("DDPB_NVLS_THREADS");
-    threads = t ? atoi(t) : 256;        // measured at 2 GPUs: 256 x 32 CTAs 0.575 ms, 512 x 32 0.589, 512 x 64 0.631, 256 x 16 0.624
+    threads = t ? atoi(t) : 256;
     if (threads != 128 && threads != 256 && threads != 512) threads = 256;
     const char* c = getenv("DDPB_NVLS_MAX_BLOCKS");
     cap = c ? atoi(c) : 32;
     if (cap < 1 || cap > P2P_MAX_BLOCKS) cap = 32;
   }
+  const long long units = n / 8 / (mode == DDPB_P2P_ONESHOT ? 1 : world);
   if (blocks <= 0) {
-    long long want = (n / 4 / world + threads * 4 - 1) / (threads * 4);
+    long long want = (units + threads * 4 - 1) / (threads * 4);
     blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
   }
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "nvls: at most %d blocks", P2P_MAX_BLOCKS);
-  NvlsArgs a;
-  memset(&a, 0, sizeof(a));
-  for (int r = 0; r < world; ++r) a.base.flags[r] = (uint32_t*)flags[r];
   a.base.master[rank] = master_local;
-  a.base.mom = mom; a.base.epochs = (uint32_t*)epochs;
-  a.base.rank = rank; a.base.world = world; a.base.slot = slot; a.base.off = off; a.base.n = n;
-  a.base.lr = lr; a.base.momentum = momentum; a.base.wd = wd;
+  a.base.shadow[rank] = (bf16*)shadow_local;
   a.base.skip_exit_barrier = skip_exit_barrier;
   a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
-  p2p_nvls_kernel<<<blocks, threads, 0, stream>>>(a);
+  a.one_shot = mode == DDPB_P2P_ONESHOT ? 1 : 0;
+  // loads in flight per thread: 2U x 16 bytes; small ranges take the low-register variant
+  if (units >= (long long)blocks * threads * 4) p2p_nvls_kernel<4><<<blocks, threads, 0, stream>>>(a);
+  else p2p_nvls_kernel<1><<<blocks, threads, 0, stream>>>(a);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
+}
+
+extern "C" int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shadow, float* master_local,
+                                  void* const* flags, float* mom, void* epochs, int rank, int world, int slot,
+                                  long long off, long long n, float lr, float momentum, float wd, int blocks,
+                                  int skip_exit_barrier, cudaStream_t stream) {
+  return ddpb_p2p_sync_nvls_sharded(DDPB_P2P_TWOSHOT, mc_grad, mc_master, mc_shadow, master_local, nullptr, flags, mom,
+                                    epochs, rank, world, slot, off, n, lr, momentum, wd, blocks, skip_exit_barrier,
+                                    nullptr, 0, stream);
+}
+
+// The record a timed-out cross-rank wait leaves behind (rec[0] = 1 when present, then rank, peer, slot,
+// phase, block, epoch): lets the caller turn the generic "unspecified launch failure" that follows the
+// trap into a specific error.  Returns 1 when a record is present.
+extern "C" int ddpb_p2p_last_timeout(unsigned int* rec8) {
+  std::lock_guard<std::mutex> lock(g_err_mutex);
+  if (!g_err_host || !g_err_host[0]) return 0;
+  if (rec8) memcpy(rec8, g_err_host, 8 * sizeof(unsigned int));
+  return 1;
 }

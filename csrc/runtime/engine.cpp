@@ -50,7 +50,8 @@ struct Block {
 
 struct Bucket { long long off, numel; int last_block; int mode; };   // last_block: -1 = classifier
 
-struct Graph { cudaGraphExec_t exec = nullptr; long long launches = 0; };
+typedef std::map<std::string, long long> NameCounts;
+struct Graph { cudaGraphExec_t exec = nullptr; long long launches = 0; NameCounts by_name; };
 
 struct Engine {
   ddpb_engine_config cfg;
@@ -78,12 +79,15 @@ struct Engine {
   bool fuse_bn_reduce = true;                 // DDPB_FUSE_BN_REDUCE=0: keep the separate reduction kernel
   void *x0cols = nullptr, *w0pad = nullptr;   // first layer as a GEMM: patch matrix [B*1024][64], weights [64][64]
   std::vector<Bucket> buckets;
+  std::vector<long long> shard;          // [lo, hi) arena ranges of the conv weights: fp32 master stays with its owner
+  bool shard_master = true;              // DDPB_SHARD_MASTER=0: publish the fp32 master of every element
   cudaStream_t comm = nullptr, comm2 = nullptr, wg = nullptr;
   bool two_comm = true, comm2_used = false;   // multi-GPU: buckets alternate between two streams (DDPB_TWO_COMM=0: one)
   std::vector<cudaEvent_t> bucket_ev, ev_dy, ev_dg, ev_wg;
   cudaEvent_t join_ev = nullptr, fork_ev = nullptr, zero_ev = nullptr, start_ev = nullptr;
   std::map<long long, Graph> graphs;     // key = kind * 1e6 + batch
   long long launches = 0, counting = 0;
+  NameCounts launches_by_name, counting_by_name;    // per entry point: what the step really launched
   bool count_only = false;
   // step-timeline profiling (ddpb_engine_profile_step): timing events, only recorded when prof_on
   bool prof_on = false;
@@ -99,6 +103,17 @@ struct Engine {
   cudaEvent_t trace_start = nullptr;
   cudaStream_t trace_main = nullptr;
 };
+
+static void count_name(Engine* e, const char* call_text) {
+  const char* p = call_text;
+  if (!strncmp(p, "ddpb_", 5)) p += 5;
+  size_t n = 0;
+  while (p[n] && p[n] != '(') ++n;
+  e->counting_by_name[std::string(p, n)] += 1;
+}
+static void add_counts(NameCounts& into, const NameCounts& from, long long times = 1) {
+  for (const auto& kv : from) into[kv.first] += kv.second * times;
+}
 
 static int trace_mark(Engine* e, cudaStream_t stream, const char* call_text) {
   if (e->trace_n == e->trace.size()) {
@@ -207,6 +222,16 @@ static void plan_buckets(Engine* e) {
   }
   for (auto& b : e->buckets)
     b.mode = (c.world > 1 && b.numel * 4 >= 256 * 1024) ? DDPB_P2P_TWOSHOT : DDPB_P2P_ONESHOT;
+  // conv weights are read in bf16 only (tensor-core path): their fp32 master is sharded like the momentum
+  e->shard.clear();
+  if (c.world > 1 && c.dtype == DDPB_BF16 && e->shard_master)
+    for (int i = 0; i < c.num_blocks; ++i) {
+      const Block& b = e->blocks[i];
+      if (b.cin % 64 == 0 && b.cout % 64 == 0 && (int)e->shard.size() < 2 * DDPB_P2P_MAX_SHARD_RANGES) {
+        e->shard.push_back(b.conv_w.off);
+        e->shard.push_back(round_up(b.conv_w.off + b.conv_w.numel, 8));
+      }
+    }
 }
 
 // Offsets of the sub-buffers inside the symmetric arena (same on every rank).
@@ -342,6 +367,7 @@ static bool use_tc_first(const Engine* e, const Block& b) {
   do {                                                            \
     ECHECK(call);                                                 \
     (e)->counting += 1;                                           \
+    count_name((e), #call);                                       \
     if ((e)->trace_on) ECHECK(trace_mark((e), (stream), #call));  \
   } while (0)
 
@@ -425,18 +451,22 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   const int mode = b.mode | (last ? 0 : DDPB_P2P_NO_EXIT_BARRIER);
   // enough CTAs to keep ~16 B x 8 loads per thread in flight on big buckets, few on small ones
   long long want = (b.numel / 4 + 512 * 4 - 1) / (512 * 4);
-  const int blocks = (int)(want < 1 ? 1 : (want > DDPB_P2P_MAX_BLOCKS ? DDPB_P2P_MAX_BLOCKS : want));
-  if (e->mc_arena && b.mode == DDPB_P2P_TWOSHOT) {
-    // NVLS: the switch reduces, one multicast store publishes (sync_p2p.cu, p2p_nvls_kernel)
+  const int blocks = (int)(want < 1 ? 1 : (want > 64 ? 64 : want));     // it runs next to the backward kernels
+  const long long* sh_tab = e->shard.empty() ? nullptr : e->shard.data();
+  const int n_sh = (int)e->shard.size() / 2;
+  if (e->mc_arena) {
+    // NVLS: the switch reduces; big buckets: the owner of a slice updates it and one multicast store
+    // publishes the result; small buckets: every rank pulls the reduced sum and updates its own replica
     char* mc = (char*)e->mc_arena;
-    LAUNCH(e, s, ddpb_p2p_sync_nvls(mc + e->off_grad, mc + e->off_master,
-                                 c.dtype == DDPB_BF16 ? (void*)(mc + e->off_shadow) : nullptr, e->master, f, e->mom,
-                                 e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr, c.momentum, c.wd, 0,
-                                 last ? 0 : 1, s));
+    LAUNCH(e, s, ddpb_p2p_sync_nvls_sharded(b.mode, mc + e->off_grad, mc + e->off_master,
+                                            c.dtype == DDPB_BF16 ? (void*)(mc + e->off_shadow) : nullptr, e->master,
+                                            c.dtype == DDPB_BF16 ? (void*)e->shadow : nullptr, f, e->mom, e->epochs,
+                                            c.rank, c.world, bi, b.off, b.numel, c.lr, c.momentum, c.wd, 0,
+                                            last ? 0 : 1, sh_tab, n_sh, s));
     return DDPB_OK;
   }
-  LAUNCH(e, s, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
-                          c.momentum, c.wd, blocks, s));
+  LAUNCH(e, s, ddpb_p2p_sync_sharded(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, bi, b.off, b.numel, c.lr,
+                                     c.momentum, c.wd, blocks, sh_tab, n_sh, s));
   return DDPB_OK;
 }
 
@@ -566,8 +596,9 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
       peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
       peer_table(e, e->off_shadow, sh); peer_table(e, e->off_flags, f);
       int mode = c.strategy == 1 ? DDPB_P2P_ROOT : DDPB_P2P_TWOSHOT;
-      LAUNCH(e, s, ddpb_p2p_sync(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1, 0,
-                              e->arena_elems, c.lr, c.momentum, c.wd, 0, s));
+      LAUNCH(e, s, ddpb_p2p_sync_sharded(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1,
+                                         0, e->arena_elems, c.lr, c.momentum, c.wd, 0,
+                                         e->shard.empty() ? nullptr : e->shard.data(), (int)e->shard.size() / 2, s));
     } else {
       LAUNCH(e, s, ddpb_sgd_step(e->master, e->mom, e->grad, dt == DDPB_BF16 ? (void*)e->shadow : nullptr,
                               e->arena_elems, c.lr, c.momentum, c.wd, 1.f, s));
@@ -607,18 +638,18 @@ static int run_kind(Engine* e, int kind, int B, cudaStream_t s) {
 
 static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
   if (!e->cfg.use_graph) {
-    e->counting = 0;
+    e->counting = 0; e->counting_by_name.clear();
     ECHECK(run_kind(e, kind, B, s));
-    e->launches += e->counting;
+    e->launches += e->counting; add_counts(e->launches_by_name, e->counting_by_name);
     return DDPB_OK;
   }
   long long key = (long long)kind * 1000000 + B;
   auto it = e->graphs.find(key);
   if (it == e->graphs.end()) {
     // one eager run first: it performs the one-time cudaFuncSetAttribute calls (not capturable)
-    e->counting = 0;
+    e->counting = 0; e->counting_by_name.clear();
     ECHECK(run_kind(e, kind, B, s));
-    e->launches += e->counting;
+    e->launches += e->counting; add_counts(e->launches_by_name, e->counting_by_name);
     DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
     DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm));
     DDPB_CUDA_CHECK(cudaStreamSynchronize(e->wg));
@@ -626,7 +657,7 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
     // launch the graph from the NEXT call on.
     Graph g;
     cudaGraph_t graph = nullptr;
-    e->counting = 0;
+    e->counting = 0; e->counting_by_name.clear();
     cudaError_t ce = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
     if (ce != cudaSuccess) {
       // e.g. the legacy default stream cannot be captured: keep running eagerly, remember why
@@ -645,7 +676,7 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
       set_last_error("CUDA graph capture failed (%s); running eagerly", cudaGetErrorString(ce));
       return DDPB_OK;
     }
-    g.launches = e->counting;
+    g.launches = e->counting; g.by_name = e->counting_by_name;
     ce = cudaGraphInstantiate(&g.exec, graph, 0);
     cudaGraphDestroy(graph);
     if (ce != cudaSuccess) {
@@ -661,7 +692,7 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
     NvtxRange r("ddpb.graph_launch");
     DDPB_CUDA_CHECK(cudaGraphLaunch(it->second.exec, s));
   }
-  e->launches += it->second.launches;
+  e->launches += it->second.launches; add_counts(e->launches_by_name, it->second.by_name);
   return DDPB_OK;
 }
 
@@ -691,6 +722,7 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   if (const char* fb = getenv("DDPB_FUSE_BN_REDUCE")) e->fuse_bn_reduce = fb[0] != '0';
   if (const char* tc = getenv("DDPB_TWO_COMM")) e->two_comm = tc[0] != '0';
   if (const char* ff = getenv("DDPB_FUSE_BN_FWD")) e->fuse_bn_fwd = ff[0] != '0';
+  if (const char* sm = getenv("DDPB_SHARD_MASTER")) e->shard_master = sm[0] != '0';
   int rc = plan_layout(e);
   if (!rc) { plan_buckets(e); rc = alloc_all(e); }
   if (rc) { delete e; return rc; }
@@ -753,6 +785,25 @@ extern "C" int ddpb_engine_info(void* handle, ddpb_engine_info_t* out) {
   out->launches = e->launches;
   out->graph_active = e->cfg.use_graph && !e->graphs.empty();
   return DDPB_OK;
+}
+
+// "name=count;name=count;..." of every entry point launched since the engine was created (graph replays
+// included): the driver-visible proof of which sync kernels a multi-GPU run really used.  Returns the
+// length needed (including the terminating NUL); writes at most cap bytes.
+extern "C" int ddpb_engine_launch_counts(void* handle, char* buf, int cap) {
+  Engine* e = (Engine*)handle;
+  if (!e) return 0;
+  std::string out;
+  for (const auto& kv : e->launches_by_name) {
+    if (!out.empty()) out += ';';
+    out += kv.first + "=" + std::to_string(kv.second);
+  }
+  if (buf && cap > 0) {
+    const size_t n = out.size() < (size_t)cap - 1 ? out.size() : (size_t)cap - 1;
+    memcpy(buf, out.data(), n);
+    buf[n] = 0;
+  }
+  return (int)out.size() + 1;
 }
 
 // peer_arena[r] = this rank's mapping of rank r's arena (ddpb_symm_open), entry `rank` ignored.
@@ -830,7 +881,7 @@ extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s,
     }
   }
   e->prof_on = true;
-  e->counting = 0;
+  e->counting = 0; e->counting_by_name.clear();
   int rc = DDPB_OK;
   cudaEventRecord(e->prof_start, s);
   rc = forward(e, batch, 1, s, true);
@@ -839,7 +890,7 @@ extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s,
   if (!rc) rc = backward(e, batch, s, true);
   cudaEventRecord(e->prof_end, s);
   e->prof_on = false;
-  e->launches += e->counting;
+  e->launches += e->counting; add_counts(e->launches_by_name, e->counting_by_name);
   if (rc) return rc;
   DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
   DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm));
@@ -881,7 +932,7 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
     DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
     DDPB_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
   }
-  e->trace_on = true; e->trace_external = graphed != 0; e->trace_n = 0; e->trace_main = s; e->counting = 0;
+  e->trace_on = true; e->trace_external = graphed != 0; e->trace_n = 0; e->trace_main = s; e->counting = 0; e->counting_by_name.clear();
   if (graphed) cudaEventRecordWithFlags(e->trace_start, s, cudaEventRecordExternal);
   else cudaEventRecord(e->trace_start, s);
   int rc = forward(e, batch, 1, s, true);
@@ -900,9 +951,9 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
     cudaGraphDestroy(graph);
     DDPB_REQUIRE(ce == cudaSuccess, "engine_trace_step: cudaGraphInstantiate failed (%s)", cudaGetErrorString(ce));
     for (int rep = 0; rep < 3; ++rep) DDPB_CUDA_CHECK(cudaGraphLaunch(exec, s));     // three real steps; the last one is read
-    e->launches += 3 * e->counting;
+    e->launches += 3 * e->counting; add_counts(e->launches_by_name, e->counting_by_name, 3);
   } else {
-    e->launches += e->counting;
+    e->launches += e->counting; add_counts(e->launches_by_name, e->counting_by_name);
     if (rc) return rc;
   }
   DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
@@ -927,10 +978,10 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
 extern "C" int ddpb_engine_eval_step(void* handle, int batch, cudaStream_t s) {
   Engine* e = (Engine*)handle;
   DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_eval_step: batch %d out of range", batch);
-  e->counting = 0;
+  e->counting = 0; e->counting_by_name.clear();
   ECHECK(forward(e, batch, 0, s));
   ECHECK(loss_fwd(e, batch, 0, s));
-  e->launches += e->counting;
+  e->launches += e->counting; add_counts(e->launches_by_name, e->counting_by_name);
   return DDPB_OK;
 }
 
@@ -942,7 +993,8 @@ extern "C" int ddpb_engine_eval_reset(void* handle, cudaStream_t s) {
 
 // Collective over the symmetric arena outside the training step: what = 0 broadcast master weights,
 // 1 broadcast BN running statistics (rank 0 -> all; DDP's init / buffer sync), 2 all-gather the
-// momentum shards of the two-shot buckets (before a checkpoint).
+// momentum shards of the two-shot buckets, 3 the same for the sharded fp32 master weights (before a
+// checkpoint / state_dict).
 extern "C" int ddpb_engine_collective(void* handle, int what, cudaStream_t s) {
   Engine* e = (Engine*)handle;
   const auto& c = e->cfg;
@@ -974,6 +1026,26 @@ extern "C" int ddpb_engine_collective(void* handle, int what, cudaStream_t s) {
       return ddpb_p2p_sync(DDPB_P2P_ALLGATHER, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot,
                            0, e->arena_elems, 0, 0, 0, 0, s);
     if (c.strategy == 1)   // root owns all momentum: broadcast it
+      return ddpb_p2p_sync(DDPB_P2P_BCAST, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot, 0,
+                           e->arena_elems, 0, 0, 0, 0, s);
+    return DDPB_OK;
+  }
+  if (what == 3) {
+    // fp32 master weights of the sharded ranges (conv weights): every rank holds current values only for
+    // the slices it owns; same ownership rule as the momentum above
+    if (e->shard.empty()) return DDPB_OK;
+    peer_table(e, e->off_master, buf);
+    if (c.strategy == 3) {
+      for (size_t i = 0; i < e->buckets.size(); ++i)
+        if (e->buckets[i].mode == DDPB_P2P_TWOSHOT)
+          ECHECK(ddpb_p2p_sync(DDPB_P2P_ALLGATHER, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world,
+                               slot, e->buckets[i].off, e->buckets[i].numel, 0, 0, 0, 0, s));
+      return DDPB_OK;
+    }
+    if (c.strategy == 2)
+      return ddpb_p2p_sync(DDPB_P2P_ALLGATHER, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot,
+                           0, e->arena_elems, 0, 0, 0, 0, s);
+    if (c.strategy == 1)
       return ddpb_p2p_sync(DDPB_P2P_BCAST, buf, nullptr, nullptr, f, nullptr, e->epochs, c.rank, c.world, slot, 0,
                            e->arena_elems, 0, 0, 0, 0, s);
     return DDPB_OK;

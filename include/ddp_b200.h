@@ -22,7 +22,8 @@ extern "C" {
 #define DDPB_BF16 1
 
 #define DDPB_MAX_RANKS 8
-#define DDPB_P2P_MAX_BLOCKS 64
+#define DDPB_P2P_MAX_BLOCKS 160
+#define DDPB_P2P_MAX_SHARD_RANGES 24
 #define DDPB_P2P_MAX_SLOTS 64
 
 #define DDPB_P2P_ONESHOT 0
@@ -206,12 +207,33 @@ int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, void* const*
                   float* mom, void* epochs, int rank, int world, int slot, long long off, long long n, float lr,
                   float momentum, float wd, int blocks, cudaStream_t stream);
 
+/* The same with "sharded" element ranges [lo, hi) (shard[2k], shard[2k+1]; 8-element aligned): ranges whose
+ * fp32 master weights the owning rank keeps to itself, like the momentum, publishing only the bf16 copy
+ * (the conv weights: nothing but the optimizer reads their fp32 form).  Two-shot / root modes with a bf16
+ * copy only; n_shard = 0 is ddpb_p2p_sync.  Bring stale slices up to date with DDPB_P2P_ALLGATHER (two-shot)
+ * or DDPB_P2P_BCAST (root) over the master buffers before a full state_dict is read. */
+int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* master, void* const* shadow, void* const* flags,
+                          float* mom, void* epochs, int rank, int world, int slot, long long off, long long n,
+                          float lr, float momentum, float wd, int blocks, const long long* shard, int n_shard,
+                          cudaStream_t stream);
+
 /* NVLS variant of the two-shot mode: mc_* are multicast mappings (runtime/vmm_arena.cpp); the switch
  * performs the reduction (multimem.ld_reduce) and the broadcast (multimem.st).  Replaces the same
  * reference calls as ddpb_p2p_sync. */
 int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shadow, float* master_local, void* const* flags,
                        float* mom, void* epochs, int rank, int world, int slot, long long off, long long n,
                        float lr, float momentum, float wd, int blocks, int skip_exit_barrier, cudaStream_t stream);
+/* NVLS with sharded ranges (see ddpb_p2p_sync_sharded) and a choice of mode: DDPB_P2P_TWOSHOT as above, or
+ * DDPB_P2P_ONESHOT where every rank pulls the switch-reduced sum of the whole range and updates its own
+ * replica (master_local / shadow_local) without any store over NVLink - the small buckets. */
+int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_master, void* mc_shadow, float* master_local,
+                               void* shadow_local, void* const* flags, float* mom, void* epochs, int rank, int world,
+                               int slot, long long off, long long n, float lr, float momentum, float wd, int blocks,
+                               int skip_exit_barrier, const long long* shard, int n_shard, cudaStream_t stream);
+/* A cross-rank wait that times out (DDPB_SYNC_TIMEOUT_S, default 120) records rec8 = {1, rank, peer, slot,
+ * phase, block, epoch, 0} in host memory before it traps the kernel; returns 1 when such a record exists.
+ * No reference counterpart (the reference blocks forever inside gloo when a rank dies). */
+int ddpb_p2p_last_timeout(unsigned int* rec8);
 
 /* Virtual-memory-management arena with an NVSwitch multicast mapping (csrc/runtime/vmm_arena.cpp).
  * ddpb_vmm_alloc ALLOCATES (cuMemCreate); fds are POSIX file descriptors to pass between processes. */
@@ -306,6 +328,10 @@ int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t stream, float
  * The reference has only three host timers per iteration (ref Part 1/main.py:33-43). */
 int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t stream, int graphed, char* names, int* block,
                            int* stream_id, float* end_ms, int max_rows, int* n_rows);
+/* "entry_point=count;..." of everything launched since the engine was created, graph replays included
+ * (no reference counterpart; the reference's sync calls are visible in its Python source instead).
+ * Returns the buffer length needed. */
+int ddpb_engine_launch_counts(void* handle, char* buf, int cap);
 /* ref Part 1/main.py:61-76: eval-mode forward; accumulates info.eval_loss / info.correct. */
 int ddpb_engine_eval_step(void* handle, int batch, cudaStream_t stream);
 int ddpb_engine_eval_reset(void* handle, cudaStream_t stream);

@@ -336,3 +336,45 @@ def test_p2p_reduce_sgd_single_gpu_emulation(F, mode_name, world):
     # every replica must hold bit-identical weights
     for r in range(1, world):
         assert torch.equal(masters[0], masters[r])
+
+
+@pytest.mark.parametrize("mode_name", ["twoshot", "root"])
+@pytest.mark.parametrize("world", [2, 4])
+def test_p2p_sharded_master_single_gpu_emulation(F, mode_name, world):
+    """Ranges marked as sharded (the conv weights) publish only their bf16 copy; the fp32 master stays with
+    the owner of the slice until an all-gather (two-shot) / broadcast (root) brings it everywhere."""
+    from cs744_ddp_b200.ops import native as nv
+    mode = {"twoshot": nv.P2P_TWOSHOT, "root": nv.P2P_ROOT}[mode_name]
+    torch.manual_seed(8)
+    n, off = 8 * 600, 64
+    total = off + n + 64
+    shard = [off + 8 * 100, off + 8 * 500]                 # the middle of the range
+    grads = [torch.randn(total, device=DEV) for _ in range(world)]
+    p0 = torch.randn(total, device=DEV)
+    masters = [p0.clone() for _ in range(world)]
+    shadows = [torch.zeros(total, device=DEV, dtype=torch.bfloat16) for _ in range(world)]
+    moms = [torch.zeros(total, device=DEV) for _ in range(world)]
+    tabs = lambda ts: [t.data_ptr() for t in ts]
+    for r in range(world):
+        F.p2p_sync(mode, tabs(grads), tabs(masters), tabs(shadows), None, moms[r], None, r, world, 0, off, n, 0.1, 0.9,
+                   1e-4, shard=shard)
+    torch.cuda.synchronize()
+    ref = p0 - 0.1 * (torch.stack(grads).mean(0) + 1e-4 * p0)
+    lo, hi = shard
+    for r in range(world):
+        # the bf16 copy is complete everywhere, and so is the fp32 master outside the sharded range
+        assert torch.equal(shadows[r][off:off + n], ref[off:off + n].to(torch.bfloat16)) or \
+            torch.allclose(shadows[r][off:off + n].float(), ref[off:off + n], rtol=1e-2, atol=1e-2)
+        assert torch.allclose(masters[r][off:lo], ref[off:lo], rtol=1e-5, atol=1e-6)
+        assert torch.allclose(masters[r][hi:off + n], ref[hi:off + n], rtol=1e-5, atol=1e-6)
+    # inside it, non-owners still hold the old values somewhere
+    stale = [int((masters[r][lo:hi] == p0[lo:hi]).sum()) for r in range(world)]
+    assert any(s > 0 for s in stale), stale
+    # bring the shards together the way the engine does before a state_dict is read
+    for r in range(world):
+        F.p2p_sync(nv.P2P_ALLGATHER if mode_name == "twoshot" else nv.P2P_BCAST, tabs(masters), None, None, None, None,
+                   None, r, world, 0, off, n)
+    torch.cuda.synchronize()
+    for r in range(world):
+        assert torch.allclose(masters[r][off:off + n], ref[off:off + n], rtol=1e-5, atol=1e-6), (mode_name, r)
+        assert torch.equal(masters[r], masters[0])

@@ -8,9 +8,16 @@ import torch
 
 pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 
-WORLD = 2
 STEPS = 3
 B = 16
+
+
+def _need(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs, this box has {torch.cuda.device_count()}")
+
+
+WORLDS = [2, 4, 8]
 
 
 def _free_port():
@@ -28,7 +35,7 @@ class _T:
         pass
 
 
-def _worker(rank, port, sync, comm, dtype, outdir, plan):
+def _worker(rank, world, port, sync, comm, dtype, outdir, plan, b):
     import torch.distributed as dist
     from cs744_ddp_b200.config import TrainConfig
     from cs744_ddp_b200.data import synthetic_cifar10
@@ -37,15 +44,15 @@ def _worker(rank, port, sync, comm, dtype, outdir, plan):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", rank=rank, world_size=WORLD, device_id=torch.device("cuda", rank))
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     torch.manual_seed(0)
-    cfg = TrainConfig(num_nodes=WORLD, rank=rank, sync=sync, comm=comm, dtype=dtype, device="cuda",
-                      backend="native", global_batch=B * WORLD, synthetic=True, bucket_plan=plan, lr=0.01)
+    cfg = TrainConfig(num_nodes=world, rank=rank, sync=sync, comm=comm, dtype=dtype, device="cuda",
+                      backend="native", global_batch=b * world, synthetic=True, bucket_plan=plan, lr=0.01)
     be = NativeBackend(cfg, torch.device("cuda", rank))
-    split = synthetic_cifar10(STEPS * B, seed=10 + rank)
+    split = synthetic_cifar10(STEPS * b, seed=10 + rank)
     losses = []
     for s in range(STEPS):
-        raw = RawBatch(split.images[s * B:(s + 1) * B], split.labels[s * B:(s + 1) * B], None, None)
+        raw = RawBatch(split.images[s * b:(s + 1) * b], split.labels[s * b:(s + 1) * b], None, None)
         losses.append(float(be.train_step(*be.prepare(raw), _T())))
     torch.cuda.synchronize()
     sd = {k: v.cpu() for k, v in be.state_dict().items()}
@@ -56,63 +63,148 @@ def _worker(rank, port, sync, comm, dtype, outdir, plan):
     dist.destroy_process_group()
 
 
-def _run(sync, comm, dtype="fp32", plan="per_layer"):
+def _run(sync, comm, dtype="fp32", plan="per_layer", world=2, b=B):
     import torch.multiprocessing as mp
     with tempfile.TemporaryDirectory() as d:
-        mp.spawn(_worker, args=(_free_port(), sync, comm, dtype, d, plan), nprocs=WORLD, join=True)
-        return [torch.load(os.path.join(d, f"{sync}_{comm}_{r}.pt"), weights_only=False) for r in range(WORLD)]
+        mp.spawn(_worker, args=(world, _free_port(), sync, comm, dtype, d, plan, b), nprocs=world, join=True)
+        return [torch.load(os.path.join(d, f"{sync}_{comm}_{r}.pt"), weights_only=False) for r in range(world)]
 
 
 def _rel(a, b):
     return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))
 
 
+def _torch_oracle(world, b, steps=STEPS):
+    """What the reference computes, in ONE process on cuda:0 in plain fp32 torch: `world` replicas with
+    identical weights each run forward / backward on their own batch (own BatchNorm statistics - the
+    reference uses plain BatchNorm2d, not SyncBatchNorm), the gradients are averaged over the replicas
+    (ref Part 2a/main.py:117-127, Part 2b/main.py:116-119) and every replica takes the same SGD step.
+    Returns (parameters after `steps` steps, per-rank losses)."""
+    from cs744_ddp_b200.config import TrainConfig
+    from cs744_ddp_b200.data import synthetic_cifar10
+    from cs744_ddp_b200.data.pipeline import RawBatch, transform_batch
+    from cs744_ddp_b200.models.vgg import build_model
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        dev = torch.device("cuda", 0)
+        torch.manual_seed(0)
+        model = build_model("VGG11").to(dev)
+        opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+        crit = torch.nn.CrossEntropyLoss()
+        splits = [synthetic_cifar10(steps * b, seed=10 + r) for r in range(world)]
+        losses = [[] for _ in range(world)]
+        model.train()
+        for s in range(steps):
+            acc = None
+            for r in range(world):
+                raw = RawBatch(splits[r].images[s * b:(s + 1) * b], splits[r].labels[s * b:(s + 1) * b], None, None).to(dev)
+                x = transform_batch(raw, "nchw", torch.float32)
+                model.zero_grad(set_to_none=True)
+                loss = crit(model(x), raw.labels)
+                loss.backward()
+                losses[r].append(float(loss))
+                g = [p.grad.detach().clone() for p in model.parameters()]
+                acc = g if acc is None else [a + q for a, q in zip(acc, g)]
+            for p, a in zip(model.parameters(), acc):
+                p.grad = a / world
+            opt.step()
+        return {k: v.detach().cpu() for k, v in model.named_parameters()}, losses
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def _check_against_oracle(got, world, b, tag):
+    ref, ref_losses = _torch_oracle(world, b)
+    for r in range(world):
+        for step, (a, q) in enumerate(zip(got[r]["losses"], ref_losses[r])):
+            tol = 2e-3 if step < 2 else 3e-2            # same bounds as the single-GPU fp32 parity test
+            assert abs(a - q) < tol * max(1.0, abs(q)), (tag, r, got[r]["losses"], ref_losses[r])
+    for k, v in ref.items():
+        tol = 0.2 if (k.endswith(".bias") and "layers" in k) else 2e-2
+        assert _rel(got[0]["sd"][k], v) < tol, (tag, k, _rel(got[0]["sd"][k], v))
+    # replicas hold bit-identical weights after the fused reduce + SGD
+    for r in range(1, world):
+        for k, v in got[0]["sd"].items():
+            if "running" in k or "num_batches" in k:
+                continue
+            assert torch.equal(v, got[r]["sd"][k]), (tag, r, k)
+
+
+@pytest.mark.parametrize("world", WORLDS)
 @pytest.mark.parametrize("sync", ["gather_scatter", "allreduce", "bucketed"])
-def test_p2p_strategy_matches_nccl_baseline(sync):
-    p2p = _run(sync, "p2p")
-    nccl = _run(sync, "nccl")
+def test_p2p_strategy_matches_nccl_baseline(sync, world):
+    _need(world)
+    p2p = _run(sync, "p2p", world=world)
+    nccl = _run(sync, "nccl", world=world)
     assert p2p[0]["comm"] == "p2p" and nccl[0]["comm"] == "nccl"
-    for r in range(WORLD):
+    for r in range(world):
         for a, b in zip(p2p[r]["losses"], nccl[r]["losses"]):
             assert abs(a - b) < 2e-3 * max(1.0, abs(b)), (sync, r, p2p[r]["losses"], nccl[r]["losses"])
     # replicas hold bit-identical weights after the fused reduce+SGD
     for k, v in p2p[0]["sd"].items():
         if "running" in k or "num_batches" in k:
             continue
-        assert torch.equal(v, p2p[1]["sd"][k]), (sync, k)
+        for r in range(1, world):
+            assert torch.equal(v, p2p[r]["sd"][k]), (sync, r, k)
         if not (k.endswith(".bias") and "layers" in k):
             assert _rel(v, nccl[0]["sd"][k]) < 5e-3, (sync, k)
     # momentum shards were gathered: every rank reports the full optimizer state
     for i, m in p2p[0]["mom"].items():
-        assert torch.equal(m, p2p[1]["mom"][i]), (sync, i)
+        for r in range(1, world):
+            assert torch.equal(m, p2p[r]["mom"][i]), (sync, r, i)
 
 
-def test_nvls_multicast_reduce_matches_nccl_baseline():
+@pytest.mark.parametrize("sync,comm,world,b", [
+    ("gather_scatter", "p2p", 2, 16), ("allreduce", "p2p", 2, 16), ("bucketed", "auto", 2, 16),
+    ("gather_scatter", "p2p", 4, 64),      # BASELINE config 2: Part 2a, 4 ranks, global batch 256 (ref Part 2a/main.py:22,173)
+    ("allreduce", "p2p", 8, 32),           # BASELINE config 3: Part 2b, 8 ranks, global batch 256 (ref Part 2b/main.py:22)
+    ("bucketed", "auto", 4, 16),
+    ("bucketed", "auto", 8, 32),           # Part 3 at 8 ranks through the NVLS reduce where the box has multicast
+])
+def test_strategies_match_fp32_torch_oracle(sync, comm, world, b):
+    """The fused P2P / NVLS reduce + SGD against an fp32 torch model of the reference's data-parallel step
+    (not against this repository's own NCCL path)."""
+    _need(world)
+    got = _run(sync, comm, world=world, b=b)
+    if comm == "p2p":
+        assert got[0]["comm"] == "p2p"
+    print(f"[multi] {sync} world {world} per-rank batch {b}: comm {got[0]['comm']}, losses rank0 {got[0]['losses']}")
+    _check_against_oracle(got, world, b, f"{sync}/w{world}")
+
+
+@pytest.mark.parametrize("world", WORLDS)
+def test_nvls_multicast_reduce_matches_nccl_baseline(world):
     """K-S3: the in-switch reduction (multimem.ld_reduce / multimem.st) where the box exposes NVSwitch
     multicast; skipped (not failed) when it does not."""
+    _need(world)
     from cs744_ddp_b200.parallel.vmm import VmmArena
     if not VmmArena.supported(torch.device("cuda", 0)):
         pytest.skip("this device/driver does not report multicast support")
     os.environ["DDPB_NVLS"] = "1"
     try:
-        got = _run("bucketed", "auto")
+        got = _run("bucketed", "auto", world=world)
     finally:
         os.environ.pop("DDPB_NVLS", None)
     if got[0]["comm"] != "nvls":
         pytest.skip(f"multicast arena could not be set up on this box (fell back to {got[0]['comm']})")
-    nccl = _run("bucketed", "nccl")
-    for r in range(WORLD):
+    nccl = _run("bucketed", "nccl", world=world)
+    for r in range(world):
         for a, b in zip(got[r]["losses"], nccl[r]["losses"]):
             assert abs(a - b) < 2e-3 * max(1.0, abs(b)), (got[r]["losses"], nccl[r]["losses"])
     for k, v in got[0]["sd"].items():
         if "running" in k or "num_batches" in k:
             continue
-        assert torch.equal(v, got[1]["sd"][k]), k
+        for r in range(1, world):
+            assert torch.equal(v, got[r]["sd"][k]), (r, k)
         if not (k.endswith(".bias") and "layers" in k):
             assert _rel(v, nccl[0]["sd"][k]) < 5e-3, k
+    _check_against_oracle(got, world, B, f"nvls/w{world}")
 
 
 def test_bucketed_bf16_ddp_plan_runs_and_replicas_agree():
+    _need(2)
     out = _run("bucketed", "p2p", dtype="bf16", plan="ddp")
     for k, v in out[0]["sd"].items():
         if "running" in k or "num_batches" in k:
@@ -121,7 +213,50 @@ def test_bucketed_bf16_ddp_plan_runs_and_replicas_agree():
     assert all(abs(a - b) < 1.0 for a, b in zip(out[0]["losses"], out[1]["losses"]))
 
 
-def _stress_worker(rank, port, outdir):
+def _fit_worker(rank, world, port, outdir, comm):
+    import torch.distributed as dist
+    from cs744_ddp_b200.config import TrainConfig
+    from cs744_ddp_b200.trainer import Trainer
+    from cs744_ddp_b200.utils.logger import RunLogger
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    path = os.path.join(outdir, "ck.pt")
+    lines = []
+    cfg = TrainConfig(num_nodes=world, rank=rank, sync="bucketed", comm=comm, dtype="bf16", device="cuda",
+                      backend="native", global_batch=16 * world, synthetic=True, train_size=16 * world * 9,
+                      test_size=32, max_iters=8, log_every=4, lr=0.01, checkpoint=path, json_log=True)
+    t = Trainer(cfg, RunLogger("3", 4, rank, sink=lines.append, json_lines=True))
+    t.fit()
+    torch.save({"lines": lines, "comm": t.backend.comm_name(),
+                "mom": {i: st["momentum_buffer"].cpu() for i, st in t.backend.optimizer_state_dict()["state"].items()}},
+               os.path.join(outdir, f"fit_{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("comm", ["p2p", "auto"])
+def test_trainer_fit_writes_a_checkpoint_on_a_multi_gpu_native_run(comm):
+    """Saving needs the momentum shards of the two-shot / NVLS buckets: a collective every rank has to join
+    (a rank-0-only save spins on the cross-rank barrier until the watchdog traps).  Also: the JSON window
+    line carries the exposed-communication fraction."""
+    _need(2)
+    import json
+    import torch.multiprocessing as mp
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_fit_worker, args=(2, _free_port(), d, comm), nprocs=2, join=True)
+        blob = torch.load(os.path.join(d, "ck.pt"), weights_only=True)
+        res = [torch.load(os.path.join(d, f"fit_{r}.pt"), weights_only=False) for r in range(2)]
+    assert len(blob["model"]) == 58 and blob["epoch"] == 1 and len(blob["optimizer"]["state"]) == 34
+    for i, st in blob["optimizer"]["state"].items():
+        assert torch.equal(st["momentum_buffer"], res[0]["mom"][int(i)])          # the FULL state, not rank 0's shard
+        assert torch.equal(res[0]["mom"][int(i)], res[1]["mom"][int(i)])
+    windows = [json.loads(l)["window"] for l in res[0]["lines"] if l.startswith("{")]
+    assert len(windows) == 2 and "exposed_comm_frac" in windows[1] and 0 <= windows[1]["exposed_comm_frac"] < 1
+
+
+def _stress_worker(rank, WORLD, port, outdir):
     """Many fused reduce+SGD calls in every mode, with random host sleeps and random device-side spins in
     front of each one so that the ranks reach every cross-GPU barrier in a different order every time."""
     import random
@@ -166,11 +301,13 @@ def _stress_worker(rank, port, outdir):
     dist.destroy_process_group()
 
 
-def test_sync_kernels_survive_random_arrival_order():
+@pytest.mark.parametrize("world", WORLDS)
+def test_sync_kernels_survive_random_arrival_order(world):
     """racecheck cannot see peer accesses, so the flag/epoch barrier protocol is stressed with
     randomised host and device delays; every call must still produce the exact averaged SGD update."""
+    _need(world)
     import torch.multiprocessing as mp
     with tempfile.TemporaryDirectory() as d:
-        mp.spawn(_stress_worker, args=(_free_port(), d), nprocs=WORLD, join=True)
-        res = [torch.load(os.path.join(d, f"stress_{r}.pt"), weights_only=False) for r in range(WORLD)]
+        mp.spawn(_stress_worker, args=(world, _free_port(), d), nprocs=world, join=True)
+        res = [torch.load(os.path.join(d, f"stress_{r}.pt"), weights_only=False) for r in range(world)]
     assert all(r["bad"] == 0 for r in res), res

@@ -56,24 +56,38 @@ def main():
     sh = torch.empty(flat.numel(), device="cuda", dtype=torch.bfloat16)
     stream = torch.cuda.Stream()
     rows = []
-    size = 4 << 10
+    # 4 KB .. 512 MB in powers of four, plus the VGG-11 gradient itself (36.9 MB) and the 512 MB end point
+    sizes = sorted({4 << (10 + 2 * k) for k in range(9)} | {36_924_456 // 32 * 32, 512 << 20})
+    sizes = [v for v in sizes if v <= max_bytes]
+    # the sweep owns the GPU: as many CTAs as the flag table allows (in a training step the same kernels run
+    # next to backward with a small grid)
+    big_grid = int(os.environ.get("SWEEP_BLOCKS", str(min(nv.P2P_MAX_BLOCKS, 148))))
     with torch.cuda.stream(stream):
-        while size <= max_bytes:
+        for size in sizes:
             n = size // 4
             iters = 50 if size <= (8 << 20) else 10
             two = size >= 256 * 1024
-            t_p2p = timed(lambda: arena.sync(nv.P2P_TWOSHOT if two else nv.P2P_ONESHOT, 0, n, 0.1, 0.9, 1e-4), iters, world)
-            t_nvls = timed(lambda: arena.sync_nvls(0, n, 0.1, 0.9, 1e-4), iters, world) if has_nvls and two else float("nan")
+            # conv weights (99.85 % of a VGG gradient) publish their bf16 copy only: the swept range is "sharded"
+            shard = [0, n] if two else None
+            blocks = big_grid if size >= (4 << 20) else 0
+            t_p2p = timed(lambda: arena.sync(nv.P2P_TWOSHOT if two else nv.P2P_ONESHOT, 0, n, 0.1, 0.9, 1e-4,
+                                             blocks=min(blocks, 64), shard=shard), iters, world)
+            t_nvls = timed(lambda: arena.sync_nvls(0, n, 0.1, 0.9, 1e-4, blocks=blocks, shard=shard, one_shot=not two),
+                           iters, world) if has_nvls else float("nan")
             t_nccl = timed(lambda: dist.all_reduce(flat[:n]), iters, world)
 
             def nccl_sgd():
                 dist.all_reduce(flat[:n])
                 F.sgd_step(p_[:n], m_[:n], flat[:n], sh[:n], 0.1, 0.9, 1e-4, 1.0 / world)
             t_ns = timed(nccl_sgd, iters, world)
-            wire = (2.0 * (world - 1) / world * size) if two else ((world - 1) * size)
+            # bytes per direction per GPU: unicast two-shot pulls (W-1)/W*S of fp32 and pushes (W-1)/W*S/2 of bf16;
+            # NVLS: (W-1)/W*S of gradients leave each GPU for the switch (the slower direction)
+            wire = ((world - 1) / world * size) if two else ((world - 1) * size)
             roof_us = wire / (LINK_GBS * 1e3)
+            nvls_wire = (world - 1) / world * size + size / (2.0 * world)      # + the bf16 copy of the own slice
             rows.append({"bytes": size, "mode": "two-shot" if two else "one-shot", "p2p_fused_us": t_p2p,
-                         "nvls_fused_us": t_nvls, "nvls_frac_of_nvlink_roofline": (size / (LINK_GBS * 1e3)) / t_nvls,
+                         "nvls_fused_us": t_nvls, "nvls_frac_of_nvlink_roofline": (nvls_wire / (LINK_GBS * 1e3)) / t_nvls,
+                         "nvls_beats_nccl": bool(t_nvls <= t_nccl),
                          "nccl_us": t_nccl, "nccl_plus_sgd_us": t_ns, "p2p_algbw_gbs": size / t_p2p / 1e3,
                          "nccl_algbw_gbs": size / t_nccl / 1e3, "p2p_frac_of_nvlink_roofline": roof_us / t_p2p})
             if rank == 0:
@@ -81,7 +95,6 @@ def main():
                 print(f"{size:>11d} B {r['mode']:8s} p2p+sgd {t_p2p:9.1f} us | nvls+sgd {t_nvls:9.1f} us | nccl {t_nccl:9.1f} us | nccl+sgd {t_ns:9.1f} us"
                       f" | p2p algbw {r['p2p_algbw_gbs']:7.1f} GB/s | roofline frac {r['p2p_frac_of_nvlink_roofline']:.2f}",
                       flush=True)
-            size *= 4
     if rank == 0:
         out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
         os.makedirs(out, exist_ok=True)
