@@ -366,8 +366,9 @@ def run_ours(args) -> dict:
     # Self-check of the work the number stands for: after all those steps every replica must hold the same
     # weights, bit for bit (hash of the fp32 master arena, compared over the control plane), and the weights
     # must have moved and stayed finite.
+    be.gather_master()          # the fp32 master of a conv weight is current only on the rank that owns its slice
     torch.cuda.synchronize()
-    m = be.master
+    m = torch.cat([be.master, be.shadow.float()]) if args.dtype == "bf16" else be.master
     digest = torch.stack([m.view(torch.int32).to(torch.int64).sum(), (m.view(torch.int32).to(torch.int64) * 31 % 1000003).sum(),
                           torch.isfinite(m).all().to(torch.int64)])
     replicas_equal, finite = True, bool(digest[2])

@@ -595,29 +595,37 @@ class NativeBackend:
                 "exposed_comm_ms": end - bwd, "exposed_comm_frac": (end - bwd) / end if end > 0 else 0.0,
                 "buckets": rows}
 
-    def trace_step(self, data: torch.Tensor, target: torch.Tensor, graphed: bool = True) -> List[Dict[str, Any]]:
-        """One training step with an event after every kernel launch (all streams) - as a CUDA graph with
-        event-record nodes (``graphed``, the product path's timing) or eagerly: rows of
-        ``{kernel, block, stream, end_ms, ms}`` in launch order, where ``ms`` is the time since the
-        previous completion on the same stream (an upper bound of the kernel's own duration: it includes
-        any wait for another stream)."""
+    def trace_step(self, data: torch.Tensor, target: torch.Tensor, mode: str = "stamps") -> List[Dict[str, Any]]:
+        """One training step with per-kernel timing on every stream.  ``mode``:
+
+        * ``"stamps"`` - the production CUDA graph, unmodified; every kernel stamps ``%globaltimer`` at its
+          first CTA's start and its last warp's end (the real timeline, programmatic launches included);
+        * ``"graph"``  - the graph with an event-record node after every kernel (no overlap across nodes);
+        * ``"eager"``  - eager launches with an event after each (host-bound for the small kernels).
+
+        Rows in launch order: ``{kernel, block, stream, begin_ms, end_ms, ms}``; for the event modes
+        ``begin_ms`` is -1 and ``ms`` is the time since the previous completion on the same stream.
+        A real step (weights are updated); on several GPUs every rank must call it."""
+        code = {"eager": 0, "graph": 1, "stamps": 2}[mode]
         cap = 256
         names = ctypes.create_string_buffer(48 * cap)
         block = (ctypes.c_int * cap)()
         sid = (ctypes.c_int * cap)()
+        begin = (ctypes.c_float * cap)()
         end = (ctypes.c_float * cap)()
         n = ctypes.c_int(0)
         with self.on_stream():
             b = self._stage(data, target)
-            check(self._lib.ddpb_engine_trace_step(self._handle, b, stream_handle(), int(graphed), names, block, sid, end, cap,
-                                                   ctypes.byref(n)), "engine_trace_step")
+            check(self._lib.ddpb_engine_trace_step(self._handle, b, stream_handle(), code, names, block, sid, begin, end,
+                                                   cap, ctypes.byref(n)), "engine_trace_step")
         rows, last = [], {}
         label = {0: "main", 1: "wgrad", 2: "comm", 3: "comm2", 4: "other"}
         for i in range(n.value):
             name = names.raw[48 * i: 48 * (i + 1)].split(b"\0", 1)[0].decode()
             prev = last.get(sid[i], 0.0)
+            dur = float(end[i]) - (float(begin[i]) if code == 2 else prev)
             rows.append({"kernel": name, "block": int(block[i]), "stream": label[int(sid[i])],
-                         "end_ms": float(end[i]), "ms": float(end[i]) - prev})
+                         "begin_ms": float(begin[i]), "end_ms": float(end[i]), "ms": dur})
             last[sid[i]] = float(end[i])
         return rows
 

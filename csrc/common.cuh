@@ -67,6 +67,17 @@ static inline int pdl_active(cudaStream_t stream, int family) {
          cap == cudaStreamCaptureStatusActive;
 }
 
+// ---- in-kernel step tracer --------------------------------------------------------------------
+// Every kernel of the training step takes an int of launch flags: bit 0 = "execute
+// griddepcontrol.launch_dependents", bits 1.. = trace id (0: not traced).  A traced kernel stamps
+// %globaltimer into slot 2*id (earliest CTA start) and 2*id+1 (latest warp end) of the trace buffer,
+// which gives the step's real timeline INSIDE the production CUDA graph, programmatic launches
+// included (ddpb_engine_trace_step, mode 2).  The buffer pointer lives in a per-translation-unit
+// __device__ variable (no relocatable device code here), set through DDPB_KTRACE_SETTER's function.
+int kernel_flags(cudaStream_t stream, int family);     // pdl_active(...) | next trace id << 1
+void ktrace_enable(int on);                             // host: start / stop handing out trace ids (restarts at 1)
+int ktrace_last_id();                                   // host: the last id handed out
+
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                                     dim3 cluster, int pdl, Args... args) {
@@ -182,6 +193,35 @@ __device__ __forceinline__ float warp_sum(float v) {
 // ------------------------------------------------------------------------------------------
 // sm_100a PTX wrappers (device only)
 // ------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+static __device__ unsigned long long* g_ktrace;
+#define DDPB_KTRACE_SETTER(tu)                                                                   \
+  extern "C" int ddpb_ktrace_set_##tu(void* p) {                                                 \
+    return cudaMemcpyToSymbol(::ddpb::g_ktrace, &p, sizeof(p)) == cudaSuccess ? 0 : 1;                  \
+  }
+__device__ __forceinline__ unsigned long long ktrace_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// Slot layout: [id][32 lanes][begin, end]; a CTA uses lane (linear block index % 32) so that a grid of
+// thousands of CTAs does not serialise on one address.  One stamp per CTA, taken by its thread 0 (in every
+// kernel here thread 0 leaves last or together with the rest: final barriers, uniform loops).
+constexpr int KTRACE_LANES = 32;
+__device__ __forceinline__ unsigned long long* ktrace_slot(int id) {
+  const unsigned b = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  return g_ktrace + ((size_t)id * KTRACE_LANES + (b % KTRACE_LANES)) * 2;
+}
+__device__ __forceinline__ void ktrace_begin(int flags) {
+  const int id = flags >> 1;
+  if (id && threadIdx.x == 0 && threadIdx.y == 0 && threadIdx.z == 0) atomicMin(ktrace_slot(id), ktrace_now());
+}
+__device__ __forceinline__ void ktrace_end(int flags) {      // call where thread 0 leaves the kernel
+  const int id = flags >> 1;
+  if (id && threadIdx.x == 0 && threadIdx.y == 0 && threadIdx.z == 0) atomicMax(ktrace_slot(id) + 1, ktrace_now());
+}
+#endif
+
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 

@@ -102,8 +102,9 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
-  if (pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (pdl & 1) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
+  ktrace_begin(pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
 
   // software pipeline: the first window is requested before the per-channel constants, every later one
   // while the previous window is being processed (small layers are one dependent-latency chain long)
@@ -178,6 +179,7 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
     // dgrad epilogue do this block's BN-backward reduction from one value per output pixel
     if (winner) store_vec<T>(winner + (size_t)op * C + c0, by);
   }
+  ktrace_end(pdl);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -197,8 +199,9 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
-  if (pdl) pdl_launch_dependents();
+  if (pdl & 1) pdl_launch_dependents();
   pdl_wait();
+  ktrace_begin(pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
   float sc[V], sh[V], mu[V], is[V], a1[V], a2[V];
   ld_coh_vec<V>(mean + c0, mu);
   ld_coh_vec<V>(invstd + c0, is);
@@ -240,6 +243,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
   }
   block_reduce_channels<V>(sm, a1, c0, pl, ppb, C, sums);
   block_reduce_channels<V>(sm, a2, c0, pl, ppb, C, sums + C);
+  ktrace_end(pdl);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -260,8 +264,9 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
   const int ppb = blockDim.x / groups;
   const int c0 = g * V;
   const PoolGeom gm{H, W, log2_exact(W >> 1), log2_exact(H >> 1)};
-  if (pdl) pdl_launch_dependents();
+  if (pdl & 1) pdl_launch_dependents();
   pdl_wait();
+  ktrace_begin(pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
   // software pipeline as in the forward kernel: first window before the constants, next one during the current
   constexpr int NQ = POOL ? 4 : 1;
   const int stride = gridDim.x * ppb;
@@ -341,6 +346,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
     }
   }
   if (dbias) block_reduce_channels<V>(sm, ab, c0, pl, ppb, C, dbias);
+  ktrace_end(pdl);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -435,6 +441,7 @@ static int bn_check(int C, int H, int W, bool pool) {
 }
 
 }  // namespace ddpb
+DDPB_KTRACE_SETTER(bn_relu_pool)
 
 using namespace ddpb;
 
@@ -451,7 +458,7 @@ int fwd_launch(const void* y, const float* stats, const float* gamma, const floa
   DDPB_CUDA_CHECK(launch_ex(bn_fwd_kernel<T, POOL>, dim3(bn_grid(bn_fwd_kernel<T, POOL>, Pout, ppb, 0)), dim3(256), 0,
                             stream, dim3(1, 1, 1), 4, (const T*)y, stats, gamma, beta, (T*)out, save_mean,
                             save_invstd, rm, rv, nbt, (T*)winner, P, Pout, C, H, W, eps, momentum, training,
-                            pdl_active(stream, 4)));
+                            kernel_flags(stream, 4)));
   return DDPB_OK;
 }
 
@@ -467,11 +474,11 @@ int bwd_launch(const void* dout, const void* y, const float* mean, const float* 
   if (reduce)
     DDPB_CUDA_CHECK(launch_ex(bn_bwd_reduce_kernel<T, POOL>, dim3(bn_grid(bn_bwd_reduce_kernel<T, POOL>, Pout, ppb, smem)),
                               dim3(256), smem, stream, dim3(1, 1, 1), 8, (const T*)dout, (const T*)y, mean, invstd,
-                              gamma, beta, sums, Pout, C, H, W, pdl_active(stream, 8)));
+                              gamma, beta, sums, Pout, C, H, W, kernel_flags(stream, 8)));
   DDPB_CUDA_CHECK(launch_ex(bn_bwd_apply_kernel<T, POOL>, dim3(bn_grid(bn_bwd_apply_kernel<T, POOL>, Pout, ppb, smem)),
                             dim3(256), smem, stream, dim3(1, 1, 1), 16, (const T*)dout, (const T*)y, mean, invstd,
                             gamma, beta, (const float*)sums, (T*)dy, dgamma, dbeta, dbias, P, Pout, C, H, W,
-                            pdl_active(stream, 16)));
+                            kernel_flags(stream, 16)));
   return DDPB_OK;
 }
 

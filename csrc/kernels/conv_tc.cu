@@ -126,8 +126,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 1) tmem_alloc<BN>(tmem_slot);
   // everything above is private to this CTA and overlaps the previous kernel's tail (programmatic
   // dependent launch); global memory may only be touched after pdl_wait()
-  if (prm.pdl) pdl_launch_dependents();
+  if (prm.pdl & 1) pdl_launch_dependents();
   pdl_wait();
+  ktrace_begin(prm.pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
   if (trc && threadIdx.x == 0) trc[1] = global_timer_ns();            // prologue done, predecessor finished
   if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? ld_coh(&bias[n_tile * BN + i]) : 0.f;
   tc_fence_before();
@@ -430,6 +431,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   if (NC > 1) cluster_barrier();      // peers may still arrive on our barriers: do not exit before them
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
+  ktrace_end(prm.pdl);
   if (trc && threadIdx.x == 0) trc[7] = global_timer_ns();            // CTA done
 }
 
@@ -574,7 +576,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
       g_bnfwd.applied = true;
     }
   }
-  prm.pdl = pdl_active(stream, 1);
+  prm.pdl = kernel_flags(stream, 1);
   DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, NC, KS), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
@@ -682,6 +684,7 @@ static int dispatch(const void* in_v, const void* w_v, void* out_v, const float*
 }
 
 }  // namespace ddpb
+DDPB_KTRACE_SETTER(conv_tc)
 
 using namespace ddpb;
 

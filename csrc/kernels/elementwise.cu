@@ -46,7 +46,8 @@ __global__ void augment_kernel(const uint8_t* __restrict__ images,   // [N,32,32
 // ------------------------------------------------------------------------------------------
 __global__ void sgd_kernel(float* __restrict__ param, float* __restrict__ mom,
                            const float* __restrict__ grad, bf16* __restrict__ shadow, long long n4,
-                           float lr, float momentum, float wd, float gscale) {
+                           float lr, float momentum, float wd, float gscale, int flags) {
+  ktrace_begin(flags);
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   long long stride = (long long)gridDim.x * blockDim.x;
   for (; i < n4; i += stride) {
@@ -66,6 +67,7 @@ __global__ void sgd_kernel(float* __restrict__ param, float* __restrict__ mom,
       reinterpret_cast<uint2*>(shadow)[i] = s;
     }
   }
+  ktrace_end(flags);
 }
 
 __global__ void cast_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long n4) {
@@ -104,7 +106,8 @@ __global__ void nchw_to_nhwc_kernel(const TI* __restrict__ src, TO* __restrict__
 __global__ void __launch_bounds__(256)
 im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
                     bf16* __restrict__ w_pad, long long n_seg, int H, int W, int h_shift, int w_shift, int Cout, int pdl) {
-  if (pdl) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
+  ktrace_begin(pdl);
+  if (pdl & 1) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
   if (i < (long long)Cout * 8) {
@@ -138,6 +141,7 @@ im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16
     pk = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
   }
   reinterpret_cast<uint4*>(cols)[i] = pk;
+  ktrace_end(pdl);
 }
 
 // W == 32 fast path: one block = one image row.  The three input rows it needs are staged in shared
@@ -146,7 +150,8 @@ im2col3x3_c3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16
 __global__ void __launch_bounds__(256)
 im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
                           bf16* __restrict__ w_pad, int H, int h_shift, int Cout, int zero_pad, int pdl) {
-  if (pdl) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
+  ktrace_begin(pdl);
+  if (pdl & 1) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
   __shared__ unsigned short rows[3][34 * 3];       // pixels -1..32 of rows h-1..h+1, zero outside the image
   const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
   const int tid = threadIdx.x;
@@ -183,6 +188,7 @@ im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w
     pk = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
   }
   reinterpret_cast<uint4*>(cols)[(size_t)row * 256 + tid] = pk;
+  ktrace_end(pdl);
 }
 
 static int grid_for(long long n, int block, int cap = 0) {
@@ -193,6 +199,7 @@ static int grid_for(long long n, int block, int cap = 0) {
 }
 
 }  // namespace ddpb
+DDPB_KTRACE_SETTER(elementwise)
 
 using namespace ddpb;
 
@@ -219,7 +226,7 @@ extern "C" int ddpb_sgd_step(float* param, float* mom, const float* grad, void* 
   DDPB_REQUIRE(n % 4 == 0, "sgd: element count must be a multiple of 4 (arena slots are 64-aligned)");
   long long n4 = n / 4;
   sgd_kernel<<<grid_for(n4, 256), 256, 0, stream>>>(param, mom, grad, (bf16*)shadow_bf16, n4, lr, momentum,
-                                                    wd, grad_scale);
+                                                    wd, grad_scale, kernel_flags(stream, 0));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -268,12 +275,12 @@ extern "C" int ddpb_im2col3x3_c3(const void* x, const void* w_bf16, void* cols, 
   const long long blocks = (n_seg + 255) / 256;
   if (W == 32) {
     im2col3x3_c3_row32_kernel<<<(unsigned)((long long)B * H), 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
-                                                                               (bf16*)w_pad, H, h_shift, Cout, zero_pad, pdl_active(stream, 64));
+                                                                               (bf16*)w_pad, H, h_shift, Cout, zero_pad, kernel_flags(stream, 64));
     DDPB_LAUNCH_CHECK();
     return DDPB_OK;
   }
   im2col3x3_c3_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
-                                                            (bf16*)w_pad, n_seg, H, W, h_shift, w_shift, Cout, pdl_active(stream, 64));
+                                                            (bf16*)w_pad, n_seg, H, W, h_shift, w_shift, Cout, kernel_flags(stream, 64));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

@@ -23,8 +23,9 @@ __global__ void __launch_bounds__(128)
 fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ bias,
                  const int64_t* __restrict__ target, float* __restrict__ logits, float* __restrict__ dlogits,
                  float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch, int pdl) {
-  if (pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (pdl & 1) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
+  ktrace_begin(pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int b = blockIdx.x * (blockDim.x >> 5) + warp;
   if (b >= batch) return;
@@ -67,6 +68,7 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
     atomicAdd(loss, (lse - lt) * inv_batch);
     if (correct && arg == t) atomicAdd(correct, 1);
   }
+  ktrace_end(pdl);
 }
 
 // blocks [0, batch*FEAT/256): dA ; remaining blocks: dW and db (one thread per (class, feature))
@@ -74,7 +76,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 fc_bwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ dlogits,
               T* __restrict__ dact, float* __restrict__ dw, float* __restrict__ db, int batch, int blocks_da, int pdl) {
-  if (pdl) pdl_launch_dependents();     // launched normally itself (it follows the gradient memset)
+  ktrace_begin(pdl);
+  if (pdl & 1) pdl_launch_dependents();     // launched normally itself (it follows the gradient memset)
   if ((int)blockIdx.x < blocks_da) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= batch * FEAT) return;
@@ -103,9 +106,11 @@ fc_bwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const floa
       atomicAdd(&db[j], s);
     }
   }
+  ktrace_end(pdl);
 }
 
 }  // namespace ddpb
+DDPB_KTRACE_SETTER(fc_ce)
 
 using namespace ddpb;
 
@@ -119,11 +124,11 @@ extern "C" int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias
   if (dtype == DDPB_BF16)
     DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<bf16>, dim3(blocks), dim3(128), 0, stream, dim3(1, 1, 1), 32,
                               (const bf16*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
-                              batch, inv, pdl_active(stream, 32)));
+                              batch, inv, kernel_flags(stream, 32)));
   else
     DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<float>, dim3(blocks), dim3(128), 0, stream, dim3(1, 1, 1), 32,
                               (const float*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
-                              batch, inv, pdl_active(stream, 32)));
+                              batch, inv, kernel_flags(stream, 32)));
   return DDPB_OK;
 }
 
@@ -134,10 +139,10 @@ extern "C" int ddpb_fc_bwd(const void* act, const float* w, const float* dlogits
   int blocks_dw = ceil_div(NCLS * FEAT + NCLS, 256) * ceil_div(batch, FC_SLICE);
   if (dtype == DDPB_BF16)
     fc_bwd_kernel<bf16><<<blocks_da + blocks_dw, 256, 0, stream>>>((const bf16*)act, w, dlogits, (bf16*)dact, dw,
-                                                                  db, batch, blocks_da, pdl_active(stream, 64));
+                                                                  db, batch, blocks_da, kernel_flags(stream, 64));
   else
     fc_bwd_kernel<float><<<blocks_da + blocks_dw, 256, 0, stream>>>((const float*)act, w, dlogits, (float*)dact,
-                                                                   dw, db, batch, blocks_da, pdl_active(stream, 64));
+                                                                   dw, db, batch, blocks_da, kernel_flags(stream, 64));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }

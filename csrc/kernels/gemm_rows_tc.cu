@@ -62,8 +62,9 @@ gemm_rows_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<2 * GR_N>(tmem_slot);
-  if (prm.pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (prm.pdl & 1) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
+  ktrace_begin(prm.pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
   for (int i = threadIdx.x; i < GR_N; i += blockDim.x) bias_s[i] = bias ? ld_coh(&bias[n_tile * GR_N + i]) : 0.f;
   tc_fence_before();
   __syncthreads();
@@ -164,9 +165,11 @@ gemm_rows_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<2 * GR_N>(tmem_base);
+  ktrace_end(prm.pdl);
 }
 
 }  // namespace ddpb
+DDPB_KTRACE_SETTER(gemm_rows_tc)
 
 using namespace ddpb;
 
@@ -195,7 +198,7 @@ extern "C" int ddpb_gemm_rows_fwd_tc(const void* x, const void* w_bf16, const fl
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(gemm_rows_tc_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                          cudaSharedmemCarveoutMaxShared));
   }
-  prm.pdl = pdl_active(stream, 1);
+  prm.pdl = kernel_flags(stream, 1);
   DDPB_CUDA_CHECK(launch_ex(gemm_rows_tc_kernel, grid, dim3(192), smem, stream, dim3(1, 1, 1), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;

@@ -61,6 +61,7 @@ struct P2PArgs {
   float lr, momentum, wd;
   unsigned long long timeout_ns;
   unsigned int* err;                   // host-mapped [8] time-out record, or null
+  int kflags;                          // launch flags: trace id << 1 (see common.cuh)
   int n_shard;                         // element ranges whose fp32 master stays with its owner
   long long shard[2 * P2P_MAX_SHARD];  // [lo, hi) pairs, multiples of 8
 };
@@ -168,6 +169,7 @@ enum { MODE_ONESHOT = 0, MODE_TWOSHOT = 1, MODE_ROOT = 2, MODE_BCAST = 3, MODE_A
 template <int MODE>
 __global__ void __launch_bounds__(512)
 p2p_kernel(const P2PArgs a) {
+  ktrace_begin(a.kflags);
   cta_barrier_all_ranks(a, 0);
   const long long n8 = a.n / 8;
   const long long base8 = a.off / 8;
@@ -259,6 +261,7 @@ p2p_kernel(const P2PArgs a) {
     }
   }
   if (!a.skip_exit_barrier) cta_barrier_all_ranks(a, 1);
+  ktrace_end(a.kflags);
 }
 
 
@@ -301,6 +304,7 @@ template <int U>
 __global__ void __launch_bounds__(512)
 p2p_nvls_kernel(const NvlsArgs n) {
   const P2PArgs& a = n.base;
+  ktrace_begin(a.kflags);
   cta_barrier_all_ranks(a, 0);
   const long long n8 = a.n / 8, base8 = a.off / 8;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -347,6 +351,7 @@ p2p_nvls_kernel(const NvlsArgs n) {
     }
   }
   if (!a.skip_exit_barrier) cta_barrier_all_ranks(a, 1);
+  ktrace_end(a.kflags);
 }
 
 // ---- host side -----------------------------------------------------------------------------
@@ -403,6 +408,7 @@ static int fill_common(P2PArgs& a, void* const* flags, float* mom, void* epochs,
 }
 
 }  // namespace ddpb
+DDPB_KTRACE_SETTER(sync_p2p)
 
 using namespace ddpb;
 
@@ -432,6 +438,7 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
     a.shadow[r] = shadow ? (bf16*)shadow[r] : nullptr;
   }
   a.skip_exit_barrier = (mode & DDPB_P2P_NO_EXIT_BARRIER) ? 1 : 0;
+  a.kflags = kernel_flags(stream, 0);
   mode &= ~DDPB_P2P_NO_EXIT_BARRIER;
   switch (mode) {
     case DDPB_P2P_ONESHOT: p2p_kernel<MODE_ONESHOT><<<blocks, 512, 0, stream>>>(a); break;
@@ -474,8 +481,11 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   int rc = fill_common(a.base, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
   if (rc) return rc;
   // CTA shape of the NVLS kernel when it runs next to the backward kernels (DDPB_NVLS_THREADS / DDPB_NVLS_MAX_BLOCKS)
-  static int threads = 0, cap = 0;
+  static int threads = 0, cap = 0, unroll = 0;
   if (!threads) {
+    const char* u = getenv("DDPB_NVLS_UNROLL");
+    unroll = u ? atoi(u) : 4;
+    if (unroll != 1 && unroll != 2 && unroll != 4) unroll = 4;
     const char* t = getenv("DDPB_NVLS_THREADS");
     threads = t ? atoi(t) : 256;
     if (threads != 128 && threads != 256 && threads != 512) threads = 256;
@@ -494,8 +504,11 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   a.base.skip_exit_barrier = skip_exit_barrier;
   a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
   a.one_shot = mode == DDPB_P2P_ONESHOT ? 1 : 0;
+  a.base.kflags = kernel_flags(stream, 0);
   // loads in flight per thread: 2U x 16 bytes; small ranges take the low-register variant
-  if (units >= (long long)blocks * threads * 4) p2p_nvls_kernel<4><<<blocks, threads, 0, stream>>>(a);
+  const bool big = units >= (long long)blocks * threads * 4;
+  if (big && unroll == 4) p2p_nvls_kernel<4><<<blocks, threads, 0, stream>>>(a);
+  else if (big && unroll == 2) p2p_nvls_kernel<2><<<blocks, threads, 0, stream>>>(a);
   else p2p_nvls_kernel<1><<<blocks, threads, 0, stream>>>(a);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;

@@ -83,8 +83,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<WG_TMEM_COLS>(tmem_slot);
-  if (prm.pdl) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  if (prm.pdl & 1) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
   pdl_wait();
+  ktrace_begin(prm.pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
   tc_fence_before();
   __syncthreads();
   if (M == 64 && prm.cl > 1) cluster_barrier();     // rank 0's red_bar exists before any peer can arrive on it
@@ -212,9 +213,11 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<WG_TMEM_COLS>(tmem_base);
+  ktrace_end(prm.pdl);
 }
 
 }  // namespace ddpb
+DDPB_KTRACE_SETTER(wgrad_tc)
 
 using namespace ddpb;
 
@@ -267,7 +270,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
   }
   if (split_k > prm.total_chunks) split_k = prm.total_chunks;
   prm.dw_raw = nullptr; prm.ld_raw = 0; prm.cols_raw = 0; prm.cl = 1;
-  prm.pdl = pdl_active(stream, 2);
+  prm.pdl = kernel_flags(stream, 2);
   dim3 grid(base_ctas / 3, 3, split_k);
   constexpr int EPI_BYTES = WG_TAPS * 2 * WG_M * 128;       // fp32 staging of the epilogue (96 KB)
 #define DDPB_WGRAD_LAUNCH(ST)                                                                                  \
@@ -313,7 +316,7 @@ extern "C" int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw
   prm.total_chunks = B * prm.chunks_per_img;
   prm.Cin = 64; prm.Cout = Cout;
   prm.dw_raw = dw; prm.ld_raw = ld; prm.cols_raw = cols;
-  prm.pdl = pdl_active(stream, 2);
+  prm.pdl = kernel_flags(stream, 2);
   const int base_ctas = Cout / 64;
   // CTA count: more CTAs per SM put more loads in flight (both operands stream from HBM), but every CTA
   // ends with 64 x 27 atomic adds on the same addresses; measured best around one CTA per SM

@@ -81,6 +81,8 @@ struct Engine {
   std::vector<Bucket> buckets;
   std::vector<long long> shard;          // [lo, hi) arena ranges of the conv weights: fp32 master stays with its owner
   bool shard_master = true;              // DDPB_SHARD_MASTER=0: publish the fp32 master of every element
+  bool zero_async = true;                // DDPB_ZERO_ASYNC=0: clear the gradients at the start of backward, on its stream
+  bool nvls_oneshot = true;              // DDPB_NVLS_ONESHOT=0: small buckets use the unicast one-shot kernel
   cudaStream_t comm = nullptr, comm2 = nullptr, wg = nullptr;
   bool two_comm = true, comm2_used = false;   // multi-GPU: buckets alternate between two streams (DDPB_TWO_COMM=0: one)
   std::vector<cudaEvent_t> bucket_ev, ev_dy, ev_dg, ev_wg;
@@ -94,7 +96,10 @@ struct Engine {
   cudaEvent_t prof_start = nullptr, prof_fwd = nullptr, prof_bwd = nullptr, prof_end = nullptr;
   std::vector<cudaEvent_t> prof_ready, prof_done;
   // per-kernel trace (ddpb_engine_trace_step): one event after every launch, on its stream
-  struct TraceRec { char name[48]; int block; int stream; cudaEvent_t ev; };
+  struct TraceRec { char name[48]; int block; int stream; cudaEvent_t ev; int id_lo, id_hi; };
+  int trace_mode = 0;                  // 0 eager events, 1 graph + event nodes, 2 graph + in-kernel stamps
+  int trace_id_mark = 0;               // trace ids handed out before the current LAUNCH
+  unsigned long long* ktrace_buf = nullptr;    // device [2 * kTraceSlots]
   bool trace_on = false;
   bool trace_external = false;         // tracing inside a stream capture: event-record NODES (cudaEventRecordExternal)
   int trace_block = -1;                // conv block the launches belong to (-1: classifier / optimizer)
@@ -115,6 +120,13 @@ static void add_counts(NameCounts& into, const NameCounts& from, long long times
   for (const auto& kv : from) into[kv.first] += kv.second * times;
 }
 
+static constexpr int kTraceSlots = 512 * 32;      // 512 trace ids x KTRACE_LANES (common.cuh)
+extern "C" {
+int ddpb_ktrace_set_conv_tc(void*); int ddpb_ktrace_set_wgrad_tc(void*); int ddpb_ktrace_set_gemm_rows_tc(void*);
+int ddpb_ktrace_set_bn_relu_pool(void*); int ddpb_ktrace_set_fc_ce(void*); int ddpb_ktrace_set_elementwise(void*);
+int ddpb_ktrace_set_sync_p2p(void*);
+}
+
 static int trace_mark(Engine* e, cudaStream_t stream, const char* call_text) {
   if (e->trace_n == e->trace.size()) {
     Engine::TraceRec r;
@@ -130,6 +142,11 @@ static int trace_mark(Engine* e, cudaStream_t stream, const char* call_text) {
   r.name[n] = 0;
   r.block = e->trace_block;
   r.stream = stream == e->trace_main ? 0 : (stream == e->wg ? 1 : (stream == e->comm ? 2 : (stream == e->comm2 ? 3 : 4)));
+  if (e->trace_mode == 2) {            // the kernels stamp themselves: remember which trace ids this call used
+    r.id_lo = e->trace_id_mark + 1; r.id_hi = ktrace_last_id();
+    e->trace_id_mark = r.id_hi;
+    return DDPB_OK;
+  }
   if (e->trace_external) DDPB_CUDA_CHECK(cudaEventRecordWithFlags(r.ev, stream, cudaEventRecordExternal));
   else DDPB_CUDA_CHECK(cudaEventRecord(r.ev, stream));
   return DDPB_OK;
@@ -454,7 +471,7 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   const int blocks = (int)(want < 1 ? 1 : (want > 64 ? 64 : want));     // it runs next to the backward kernels
   const long long* sh_tab = e->shard.empty() ? nullptr : e->shard.data();
   const int n_sh = (int)e->shard.size() / 2;
-  if (e->mc_arena) {
+  if (e->mc_arena && (b.mode == DDPB_P2P_TWOSHOT || e->nvls_oneshot)) {
     // NVLS: the switch reduces; big buckets: the owner of a slice updates it and one multicast store
     // publishes the result; small buckets: every rank pulls the reduced sum and updates its own replica
     char* mc = (char*)e->mc_arena;
@@ -623,7 +640,7 @@ struct NvtxRange {
 };
 
 static int run_kind(Engine* e, int kind, int B, cudaStream_t s) {
-  const bool whole = kind == KIND_STEP;
+  const bool whole = kind == KIND_STEP && e->zero_async;
   if (kind & KIND_FWD) {
     NvtxRange r("ddpb.forward");
     ECHECK(forward(e, B, 1, s, whole));
@@ -723,6 +740,8 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   if (const char* tc = getenv("DDPB_TWO_COMM")) e->two_comm = tc[0] != '0';
   if (const char* ff = getenv("DDPB_FUSE_BN_FWD")) e->fuse_bn_fwd = ff[0] != '0';
   if (const char* sm = getenv("DDPB_SHARD_MASTER")) e->shard_master = sm[0] != '0';
+  if (const char* za = getenv("DDPB_ZERO_ASYNC")) e->zero_async = za[0] != '0';
+  if (const char* no = getenv("DDPB_NVLS_ONESHOT")) e->nvls_oneshot = no[0] != '0';
   int rc = plan_layout(e);
   if (!rc) { plan_buckets(e); rc = alloc_all(e); }
   if (rc) { delete e; return rc; }
@@ -739,6 +758,7 @@ extern "C" int ddpb_engine_destroy(void* handle) {
   for (int r = 0; r < e->cfg.world; ++r)
     if (r != e->cfg.rank && e->peer_arena[r] && !e->arena_external) cudaIpcCloseMemHandle(e->peer_arena[r]);
   for (auto& b : e->blocks) { cudaFree(b.y); cudaFree(b.act); if (b.win) cudaFree(b.win); }
+  if (e->ktrace_buf) cudaFree(e->ktrace_buf);
   void* frees[] = {e->epochs, e->scratch, e->mean, e->invstd, e->nbt, e->logits, e->dlogits, e->eval_loss,
                    e->input, e->target, e->dy_buf2[0], e->dy_buf2[1], e->dact, e->x0cols, e->w0pad,
                    e->arena_external ? nullptr : e->arena};
@@ -884,10 +904,10 @@ extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s,
   e->counting = 0; e->counting_by_name.clear();
   int rc = DDPB_OK;
   cudaEventRecord(e->prof_start, s);
-  rc = forward(e, batch, 1, s, true);
+  rc = forward(e, batch, 1, s, e->zero_async);
   if (!rc) rc = loss_fwd(e, batch, 1, s);
   cudaEventRecord(e->prof_fwd, s);
-  if (!rc) rc = backward(e, batch, s, true);
+  if (!rc) rc = backward(e, batch, s, e->zero_async);
   cudaEventRecord(e->prof_end, s);
   e->prof_on = false;
   e->launches += e->counting; add_counts(e->launches_by_name, e->counting_by_name);
@@ -918,27 +938,42 @@ extern "C" int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t s,
 // nodes (no host in the loop, three launches, the last one is read); 0 launches eagerly.  Real steps: weights
 // are updated.  Synchronises.
 extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, int graphed, char* names, int* block,
-                                      int* stream_id, float* end_ms, int max_rows, int* n_rows) {
+                                      int* stream_id, float* begin_ms, float* end_ms, int max_rows, int* n_rows) {
   Engine* e = (Engine*)handle;
   DDPB_REQUIRE(e && names && block && stream_id && end_ms && n_rows, "engine_trace_step: null argument");
   DDPB_REQUIRE(batch > 0 && batch <= e->cfg.max_batch, "engine_trace_step: batch %d out of range", batch);
+  DDPB_REQUIRE(graphed >= 0 && graphed <= 2, "engine_trace_step: mode must be 0, 1 or 2");
   if (!e->trace_start) DDPB_CUDA_CHECK(cudaEventCreate(&e->trace_start));
+  const bool stamps = graphed == 2;
+  if (stamps && !e->ktrace_buf) {
+    DDPB_CUDA_CHECK(cudaMalloc(&e->ktrace_buf, sizeof(unsigned long long) * 2 * kTraceSlots));
+    void* p = e->ktrace_buf;
+    int bad = ddpb_ktrace_set_conv_tc(p) | ddpb_ktrace_set_wgrad_tc(p) | ddpb_ktrace_set_gemm_rows_tc(p) |
+              ddpb_ktrace_set_bn_relu_pool(p) | ddpb_ktrace_set_fc_ce(p) | ddpb_ktrace_set_elementwise(p) |
+              ddpb_ktrace_set_sync_p2p(p);
+    DDPB_REQUIRE(!bad, "engine_trace_step: could not publish the trace buffer to the kernels");
+  }
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   if (graphed) {
-    // The step as the product path runs it - one CUDA graph, no host in the loop - with an event-record
-    // node after every kernel.  (Such a node sits between two kernels, so programmatic dependent launch
-    // does not apply across it: the rows are kernel times without prologue overlap.)
+    // The step as the product path runs it: one CUDA graph, no host in the loop.  Mode 1 puts an
+    // event-record node after every kernel (which also disables programmatic launches across it and costs
+    // a few microseconds per node); mode 2 captures the unmodified step and lets every kernel stamp
+    // %globaltimer itself, so the rows are the real timeline, prologue overlap included.
     DDPB_CUDA_CHECK(cudaStreamSynchronize(s));
     DDPB_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
   }
-  e->trace_on = true; e->trace_external = graphed != 0; e->trace_n = 0; e->trace_main = s; e->counting = 0; e->counting_by_name.clear();
-  if (graphed) cudaEventRecordWithFlags(e->trace_start, s, cudaEventRecordExternal);
+  e->trace_on = true; e->trace_external = graphed == 1; e->trace_mode = graphed; e->trace_n = 0; e->trace_main = s;
+  e->trace_id_mark = 0;
+  e->counting = 0; e->counting_by_name.clear();
+  if (stamps) ktrace_enable(1);
+  else if (graphed) cudaEventRecordWithFlags(e->trace_start, s, cudaEventRecordExternal);
   else cudaEventRecord(e->trace_start, s);
-  int rc = forward(e, batch, 1, s, true);
+  int rc = forward(e, batch, 1, s, e->zero_async);
   if (!rc) rc = loss_fwd(e, batch, 1, s);
-  if (!rc) rc = backward(e, batch, s, true);
-  e->trace_on = false; e->trace_external = false;
+  if (!rc) rc = backward(e, batch, s, e->zero_async);
+  if (stamps) ktrace_enable(0);
+  e->trace_on = false; e->trace_external = false; e->trace_mode = 0;
   if (graphed) {
     cudaError_t ce = cudaStreamEndCapture(s, &graph);
     if (rc || ce != cudaSuccess || !graph) {
@@ -950,7 +985,14 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
     ce = cudaGraphInstantiate(&exec, graph, 0);
     cudaGraphDestroy(graph);
     DDPB_REQUIRE(ce == cudaSuccess, "engine_trace_step: cudaGraphInstantiate failed (%s)", cudaGetErrorString(ce));
-    for (int rep = 0; rep < 3; ++rep) DDPB_CUDA_CHECK(cudaGraphLaunch(exec, s));     // three real steps; the last one is read
+    for (int rep = 0; rep < 3; ++rep) {           // three real steps; the last one is read
+      if (stamps) {
+        DDPB_CUDA_CHECK(cudaMemsetAsync(e->ktrace_buf, 0xFF, sizeof(unsigned long long) * 2 * kTraceSlots, s));
+        // (begin slots start at the maximum, end slots are taken with atomicMax: clear those to zero)
+        DDPB_CUDA_CHECK(cudaMemset2DAsync(e->ktrace_buf + 1, 16, 0, 8, kTraceSlots, s));
+      }
+      DDPB_CUDA_CHECK(cudaGraphLaunch(exec, s));
+    }
     e->launches += 3 * e->counting; add_counts(e->launches_by_name, e->counting_by_name, 3);
   } else {
     e->launches += e->counting; add_counts(e->launches_by_name, e->counting_by_name);
@@ -961,14 +1003,35 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
   DDPB_CUDA_CHECK(cudaStreamSynchronize(e->comm2));
   DDPB_CUDA_CHECK(cudaStreamSynchronize(e->wg));
   if (exec) cudaGraphExecDestroy(exec);
+  std::vector<unsigned long long> host;
+  unsigned long long t0 = ~0ull;
+  if (stamps) {
+    host.resize(2 * kTraceSlots);
+    DDPB_CUDA_CHECK(cudaMemcpy(host.data(), e->ktrace_buf, host.size() * 8, cudaMemcpyDeviceToHost));
+    for (int i = 32; i < kTraceSlots; ++i) if (host[2 * i + 1] != 0 && host[2 * i] < t0) t0 = host[2 * i];
+  }
   int n = 0;
   for (size_t i = 0; i < e->trace_n && n < max_rows; ++i, ++n) {
     const Engine::TraceRec& r = e->trace[i];
     memcpy(names + 48 * n, r.name, 48);
     block[n] = r.block; stream_id[n] = r.stream;
-    float ms = -1.f;
-    if (cudaEventElapsedTime(&ms, e->trace_start, r.ev) != cudaSuccess) { (void)cudaGetLastError(); ms = -1.f; }
-    end_ms[n] = ms;
+    float b_ms = -1.f, e_ms = -1.f;
+    if (stamps) {
+      unsigned long long lo = ~0ull, hi = 0;
+      for (int id = r.id_lo; id <= r.id_hi && id < kTraceSlots / 32; ++id)
+        for (int lane = 0; lane < 32; ++lane) {
+          const size_t k = 2 * ((size_t)id * 32 + lane);
+          if (host[k + 1] == 0) continue;           // lane unused / kernel not instrumented
+          if (host[k] < lo) lo = host[k];
+          if (host[k + 1] > hi) hi = host[k + 1];
+        }
+      if (hi) { b_ms = (float)((double)(lo - t0) * 1e-6); e_ms = (float)((double)(hi - t0) * 1e-6); }
+    } else if (cudaEventElapsedTime(&e_ms, e->trace_start, r.ev) != cudaSuccess) {
+      (void)cudaGetLastError();
+      e_ms = -1.f;
+    }
+    if (begin_ms) begin_ms[n] = b_ms;
+    end_ms[n] = e_ms;
   }
   *n_rows = n;
   return DDPB_OK;

@@ -41,6 +41,15 @@ int pdl_mask() {
   return m;
 }
 
+static int g_ktrace_on = 0, g_ktrace_id = 0;
+void ktrace_enable(int on) { g_ktrace_on = on ? 1 : 0; g_ktrace_id = 0; }
+int ktrace_last_id() { return g_ktrace_id; }
+int kernel_flags(cudaStream_t stream, int family) {
+  const int pdl = pdl_active(stream, family) ? 1 : 0;
+  if (!g_ktrace_on) return pdl;
+  return pdl | (++g_ktrace_id << 1);
+}
+
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;

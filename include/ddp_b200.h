@@ -324,10 +324,12 @@ int ddpb_engine_profile_step(void* handle, int batch, cudaStream_t stream, float
  * Row i: names + 48 * i (entry point name), block[i] (conv block, -1 classifier / optimizer),
  * stream_id[i] (0 main, 1 weight-gradient, 2 / 3 communication), end_ms[i] (completion time since the
  * step start).  graphed = 1: the step runs as one CUDA graph with event-record nodes (the product path's
- * timing, minus programmatic-launch overlap); 0: eager launches (host-bound for the small kernels).
+ * timing, minus programmatic-launch overlap); 0: eager launches (host-bound for the small kernels);
+ * 2: the unmodified production graph with every kernel stamping %globaltimer itself (begin_ms = first CTA
+ * start, end_ms = last warp end): the real timeline, programmatic launch overlap included.
  * The reference has only three host timers per iteration (ref Part 1/main.py:33-43). */
 int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t stream, int graphed, char* names, int* block,
-                           int* stream_id, float* end_ms, int max_rows, int* n_rows);
+                           int* stream_id, float* begin_ms, float* end_ms, int max_rows, int* n_rows);
 /* "entry_point=count;..." of everything launched since the engine was created, graph replays included
  * (no reference counterpart; the reference's sync calls are visible in its Python source instead).
  * Returns the buffer length needed. */
