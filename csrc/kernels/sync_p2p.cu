@@ -89,6 +89,9 @@ __device__ __forceinline__ void st_peer(float* p, float4 v) {
                "f"(v.w)
                : "memory");
 }
+__device__ __forceinline__ void st_peer_u2(void* p, uint2 v) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
 __device__ __forceinline__ void st_peer_u4(void* p, uint4 v) {
   asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
@@ -146,6 +149,7 @@ __device__ __forceinline__ void slice_of(long long units, int world, int r, long
   *lo = a; *hi = b;
 }
 
+// (slices are cut in units of 4 elements; every range handed in is a multiple of 8 elements)
 // is arena element e inside one of the ranges whose fp32 master is not published?
 __device__ __forceinline__ bool is_sharded(const P2PArgs& a, long long e) {
   bool in = false;
@@ -165,80 +169,71 @@ __device__ __forceinline__ uint4 pack8(const float4& a, const float4& b) {
 
 enum { MODE_ONESHOT = 0, MODE_TWOSHOT = 1, MODE_ROOT = 2, MODE_BCAST = 3, MODE_ALLGATHER = 4 };
 
-// The unit of work is 8 consecutive elements: two 16-byte fp32 accesses and one 16-byte bf16 access.
-template <int MODE>
-__global__ void __launch_bounds__(512)
+// The unit of work is one 16-byte access (4 elements) per thread with consecutive lanes on consecutive
+// addresses: a warp's load instruction covers 512 contiguous bytes.  (Two adjacent 16-byte loads per thread
+// - a 32-byte stride between lanes - ran at HALF the NVLink read rate: 360 instead of 690 GB/s, measured
+// with tools/peer_read_probe.py.)  Shapes as for the NVLS kernel below: THREADS = 128 runs next to the
+// backward kernels; THREADS = 512 is for a caller that owns the GPU.  U units are in flight per thread.
+template <int MODE, int U, int THREADS>
+__global__ void __launch_bounds__(THREADS)
 p2p_kernel(const P2PArgs a) {
   ktrace_begin(a.kflags);
   cta_barrier_all_ranks(a, 0);
-  const long long n8 = a.n / 8;
-  const long long base8 = a.off / 8;
-  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long nthr = (long long)gridDim.x * blockDim.x;
+  const long long n4 = a.n / 4;
+  const long long base4 = a.off / 4;
+  const long long tid = (long long)blockIdx.x * THREADS + threadIdx.x;
+  const long long nthr = (long long)gridDim.x * THREADS;
   const float inv_w = 1.f / (float)a.world;
 
   if (MODE == MODE_ONESHOT || MODE == MODE_TWOSHOT || MODE == MODE_ROOT) {
-    long long lo = 0, hi = n8;
-    if (MODE == MODE_TWOSHOT) slice_of(n8, a.world, a.rank, &lo, &hi);
+    long long lo = 0, hi = n4;
+    if (MODE == MODE_TWOSHOT) slice_of(n4, a.world, a.rank, &lo, &hi);
     if (MODE == MODE_ROOT && a.rank != 0) hi = lo;          // only the root computes
-    // A peer load takes ~2 us over NVLink: each thread keeps 2U independent 16-byte loads per rank in
-    // flight (U units `nthr` apart), otherwise the loop is bound by latency, not by the link.
-    constexpr int U = 2;
+    float* const master = a.master[a.rank];
     for (long long i0 = lo + tid; i0 < hi; i0 += nthr * U) {
-      float4 s[U][2];
+      float4 s[U], pp[U], mm[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) s[u][0] = s[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int u = 0; u < U; ++u) {
+        s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        // master weights and momentum do not depend on the peers: fetch them under the same round trip
+        const long long i = i0 + u * nthr;
+        const long long e = (base4 + (i < hi ? i : lo)) * 4;      // clamp: a harmless in-range re-read
+        pp[u] = *reinterpret_cast<const float4*>(master + e);
+        mm[u] = *reinterpret_cast<const float4*>(a.mom + e);
+      }
 #pragma unroll
       for (int r = 0; r < P2P_MAX_RANKS; ++r) {          // fixed rank order: identical sums on every rank
         if (r < a.world) {
-          float4 g[U][2];
+          float4 g[U];
 #pragma unroll
           for (int u = 0; u < U; ++u) {
             const long long i = i0 + u * nthr;
-            const long long e = (base8 + (i < hi ? i : lo)) * 8;      // clamp: a harmless in-range re-read
-            if (r == a.rank) {
-              g[u][0] = *reinterpret_cast<const float4*>(a.grad[r] + e);
-              g[u][1] = *reinterpret_cast<const float4*>(a.grad[r] + e + 4);
-            } else {
-              g[u][0] = ld_peer(a.grad[r] + e);
-              g[u][1] = ld_peer(a.grad[r] + e + 4);
-            }
+            const long long e = (base4 + (i < hi ? i : lo)) * 4;
+            g[u] = (r == a.rank) ? *reinterpret_cast<const float4*>(a.grad[r] + e) : ld_peer(a.grad[r] + e);
           }
 #pragma unroll
-          for (int u = 0; u < U; ++u)
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              s[u][h].x += g[u][h].x; s[u][h].y += g[u][h].y; s[u][h].z += g[u][h].z; s[u][h].w += g[u][h].w;
-            }
+          for (int u = 0; u < U; ++u) { s[u].x += g[u].x; s[u].y += g[u].y; s[u].z += g[u].z; s[u].w += g[u].w; }
         }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const long long i = i0 + u * nthr;
         if (i >= hi) break;
-        const long long e = (base8 + i) * 8;
-        float* mp = a.master[a.rank] + e;
-        float4 p0 = *reinterpret_cast<const float4*>(mp), p1 = *reinterpret_cast<const float4*>(mp + 4);
-        float4 m0 = *reinterpret_cast<const float4*>(a.mom + e), m1 = *reinterpret_cast<const float4*>(a.mom + e + 4);
-        sgd_update(s[u][0], p0, m0, inv_w, a.lr, a.momentum, a.wd);
-        sgd_update(s[u][1], p1, m1, inv_w, a.lr, a.momentum, a.wd);
-        *reinterpret_cast<float4*>(a.mom + e) = m0;
-        *reinterpret_cast<float4*>(a.mom + e + 4) = m1;
-        const uint4 sh = pack8(p0, p1);
+        const long long e = (base4 + i) * 4;
+        float4 p = pp[u], m = mm[u];
+        sgd_update(s[u], p, m, inv_w, a.lr, a.momentum, a.wd);
+        *reinterpret_cast<float4*>(a.mom + e) = m;
+        const uint2 sh = make_uint2(pack_bf16x2(p.x, p.y), pack_bf16x2(p.z, p.w));
         if (MODE == MODE_ONESHOT) {
-          *reinterpret_cast<float4*>(mp) = p0;
-          *reinterpret_cast<float4*>(mp + 4) = p1;
-          if (a.shadow[a.rank]) *reinterpret_cast<uint4*>(a.shadow[a.rank] + e) = sh;
+          *reinterpret_cast<float4*>(master + e) = p;
+          if (a.shadow[a.rank]) *reinterpret_cast<uint2*>(a.shadow[a.rank] + e) = sh;
         } else {
           // fp32 master of a sharded range stays here; peers only ever read its bf16 copy
           const bool keep = a.shadow[a.rank] != nullptr && is_sharded(a, e);
-          if (keep) {
-            *reinterpret_cast<float4*>(mp) = p0;
-            *reinterpret_cast<float4*>(mp + 4) = p1;
-          }
+          if (keep) *reinterpret_cast<float4*>(master + e) = p;
           for (int r = 0; r < a.world; ++r) {
-            if (!keep) { st_peer(a.master[r] + e, p0); st_peer(a.master[r] + e + 4, p1); }
-            if (a.shadow[r]) st_peer_u4(a.shadow[r] + e, sh);
+            if (!keep) st_peer(a.master[r] + e, p);
+            if (a.shadow[r]) st_peer_u2(a.shadow[r] + e, sh);
           }
         }
       }
@@ -246,15 +241,15 @@ p2p_kernel(const P2PArgs a) {
   } else if (MODE == MODE_BCAST) {
     // `grad` holds the buffer being broadcast (any fp32 range of the symmetric arena)
     if (a.rank != 0)
-      for (long long i = tid; i < n8 * 2; i += nthr) {
-        const long long e = base8 * 8 + i * 4;
+      for (long long i = tid; i < n4; i += nthr) {
+        const long long e = (base4 + i) * 4;
         *reinterpret_cast<float4*>(a.grad[a.rank] + e) = ld_peer(a.grad[0] + e);
       }
   } else if (MODE == MODE_ALLGATHER) {
     long long lo, hi;
-    slice_of(n8, a.world, a.rank, &lo, &hi);
-    for (long long i = lo * 2 + tid; i < hi * 2; i += nthr) {
-      const long long e = base8 * 8 + i * 4;
+    slice_of(n4, a.world, a.rank, &lo, &hi);
+    for (long long i = lo + tid; i < hi; i += nthr) {
+      const long long e = (base4 + i) * 4;
       float4 v = *reinterpret_cast<const float4*>(a.grad[a.rank] + e);
       for (int r = 0; r < a.world; ++r)
         if (r != a.rank) st_peer(a.grad[r] + e, v);
@@ -286,6 +281,9 @@ __device__ __forceinline__ void multimem_st(float* mc, float4 v) {
                "f"(v.z), "f"(v.w)
                : "memory");
 }
+__device__ __forceinline__ void multimem_st_bf16x4(void* mc, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(mc), "r"(v.x), "r"(v.y) : "memory");
+}
 __device__ __forceinline__ void multimem_st_bf16x8(void* mc, uint4 v) {
   asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y),
                "r"(v.z), "r"(v.w)
@@ -300,58 +298,106 @@ struct NvlsArgs {
   int one_shot;            // 1: every rank reduces the WHOLE range through the switch and updates its own replica
 };
 
-template <int U>
-__global__ void __launch_bounds__(512)
+// U units (one 16-byte access each, lanes contiguous) per thread and iteration.  ALL loads of an iteration -
+// the switch-reduced gradients and the local master weights and momentum - are issued before anything is
+// consumed, so one round trip covers them all.  Two shapes: THREADS = 128 is the one that runs next to the
+// backward kernels (under 10 K registers per CTA: it fits beside two convolution CTAs instead of evicting
+// one); THREADS = 512 is for a caller that owns the GPU (the bandwidth sweep).
+template <int U, int THREADS>
+__global__ void __launch_bounds__(THREADS)
 p2p_nvls_kernel(const NvlsArgs n) {
   const P2PArgs& a = n.base;
   ktrace_begin(a.kflags);
   cta_barrier_all_ranks(a, 0);
-  const long long n8 = a.n / 8, base8 = a.off / 8;
-  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long nthr = (long long)gridDim.x * blockDim.x;
+  const long long n4 = a.n / 4, base4 = a.off / 4;
+  const long long tid = (long long)blockIdx.x * THREADS + threadIdx.x;
+  const long long nthr = (long long)gridDim.x * THREADS;
   const float inv_w = 1.f / (float)a.world;
-  long long lo = 0, hi = n8;
-  if (!n.one_shot) slice_of(n8, a.world, a.rank, &lo, &hi);
+  long long lo = 0, hi = n4;
+  if (!n.one_shot) slice_of(n4, a.world, a.rank, &lo, &hi);
+  float* const master = a.master[a.rank];
   for (long long i0 = lo + tid; i0 < hi; i0 += nthr * U) {
-    float4 s[U][2];
+    float4 s[U], p[U], m[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long i = i0 + u * nthr;
-      const float* src = n.mc_grad + (base8 + (i < hi ? i : lo)) * 8;
-      s[u][0] = multimem_ld_reduce_add(src);
-      s[u][1] = multimem_ld_reduce_add(src + 4);
+      const long long e = (base4 + (i < hi ? i : lo)) * 4;        // clamp: a harmless in-range re-read
+      s[u] = multimem_ld_reduce_add(n.mc_grad + e);
+      p[u] = *reinterpret_cast<const float4*>(master + e);
+      m[u] = *reinterpret_cast<const float4*>(a.mom + e);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long i = i0 + u * nthr;
       if (i >= hi) break;
-      const long long e = (base8 + i) * 8;
-      float* mp = a.master[a.rank] + e;
-      float4 p0 = *reinterpret_cast<const float4*>(mp), p1 = *reinterpret_cast<const float4*>(mp + 4);
-      float4 m0 = *reinterpret_cast<const float4*>(a.mom + e), m1 = *reinterpret_cast<const float4*>(a.mom + e + 4);
-      sgd_update(s[u][0], p0, m0, inv_w, a.lr, a.momentum, a.wd);
-      sgd_update(s[u][1], p1, m1, inv_w, a.lr, a.momentum, a.wd);
-      *reinterpret_cast<float4*>(a.mom + e) = m0;
-      *reinterpret_cast<float4*>(a.mom + e + 4) = m1;
+      const long long e = (base4 + i) * 4;
+      sgd_update(s[u], p[u], m[u], inv_w, a.lr, a.momentum, a.wd);
+      *reinterpret_cast<float4*>(a.mom + e) = m[u];
+      const uint2 sh = make_uint2(pack_bf16x2(p[u].x, p[u].y), pack_bf16x2(p[u].z, p[u].w));
       if (n.one_shot) {
         // every rank computed the same update from the same switch-reduced sum: purely local stores
-        *reinterpret_cast<float4*>(mp) = p0;
-        *reinterpret_cast<float4*>(mp + 4) = p1;
-        if (a.shadow[a.rank]) *reinterpret_cast<uint4*>(a.shadow[a.rank] + e) = pack8(p0, p1);
+        *reinterpret_cast<float4*>(master + e) = p[u];
+        if (a.shadow[a.rank]) *reinterpret_cast<uint2*>(a.shadow[a.rank] + e) = sh;
         continue;
       }
-      if (n.mc_shadow != nullptr && is_sharded(a, e)) {
-        *reinterpret_cast<float4*>(mp) = p0;
-        *reinterpret_cast<float4*>(mp + 4) = p1;
-      } else {
-        multimem_st(n.mc_master + e, p0);
-        multimem_st(n.mc_master + e + 4, p1);
-      }
-      if (n.mc_shadow) multimem_st_bf16x8(n.mc_shadow + e, pack8(p0, p1));
+      if (n.mc_shadow != nullptr && is_sharded(a, e)) *reinterpret_cast<float4*>(master + e) = p[u];
+      else multimem_st(n.mc_master + e, p[u]);
+      if (n.mc_shadow) multimem_st_bf16x4(n.mc_shadow + e, sh);
     }
   }
   if (!a.skip_exit_barrier) cta_barrier_all_ranks(a, 1);
   ktrace_end(a.kflags);
+}
+
+// Diagnostic: how fast can this GPU READ a buffer (peer memory, or the switch-reduced multicast view) with
+// a given CTA shape?  kind 0 = plain 16-byte loads, 1 = ld.relaxed.sys (what the sync kernels use), 2 =
+// multimem.ld_reduce.  Every thread keeps U loads in flight and folds the values into one float so that
+// nothing is optimised away.  tools/peer_read_probe.py; no reference counterpart.
+template <int U>
+__global__ void __launch_bounds__(512)
+peer_read_probe_kernel(const float* __restrict__ src, float* __restrict__ sink, long long n8, int kind, bf16* dst,
+                       float* local_rw) {
+  // unit = 8 floats: two 16-byte loads; kinds >= 3 also store the 8 values as bf16 (16 bytes) to dst:
+  // 3 = multimem.ld_reduce + multimem.st, 4 = ld.relaxed.sys + st.relaxed.sys, 5 = kind 3 plus the optimizer's
+  // local traffic (read 64 B, write 64 B per unit), 6 = kind 3 without any load (stores only)
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long nthr = (long long)gridDim.x * blockDim.x;
+  float acc = 0.f;
+  for (long long i0 = tid; i0 < n8; i0 += nthr * U) {
+    float4 v[U][2], w[U][2];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * nthr;
+      const float* p = src + (i < n8 ? i : tid) * 8;
+      if (kind == 0) { v[u][0] = *reinterpret_cast<const float4*>(p); v[u][1] = *reinterpret_cast<const float4*>(p + 4); }
+      else if (kind == 1 || kind == 4) { v[u][0] = ld_peer(p); v[u][1] = ld_peer(p + 4); }
+      else if (kind == 6) { v[u][0] = v[u][1] = make_float4(1.f, 2.f, 3.f, 4.f); }
+      else { v[u][0] = multimem_ld_reduce_add(p); v[u][1] = multimem_ld_reduce_add(p + 4); }
+      if (kind == 5) {
+        const float* q = local_rw + (i < n8 ? i : tid) * 16;
+        w[u][0] = *reinterpret_cast<const float4*>(q); w[u][1] = *reinterpret_cast<const float4*>(q + 4);
+        const float4 w2 = *reinterpret_cast<const float4*>(q + 8), w3 = *reinterpret_cast<const float4*>(q + 12);
+        w[u][0].x += w2.x; w[u][1].x += w3.x;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * nthr;
+      acc += v[u][0].x + v[u][1].w;
+      if (kind >= 3 && i < n8) {
+        const uint4 pk = pack8(v[u][0], v[u][1]);
+        if (kind == 4) st_peer_u4(dst + i * 8, pk);
+        else multimem_st_bf16x8(dst + i * 8, pk);
+        if (kind == 5) {
+          float* q = local_rw + i * 16;
+          w[u][0].x += v[u][0].x; w[u][1].y += v[u][1].y;
+          *reinterpret_cast<float4*>(q) = w[u][0]; *reinterpret_cast<float4*>(q + 4) = w[u][1];
+          *reinterpret_cast<float4*>(q + 8) = w[u][1]; *reinterpret_cast<float4*>(q + 12) = w[u][0];
+        }
+      }
+    }
+  }
+  if (acc == 123.456f) sink[tid] = acc;
 }
 
 // ---- host side -----------------------------------------------------------------------------
@@ -427,9 +473,14 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
   memset(&a, 0, sizeof(a));
   int rc = fill_common(a, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
   if (rc) return rc;
-  if (blocks <= 0) {
-    long long want = (n / 8 + 512 * 4 - 1) / (512 * 4);
-    blocks = (int)(want < 1 ? 1 : (want > 32 ? 32 : want));
+  // blocks = 0: the lean shape (128 threads, at most one CTA per SM) that runs next to the backward kernels;
+  // blocks > 0: the caller owns the GPU and gets 512-thread CTAs with two units in flight per thread
+  const bool lean = blocks <= 0;
+  if (lean) {
+    const long long per_rank = n / 4 / ((mode & ~DDPB_P2P_NO_EXIT_BARRIER) == DDPB_P2P_TWOSHOT ? world : 1);
+    long long want = (per_rank + 128 * 8 - 1) / (128 * 8);          // >= 2 iterations of 4 units per thread before adding CTAs
+    const int cap = sm_count() < P2P_MAX_BLOCKS ? sm_count() : P2P_MAX_BLOCKS;
+    blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
   }
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "p2p: at most %d blocks", P2P_MAX_BLOCKS);
   for (int r = 0; r < world; ++r) {
@@ -440,14 +491,20 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
   a.skip_exit_barrier = (mode & DDPB_P2P_NO_EXIT_BARRIER) ? 1 : 0;
   a.kflags = kernel_flags(stream, 0);
   mode &= ~DDPB_P2P_NO_EXIT_BARRIER;
+#define DDPB_P2P_LAUNCH(M)                                                          \
+  do {                                                                              \
+    if (lean) p2p_kernel<M, 4, 128><<<blocks, 128, 0, stream>>>(a);                 \
+    else p2p_kernel<M, 4, 512><<<blocks, 512, 0, stream>>>(a);                      \
+  } while (0)
   switch (mode) {
-    case DDPB_P2P_ONESHOT: p2p_kernel<MODE_ONESHOT><<<blocks, 512, 0, stream>>>(a); break;
-    case DDPB_P2P_TWOSHOT: p2p_kernel<MODE_TWOSHOT><<<blocks, 512, 0, stream>>>(a); break;
-    case DDPB_P2P_ROOT: p2p_kernel<MODE_ROOT><<<blocks, 512, 0, stream>>>(a); break;
-    case DDPB_P2P_BCAST: p2p_kernel<MODE_BCAST><<<blocks, 512, 0, stream>>>(a); break;
-    case DDPB_P2P_ALLGATHER: p2p_kernel<MODE_ALLGATHER><<<blocks, 512, 0, stream>>>(a); break;
+    case DDPB_P2P_ONESHOT: DDPB_P2P_LAUNCH(MODE_ONESHOT); break;
+    case DDPB_P2P_TWOSHOT: DDPB_P2P_LAUNCH(MODE_TWOSHOT); break;
+    case DDPB_P2P_ROOT: DDPB_P2P_LAUNCH(MODE_ROOT); break;
+    case DDPB_P2P_BCAST: DDPB_P2P_LAUNCH(MODE_BCAST); break;
+    case DDPB_P2P_ALLGATHER: DDPB_P2P_LAUNCH(MODE_ALLGATHER); break;
     default: DDPB_REQUIRE(false, "p2p: unknown mode %d", mode);
   }
+#undef DDPB_P2P_LAUNCH
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -480,22 +537,18 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   memset(&a, 0, sizeof(a));
   int rc = fill_common(a.base, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
   if (rc) return rc;
-  // CTA shape of the NVLS kernel when it runs next to the backward kernels (DDPB_NVLS_THREADS / DDPB_NVLS_MAX_BLOCKS)
-  static int threads = 0, cap = 0, unroll = 0;
-  if (!threads) {
-    const char* u = getenv("DDPB_NVLS_UNROLL");
-    unroll = u ? atoi(u) : 4;
-    if (unroll != 1 && unroll != 2 && unroll != 4) unroll = 4;
-    const char* t = getenv("DDPB_NVLS_THREADS");
-    threads = t ? atoi(t) : 256;
-    if (threads != 128 && threads != 256 && threads != 512) threads = 256;
+  // blocks = 0: the lean shape that runs next to the backward kernels, at most one CTA per SM
+  // (DDPB_NVLS_MAX_BLOCKS overrides the cap); blocks > 0: the caller owns the GPU and gets the fat shape.
+  static int cap = 0;
+  if (!cap) {
     const char* c = getenv("DDPB_NVLS_MAX_BLOCKS");
-    cap = c ? atoi(c) : 32;
-    if (cap < 1 || cap > P2P_MAX_BLOCKS) cap = 32;
+    cap = c ? atoi(c) : sm_count();
+    if (cap < 1 || cap > P2P_MAX_BLOCKS) cap = sm_count() < P2P_MAX_BLOCKS ? sm_count() : P2P_MAX_BLOCKS;
   }
-  const long long units = n / 8 / (mode == DDPB_P2P_ONESHOT ? 1 : world);
-  if (blocks <= 0) {
-    long long want = (units + threads * 4 - 1) / (threads * 4);
+  const bool lean = blocks <= 0;
+  const long long units = n / 4 / (mode == DDPB_P2P_ONESHOT ? 1 : world);
+  if (lean) {
+    long long want = (units + 128 * 8 - 1) / (128 * 8);          // >= 2 iterations of 4 units per thread before adding CTAs
     blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
   }
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "nvls: at most %d blocks", P2P_MAX_BLOCKS);
@@ -505,11 +558,8 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
   a.one_shot = mode == DDPB_P2P_ONESHOT ? 1 : 0;
   a.base.kflags = kernel_flags(stream, 0);
-  // loads in flight per thread: 2U x 16 bytes; small ranges take the low-register variant
-  const bool big = units >= (long long)blocks * threads * 4;
-  if (big && unroll == 4) p2p_nvls_kernel<4><<<blocks, threads, 0, stream>>>(a);
-  else if (big && unroll == 2) p2p_nvls_kernel<2><<<blocks, threads, 0, stream>>>(a);
-  else p2p_nvls_kernel<1><<<blocks, threads, 0, stream>>>(a);
+  if (lean) p2p_nvls_kernel<4, 128><<<blocks, 128, 0, stream>>>(a);
+  else p2p_nvls_kernel<4, 512><<<blocks, 512, 0, stream>>>(a);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -521,6 +571,25 @@ extern "C" int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shado
   return ddpb_p2p_sync_nvls_sharded(DDPB_P2P_TWOSHOT, mc_grad, mc_master, mc_shadow, master_local, nullptr, flags, mom,
                                     epochs, rank, world, slot, off, n, lr, momentum, wd, blocks, skip_exit_barrier,
                                     nullptr, 0, stream);
+}
+
+extern "C" int ddpb_probe_peer_read(const void* src, void* sink, long long n_floats, int kind, int blocks, int threads,
+                                    int unroll, void* dst_bf16, float* local_rw, cudaStream_t stream) {
+  DDPB_REQUIRE(src && sink && n_floats % 8 == 0 && blocks > 0 && threads > 0 && threads <= 512, "peer_read_probe: bad argument");
+  DDPB_REQUIRE(kind < 3 || dst_bf16, "peer_read_probe: kinds >= 3 need a destination");
+  DDPB_REQUIRE(kind != 5 || local_rw, "peer_read_probe: kind 5 needs a local read/write buffer of 2 * n floats");
+  const long long n8 = n_floats / 8;
+#define DDPB_PROBE(UU) peer_read_probe_kernel<UU><<<blocks, threads, 0, stream>>>((const float*)src, (float*)sink, n8, kind, (bf16*)dst_bf16, local_rw)
+  switch (unroll) {
+    case 1: DDPB_PROBE(1); break;
+    case 2: DDPB_PROBE(2); break;
+    case 4: DDPB_PROBE(4); break;
+    case 8: DDPB_PROBE(8); break;
+    default: DDPB_REQUIRE(false, "peer_read_probe: unroll must be 1, 2, 4 or 8");
+  }
+#undef DDPB_PROBE
+  DDPB_LAUNCH_CHECK();
+  return DDPB_OK;
 }
 
 // The record a timed-out cross-rank wait leaves behind (rec[0] = 1 when present, then rank, peer, slot,

@@ -466,9 +466,7 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   // done reading our gradients and that all their weight pushes into our arena have landed.
   const bool last = bi + 1 == (int)e->buckets.size();
   const int mode = b.mode | (last ? 0 : DDPB_P2P_NO_EXIT_BARRIER);
-  // enough CTAs to keep ~16 B x 8 loads per thread in flight on big buckets, few on small ones
-  long long want = (b.numel / 4 + 512 * 4 - 1) / (512 * 4);
-  const int blocks = (int)(want < 1 ? 1 : (want > 64 ? 64 : want));     // it runs next to the backward kernels
+  const int blocks = 0;     // the launcher's lean shape: it runs next to the backward kernels
   const long long* sh_tab = e->shard.empty() ? nullptr : e->shard.data();
   const int n_sh = (int)e->shard.size() / 2;
   if (e->mc_arena && (b.mode == DDPB_P2P_TWOSHOT || e->nvls_oneshot)) {

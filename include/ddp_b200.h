@@ -235,6 +235,12 @@ int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_master, void* m
  * No reference counterpart (the reference blocks forever inside gloo when a rank dies). */
 int ddpb_p2p_last_timeout(unsigned int* rec8);
 
+/* Diagnostic (tools/peer_read_probe.py): read bandwidth of `src` (local, peer or multicast memory) with a
+ * given CTA shape; kind 0 plain loads, 1 ld.relaxed.sys, 2 multimem.ld_reduce, 3-6 with bf16 stores / local
+ * optimizer traffic added (see sync_p2p.cu).  No reference counterpart. */
+int ddpb_probe_peer_read(const void* src, void* sink, long long n_floats, int kind, int blocks, int threads, int unroll,
+                         void* dst_bf16, float* local_rw, cudaStream_t stream);
+
 /* Virtual-memory-management arena with an NVSwitch multicast mapping (csrc/runtime/vmm_arena.cpp).
  * ddpb_vmm_alloc ALLOCATES (cuMemCreate); fds are POSIX file descriptors to pass between processes. */
 int ddpb_vmm_supported(int* multicast_supported);

@@ -71,7 +71,7 @@ def main():
             shard = [0, n] if two else None
             blocks = big_grid if size >= (4 << 20) else 0
             t_p2p = timed(lambda: arena.sync(nv.P2P_TWOSHOT if two else nv.P2P_ONESHOT, 0, n, 0.1, 0.9, 1e-4,
-                                             blocks=min(blocks, 64), shard=shard), iters, world)
+                                             blocks=blocks, shard=shard), iters, world)
             t_nvls = timed(lambda: arena.sync_nvls(0, n, 0.1, 0.9, 1e-4, blocks=blocks, shard=shard, one_shot=not two),
                            iters, world) if has_nvls else float("nan")
             t_nccl = timed(lambda: dist.all_reduce(flat[:n]), iters, world)
