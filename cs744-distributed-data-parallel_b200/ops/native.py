@@ -16,7 +16,7 @@ import torch
 
 F32, BF16 = 0, 1
 P2P_ONESHOT, P2P_TWOSHOT, P2P_ROOT, P2P_BCAST, P2P_ALLGATHER = range(5)
-MAX_RANKS, P2P_MAX_BLOCKS, P2P_MAX_SLOTS = 8, 160, 64
+MAX_RANKS, P2P_MAX_BLOCKS, P2P_MAX_SLOTS = 8, 320, 64
 
 _PKG = pathlib.Path(__file__).resolve().parent.parent
 LIB_PATH = _PKG / "_native" / "libddpb200.so"

@@ -85,11 +85,20 @@ __device__ __forceinline__ int tile_swizzle(int row) {
 // cluster (blockIdx.z) each accumulate 1/KS of the K range of the SAME tile; then every CTA sends the
 // other CTAs' column blocks of its fp32 partial tile through distributed shared memory and finishes
 // BN/KS columns itself (reduce-scatter), so the epilogue work is split KS ways too.
-template <int BN, int STAGES, bool DGRAD, int NC, int KS>
+//
+// PAIR (cta_group::2): two CTAs with consecutive pixel tiles (cluster ranks 2k, 2k+1, the two SMs of a TPC)
+// form ONE tcgen05.mma of M = 256: each loads its own 128-pixel A tile and only HALF of the weight tile,
+// the leader issues the MMAs, which read both CTAs' shared memory and write each CTA's 128 x BN accumulator
+// into that CTA's TMEM.  Per byte brought in from L2 a CTA performs 2x (BN = 256) the MMA work of the
+// single-CTA 128 x 128 tile - and these kernels are bound by L2 -> SM traffic, not by the tensor pipe.
+// PAIR combines with KS (cluster = 2 x KS CTAs) so that layers with few pixel tiles still fill the GPU.
+template <int BN, int STAGES, bool DGRAD, int NC, int KS, bool PAIR>
 __global__ void __launch_bounds__(192)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const float* __restrict__ bias, float* __restrict__ stats, const ConvTcParams prm) {
-  constexpr int B_BYTES = BN * KCHUNK * 2;
+  static_assert(!PAIR || NC == 1, "pair tiles do not combine with the activation-multicast clusters");
+  constexpr int BH = PAIR ? BN / 2 : BN;             // weight-tile channels held by THIS CTA
+  constexpr int B_BYTES = BH * KCHUNK * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle (TMA and UMMA agree on address bits)
@@ -112,6 +121,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   else { n0 = m_tile * prm.imgs_per_tile; h0 = 0; }
   const int k_total = prm.taps * prm.k_chunks;
   const int ks_rank = KS > 1 ? (int)blockIdx.z : 0;
+  const int pr = PAIR ? (int)(cluster_rank() & 1u) : 0;        // rank inside the pair; 0 = leader
+  // cluster ranks of this CTA's pair (bits of the commit multicast mask) and of its split-K partners
+  const uint16_t pair_mask = PAIR ? (uint16_t)(3u << (2 * ks_rank)) : (uint16_t)0;
   const int it_lo = KS > 1 ? k_total * ks_rank / KS : 0;
   const int k_iters = (KS > 1 ? k_total * (ks_rank + 1) / KS : k_total) - it_lo;
 
@@ -119,11 +131,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     // a stage is written by all NC CTAs (multicast slices), so it is free only when all NC have consumed it
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], NC); }
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], NC); }   // (pair: the leader's full barrier counts both CTAs' bytes)
     mbar_init(accum_bar, 1);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<BN>(tmem_slot);
+  if (warp == 1) { if (PAIR) tmem2_alloc<BN>(tmem_slot); else tmem_alloc<BN>(tmem_slot); }
   // everything above is private to this CTA and overlaps the previous kernel's tail (programmatic
   // dependent launch); global memory may only be touched after pdl_wait()
   if (prm.pdl & 1) pdl_launch_dependents();
@@ -133,11 +145,14 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (!DGRAD) for (int i = threadIdx.x; i < BN; i += blockDim.x) bias_s[i] = bias ? ld_coh(&bias[n_tile * BN + i]) : 0.f;
   tc_fence_before();
   __syncthreads();
-  if (NC > 1) cluster_barrier();      // every CTA's barriers exist before a peer's multicast can touch them
+  if (NC > 1 || PAIR) cluster_barrier();      // every CTA's barriers exist before a peer's loads / commits can touch them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint16_t MC_MASK = (uint16_t)((1u << NC) - 1);
-  uint4 ywin[BN / KS / 8];               // dgrad + fused BN reduction only (epilogue warps)
+  // dgrad + fused BN reduction only (epilogue warps): this thread's share of the winner tensor, fetched ahead
+  // of the accumulator when it fits in registers (up to 16 x 16 bytes), else loaded where it is used
+  constexpr bool WIN_PREFETCH = BN / KS / 8 <= 16;
+  uint4 ywin[WIN_PREFETCH ? BN / KS / 8 : 1];
   float bn_mu[8], bn_is[8], bn_sc[8], bn_sh[8];   // its per-channel BatchNorm constants, fetched up front as well
 
   if (warp == 0) {
@@ -150,9 +165,25 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int r = prm.taps == 1 ? 1 : tap / 3, s = prm.taps == 1 ? 1 : tap % 3;
         uint8_t* sa = smem + stage * STAGE_BYTES;
         uint8_t* sb = sa + A_BYTES;
-        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+        if (!PAIR) mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+        else if (pr == 0) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
         // fprop reads X at p + (r-1, s-1); dgrad reads dY at p - (r-1, s-1)
         const int dh = DGRAD ? 1 - r : r - 1, dw = DGRAD ? 1 - s : s - 1;
+        if (PAIR) {
+          // both CTAs load into their own shared memory; the bytes are counted on the LEADER's barrier, which
+          // is what the one MMA-issuing thread waits for
+          const uint32_t lbar = pair_leader_bar(&full_bar[stage]);
+          tma2_load_4d(sa, &tmA, lbar, kc * KCHUNK, dw, h0 + dh, n0);
+          if (!DGRAD) {
+            tma2_load_2d(sb, &tmB, lbar, tap * prm.k_total_cols + kc * KCHUNK, n_tile * BN + pr * BH);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BH / 64; ++j)
+              tma2_load_2d(sb + j * (64 * 128), &tmB, lbar, tap * prm.k_total_cols + n_tile * BN + pr * BH + j * 64,
+                           kc * KCHUNK);
+          }
+          continue;
+        }
         if (NC == 1) {
           tma_load_4d(sa, &tmA, &full_bar[stage], kc * KCHUNK, dw, h0 + dh, n0);
         } else {
@@ -176,8 +207,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(TILE_M, BN, false, DGRAD);
+    if (lane == 0 && pr == 0) {         // (pair: the leader's thread drives both SMs)
+      constexpr uint32_t idesc = umma_idesc_bf16(PAIR ? 2 * TILE_M : TILE_M, BN, false, DGRAD);
       for (int it = 0; it < k_iters; ++it) {
         const int stage = it % STAGES, use = it / STAGES;
         mbar_wait(&full_bar[stage], use & 1);
@@ -192,12 +223,16 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           // dgrad B is MN-major: 16 K-rows = 2048 bytes; 64-wide N blocks are 8192 B apart (LBO)
           const uint64_t db = DGRAD ? umma_desc(sb + kk * 2048, 64 * 128, 1024)
                                     : umma_desc(sb + kk * 32, 16, 1024);
-          umma_bf16(tmem_base, da, db, idesc, (it | kk) != 0);
+          if (PAIR) umma2_bf16(tmem_base, da, db, idesc, (it | kk) != 0);
+          else umma_bf16(tmem_base, da, db, idesc, (it | kk) != 0);
         }
-        // frees the stage when these MMAs have read it (in every CTA that multicasts into it)
-        if (NC == 1) umma_commit(&empty_bar[stage]); else umma_commit_mc(&empty_bar[stage], MC_MASK);
+        // frees the stage when these MMAs have read it (in every CTA that multicasts into it / in both CTAs of a pair)
+        if (PAIR) umma2_commit_mc(&empty_bar[stage], pair_mask);
+        else if (NC == 1) umma_commit(&empty_bar[stage]);
+        else umma_commit_mc(&empty_bar[stage], MC_MASK);
       }
-      umma_commit(accum_bar);                  // accumulator complete
+      if (PAIR) umma2_commit_mc(accum_bar, pair_mask);       // accumulator complete, in both CTAs
+      else umma_commit(accum_bar);
       if (trc) trc[3] = global_timer_ns();                             // last MMA issued
     }
   } else {
@@ -212,7 +247,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       ld_coh_vec<8>(prm.bn_gamma + col, bn_sc);
       ld_coh_vec<8>(prm.bn_beta + col, bn_sh);
 #pragma unroll
-      for (int k = 0; k < BN / KS / 8; ++k) {
+      for (int k = 0; k < (WIN_PREFETCH ? BN / KS / 8 : 0); ++k) {
         const long long grow = (long long)m_tile * TILE_M + t2 / (BN / KS / 8) + k * (128 / (BN / KS / 8));
         ywin[k] = grow < prm.total_pixels
                       ? DDPB_LD_COH(reinterpret_cast<const uint4*>(prm.bn_y + grow * prm.n_out + col))
@@ -238,7 +273,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   constexpr int RP = 128;                     // receive buffer: [sender][column][row] fp32 (column-major: conflict-free)
   float* recv = reinterpret_cast<float*>(smem);
   uint8_t* tile = smem + (KS - 1) * CW * RP * 4;                        // [128 rows][CW] bf16
-  float* red = reinterpret_cast<float*>(tile + TILE_M * CW * 2);         // [PARTS][2 * CW]
+  // [PARTS][2 * CW]; with split-K it reuses the receive area, which is dead once step 1 below has run
+  float* red = KS > 1 ? recv : reinterpret_cast<float*>(tile + TILE_M * CW * 2);
   const int q = warp & 3, row = q * 32 + lane, t = threadIdx.x - 64;
   const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
   if constexpr (KS > 1) {
@@ -250,7 +286,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int d = 0; d < KS; ++d) {
         if (d == ks_rank) continue;
         const int slot = ks_rank < d ? ks_rank : ks_rank - 1;
-        const uint32_t remote = cluster_map_shared(smem_u32(recv + slot * CW * RP), (uint32_t)d);
+        const uint32_t remote = cluster_map_shared(smem_u32(recv + slot * CW * RP), (uint32_t)(PAIR ? 2 * d + pr : d));
 #pragma unroll 1
         for (int c = 0; c < CW; c += 16) {
           float v[16];
@@ -322,7 +358,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (bn_red) {
         // yw: the previous block's conv output behind this pixel (NaN: ReLU blocked it -> z > 0 is false)
         float v[8];
-        { const uint4 w4 = ywin[k];
+        { const uint4 w4 = WIN_PREFETCH ? ywin[WIN_PREFETCH ? k : 0]
+                                        : DDPB_LD_COH(reinterpret_cast<const uint4*>(prm.bn_y + grow * prm.n_out + col0));
           const float2 a = unpack_bf16x2(w4.x), b = unpack_bf16x2(w4.y), c2 = unpack_bf16x2(w4.z), e = unpack_bf16x2(w4.w);
           v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c2.x; v[5] = c2.y; v[6] = e.x; v[7] = e.y; }
 #pragma unroll
@@ -429,14 +466,16 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
-  if (NC > 1) cluster_barrier();      // peers may still arrive on our barriers: do not exit before them
-  if (warp == 1) tmem_dealloc<BN>(tmem_base);
+  if (NC > 1 || PAIR) cluster_barrier();      // peers may still arrive on our barriers / read our shared memory through the pair MMA
+  if (warp == 1) { if (PAIR) tmem2_dealloc<BN>(tmem_base); else tmem_dealloc<BN>(tmem_base); }
   ktrace_end(prm.pdl);
   if (trc && threadIdx.x == 0) trc[7] = global_timer_ns();            // CTA done
 }
 
-template <int BN, int STAGES>
-constexpr int conv_tc_smem() { return STAGES * (A_BYTES + BN * KCHUNK * 2) + (2 * STAGES + 1) * 8 + 16 + BN * 4 + 1024; }
+template <int BN, int STAGES, bool PAIR = false>
+constexpr int conv_tc_smem() {
+  return STAGES * (A_BYTES + (PAIR ? BN / 2 : BN) * KCHUNK * 2) + (2 * STAGES + 1) * 8 + 16 + BN * 4 + 1024;
+}
 
 // pixel box (w, h, n) holding `pixels` (128 or 64) consecutive NHWC pixels of an HxW image
 void pixel_box(int H, int W, int pixels, int* bw, int* bh, int* bn) {
@@ -472,7 +511,7 @@ struct ConvExtra {
 };
 static const ConvExtra kNoExtra;
 
-template <int BN, int STAGES, bool DGRAD, int NC = 1, int KS = 1>
+template <int BN, int STAGES, bool DGRAD, int NC = 1, int KS = 1, bool PAIR = false>
 static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, float* stats, int B, int H, int W,
                   int Cin, int Cout, cudaStream_t stream, const ConvExtra& ex = kNoExtra, int taps = 9) {
   const int Kc = DGRAD ? Cout : Cin;     // reduction channels
@@ -502,7 +541,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   int rc = make_tmap_nhwc_bf16(&tmA, in, B, H, W, Kc, KCHUNK, bw, sbh, sbn);
   if (rc) return rc;
   // weight matrix [Cout rows][9*Cin cols]; fprop box = 64 cols x BN rows, dgrad box = 64 cols x 64 rows
-  rc = make_tmap_2d_bf16(&tmB, w, Cout, (long long)taps * Cin, KCHUNK, DGRAD ? 64 : BN);
+  rc = make_tmap_2d_bf16(&tmB, w, Cout, (long long)taps * Cin, KCHUNK, DGRAD ? 64 : (PAIR ? BN / 2 : BN));
   if (rc) return rc;
   prm.H = H; prm.W = W;
   prm.tiles_per_img = H * W >= TILE_M ? H * W / TILE_M : 0;
@@ -526,12 +565,16 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
   prm.bn_sums = br.sums;
   prm.bnf_out = nullptr;
   static_assert(KS == 1 || NC == 1, "split-K and multicast clusters are separate variants");
-  static_assert((KS - 1) * (BN / KS) * 128 * 4 + TILE_M * (BN / KS) * 2 + TILE_M * 2 * 8 * 4 <= STAGES * (A_BYTES + BN * KCHUNK * 2),
+  // epilogue buffers live in the pipeline stages: split-K receive area + bf16 tile (+ the partial sums, which
+  // reuse the receive area when there is one)
+  static_assert((KS - 1) * (BN / KS) * 128 * 4 + TILE_M * (BN / KS) * 2 + (KS > 1 ? 0 : TILE_M * 2 * 8 * 4) <=
+                    STAGES * (A_BYTES + (PAIR ? BN / 2 : BN) * KCHUNK * 2),
                 "epilogue buffers (split-K receive area, bf16 tile, partial sums) must fit in the pipeline stages");
   int m_tiles = prm.tiles_per_img > 0 ? B * prm.tiles_per_img : ceil_div(B, prm.imgs_per_tile);
+  if (PAIR) m_tiles = (m_tiles + 1) & ~1;        // pairs; a surplus tile lies wholly out of range (zero-filled loads, no stores)
   dim3 grid(m_tiles, Nc / BN, KS);
-  constexpr int smem = conv_tc_smem<BN, STAGES>();
-  auto kern = conv3x3_tc_kernel<BN, STAGES, DGRAD, NC, KS>;
+  constexpr int smem = conv_tc_smem<BN, STAGES, PAIR>();
+  auto kern = conv3x3_tc_kernel<BN, STAGES, DGRAD, NC, KS, PAIR>;
   static unsigned long long configured = 0;
   if (first_on_device(&configured)) {
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -539,7 +582,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     // occupancy query below reports that)
     DDPB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   }
-  if (!DGRAD && ex.bnfwd && ex.bnfwd->out && stats) {
+  if (!DGRAD && !PAIR && ex.bnfwd && ex.bnfwd->out && stats) {
     BnFwdArgs& g_bnfwd = *ex.bnfwd;
     // the fused BatchNorm needs a grid-wide barrier: only when every CTA is resident at the same time
     static int capacity = -1;
@@ -577,7 +620,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
     }
   }
   prm.pdl = kernel_flags(stream, 1);
-  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(1, NC, KS), 1, tmA, tmB, bias, stats, prm));
+  DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(PAIR ? 2 : 1, NC, KS), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
@@ -591,7 +634,8 @@ static long long cta_count(int B, int H, int W, int n_channels, int tile_n) {
 int launch_conv_tc2(bool dgrad, int bn, const void* in, const void* w, void* out, const float* bias, float* stats,
                     int B, int H, int W, int Cin, int Cout, cudaStream_t stream);
 
-// tile_n codes: 4264 / 4464 / 4228 / 4428 = cluster split-K (2 or 4 CTAs per 64- or 128-channel tile);
+// tile_n codes: 61128 / 61256 / 62128 / 62256 = CTA pairs (cta_group::2) with 128 / 256 channels per pair tile,
+// without / with 2-way cluster split-K (this file); 4264 / 4464 / 4228 / 4428 = cluster split-K (2 or 4 CTAs per 64- or 128-channel tile);
 // 64 / 128 = one CTA per tile; 1864 / 1464 / 1264 = 64-channel tiles in clusters of 8 / 4 / 2
 // CTAs that multicast the activation tile, 1228 = 128-channel tiles in clusters of 2; 2128 / 2256 = CTA
 // pair (cta_group::2) with 128 / 256 channels per tile; 0 = automatic.  DDPB_CONV_2CTA=1 in the environment lets the automatic choice use pair tiles.
@@ -646,6 +690,16 @@ static int dispatch(const void* in_v, const void* w_v, void* out_v, const float*
   const bf16 *in = (const bf16*)in_v, *w = (const bf16*)w_v;
   bf16* out = (bf16*)out_v;
 #define DDPB_CONV(BN_, ST_, NC_, KS_) launch<BN_, ST_, DGRAD, NC_, KS_>(in, w, out, bias, stats, B, H, W, Cin, Cout, stream, ex)
+  if (tile_n > 60000) {         // 6<splits><tile>: CTA pairs (cta_group::2), optionally with cluster split-K
+    const int bn = tile_n % 1000, ks = (tile_n / 1000) % 10;
+    DDPB_REQUIRE((bn == 128 || bn == 256) && (ks == 1 || ks == 2), "%s: unknown pair tile code %d", what, tile_n);
+    DDPB_REQUIRE(n_ch % bn == 0, "%s: %d channels are not a multiple of pair tile %d", what, n_ch, bn);
+    DDPB_REQUIRE(!(ex.bnfwd && ex.bnfwd->out), "%s: pair tiles have no fused BatchNorm forward", what);
+#define DDPB_CONVP(BN_, ST_, KS_) launch<BN_, ST_, DGRAD, 1, KS_, true>(in, w, out, bias, stats, B, H, W, Cin, Cout, stream, ex)
+    if (bn == 128) return ks == 1 ? DDPB_CONVP(128, 4, 1) : DDPB_CONVP(128, 4, 2);
+    return ks == 1 ? DDPB_CONVP(256, 3, 1) : DDPB_CONVP(256, 3, 2);
+#undef DDPB_CONVP
+  }
   if (tile_n > 2000 && tile_n < 4000) {
     DDPB_REQUIRE(n_ch % (tile_n - 2000) == 0, "%s: %d channels are not a multiple of pair tile %d", what, n_ch, tile_n - 2000);
     DDPB_REQUIRE(!(ex.bnred && ex.bnred->y) && !(ex.bnfwd && ex.bnfwd->out),
@@ -736,7 +790,7 @@ extern "C" int ddpb_conv3x3_dgrad_bnred_tc(const void* dy, const void* w_bf16, v
                                            const float* invstd, const float* gamma, const float* beta, float* sums,
                                            cudaStream_t stream) {
   DDPB_REQUIRE(y_win && mean && invstd && gamma && beta && sums, "dgrad_bnred: null BatchNorm argument");
-  DDPB_REQUIRE(tile_n < 2000 || tile_n > 4000, "dgrad_bnred: pair tiles have no fused reduction");
+  DDPB_REQUIRE(tile_n < 2000 || tile_n > 4000, "dgrad_bnred: the conv_tc2.cu pair tiles (2128 / 2256) have no fused reduction");
   BnRedArgs br;
   br.y = y_win; br.mean = mean; br.invstd = invstd; br.gamma = gamma; br.beta = beta; br.sums = sums;
   ConvExtra ex;

@@ -172,7 +172,7 @@ enum { MODE_ONESHOT = 0, MODE_TWOSHOT = 1, MODE_ROOT = 2, MODE_BCAST = 3, MODE_A
 // The unit of work is one 16-byte access (4 elements) per thread with consecutive lanes on consecutive
 // addresses: a warp's load instruction covers 512 contiguous bytes.  (Two adjacent 16-byte loads per thread
 // - a 32-byte stride between lanes - ran at HALF the NVLink read rate: 360 instead of 690 GB/s, measured
-// with tools/peer_read_probe.py.)  Shapes as for the NVLS kernel below: THREADS = 128 runs next to the
+// with tools/peer_read_probe.py.)  Shapes as for the NVLS kernel below: THREADS = 64 runs next to the
 // backward kernels; THREADS = 512 is for a caller that owns the GPU.  U units are in flight per thread.
 template <int MODE, int U, int THREADS>
 __global__ void __launch_bounds__(THREADS)
@@ -300,9 +300,9 @@ struct NvlsArgs {
 
 // U units (one 16-byte access each, lanes contiguous) per thread and iteration.  ALL loads of an iteration -
 // the switch-reduced gradients and the local master weights and momentum - are issued before anything is
-// consumed, so one round trip covers them all.  Two shapes: THREADS = 128 is the one that runs next to the
-// backward kernels (under 10 K registers per CTA: it fits beside two convolution CTAs instead of evicting
-// one); THREADS = 512 is for a caller that owns the GPU (the bandwidth sweep).
+// consumed, so one round trip covers them all.  Two shapes: THREADS = 64 is the one that runs next to the
+// backward kernels (under 5 K registers per CTA, two per SM: they fit beside two convolution CTAs, whose
+// ~29 K registers each leave no room for anything bigger, instead of evicting one); THREADS = 512 is for a caller that owns the GPU (the bandwidth sweep).
 template <int U, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 p2p_nvls_kernel(const NvlsArgs n) {
@@ -418,6 +418,16 @@ static unsigned int* err_record() {
   return g_err_host;        // unified addressing: the host pointer is valid on the device
 }
 
+// threads per CTA of the in-step ("lean") shape: DDPB_SYNC_THREADS = 64 or 128 (default, measured faster)
+static int lean_threads() {
+  static int v = 0;
+  if (!v) {
+    const char* e = getenv("DDPB_SYNC_THREADS");
+    v = (e && atoi(e) == 64) ? 64 : 128;
+  }
+  return v;
+}
+
 static unsigned long long timeout_ns() {
   static unsigned long long v = 0;
   if (!v) {
@@ -478,8 +488,10 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
   const bool lean = blocks <= 0;
   if (lean) {
     const long long per_rank = n / 4 / ((mode & ~DDPB_P2P_NO_EXIT_BARRIER) == DDPB_P2P_TWOSHOT ? world : 1);
-    long long want = (per_rank + 128 * 8 - 1) / (128 * 8);          // >= 2 iterations of 4 units per thread before adding CTAs
-    const int cap = sm_count() < P2P_MAX_BLOCKS ? sm_count() : P2P_MAX_BLOCKS;
+    const int thr = lean_threads();
+    long long want = (per_rank + thr * 8 - 1) / (thr * 8);          // >= 2 iterations of 4 units per thread before adding CTAs
+    const int per_sm = thr == 64 ? 2 : 1;
+    const int cap = per_sm * sm_count() < P2P_MAX_BLOCKS ? per_sm * sm_count() : P2P_MAX_BLOCKS;
     blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
   }
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "p2p: at most %d blocks", P2P_MAX_BLOCKS);
@@ -493,7 +505,8 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
   mode &= ~DDPB_P2P_NO_EXIT_BARRIER;
 #define DDPB_P2P_LAUNCH(M)                                                          \
   do {                                                                              \
-    if (lean) p2p_kernel<M, 4, 128><<<blocks, 128, 0, stream>>>(a);                 \
+    if (lean && lean_threads() == 64) p2p_kernel<M, 4, 64><<<blocks, 64, 0, stream>>>(a);   \
+    else if (lean) p2p_kernel<M, 4, 128><<<blocks, 128, 0, stream>>>(a);            \
     else p2p_kernel<M, 4, 512><<<blocks, 512, 0, stream>>>(a);                      \
   } while (0)
   switch (mode) {
@@ -542,13 +555,14 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   static int cap = 0;
   if (!cap) {
     const char* c = getenv("DDPB_NVLS_MAX_BLOCKS");
-    cap = c ? atoi(c) : sm_count();
-    if (cap < 1 || cap > P2P_MAX_BLOCKS) cap = sm_count() < P2P_MAX_BLOCKS ? sm_count() : P2P_MAX_BLOCKS;
+    const int dflt = (lean_threads() == 64 ? 2 : 1) * sm_count();
+    cap = c ? atoi(c) : dflt;
+    if (cap < 1 || cap > P2P_MAX_BLOCKS) cap = dflt < P2P_MAX_BLOCKS ? dflt : P2P_MAX_BLOCKS;
   }
   const bool lean = blocks <= 0;
   const long long units = n / 4 / (mode == DDPB_P2P_ONESHOT ? 1 : world);
   if (lean) {
-    long long want = (units + 128 * 8 - 1) / (128 * 8);          // >= 2 iterations of 4 units per thread before adding CTAs
+    long long want = (units + lean_threads() * 8 - 1) / (lean_threads() * 8);      // >= 2 iterations of 4 units per thread
     blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
   }
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "nvls: at most %d blocks", P2P_MAX_BLOCKS);
@@ -558,7 +572,8 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
   a.one_shot = mode == DDPB_P2P_ONESHOT ? 1 : 0;
   a.base.kflags = kernel_flags(stream, 0);
-  if (lean) p2p_nvls_kernel<4, 128><<<blocks, 128, 0, stream>>>(a);
+  if (lean && lean_threads() == 64) p2p_nvls_kernel<4, 64><<<blocks, 64, 0, stream>>>(a);
+  else if (lean) p2p_nvls_kernel<4, 128><<<blocks, 128, 0, stream>>>(a);
   else p2p_nvls_kernel<4, 512><<<blocks, 512, 0, stream>>>(a);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;

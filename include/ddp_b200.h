@@ -22,7 +22,7 @@ extern "C" {
 #define DDPB_BF16 1
 
 #define DDPB_MAX_RANKS 8
-#define DDPB_P2P_MAX_BLOCKS 160
+#define DDPB_P2P_MAX_BLOCKS 320
 #define DDPB_P2P_MAX_SHARD_RANGES 24
 #define DDPB_P2P_MAX_SLOTS 64
 

@@ -163,6 +163,8 @@ def _tile_ok(code, channels, hw):
     """Can this tile code run a layer with `channels` output channels on hw x hw images?"""
     if code < 1000:
         return channels % code == 0
+    if code > 60000:          # CTA pairs: 6<splits><tile>
+        return channels % (code % 1000) == 0
     if code > 4000:           # cluster split-K: 4<splits><tile>
         return channels % (64 if code % 100 == 64 else 128) == 0
     if code > 2000:
@@ -174,7 +176,7 @@ def _tile_ok(code, channels, hw):
     return bn % nc == 0 or (bn == 1 and bh % nc == 0)
 
 
-TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256, 4264, 4464, 4228, 4428]
+TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256, 4264, 4464, 4228, 4428, 61128, 61256, 62128, 62256]
 
 TC_SHAPES = [  # (hw, cin, cout) of VGG-11 blocks 1..7
     (16, 64, 128), (8, 128, 256), (8, 256, 256), (4, 256, 512), (4, 512, 512), (2, 512, 512)]
@@ -249,7 +251,7 @@ def test_conv_tc_forward_fused_bn(F, R, b, hw, cin, cout, tile_n, pool):
 @pytest.mark.parametrize("b", [16, 10])
 @pytest.mark.parametrize("pool", [False, True])
 @pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
-@pytest.mark.parametrize("tile_n", [0, 64, 128, 1264, 4264, 4464, 4228, 4428])
+@pytest.mark.parametrize("tile_n", [0, 64, 128, 1264, 4264, 4464, 4228, 4428, 61128, 61256, 62128, 62256])
 def test_conv_tc_dgrad_fused_bn_reduce(F, R, b, hw, cin, cout, tile_n, pool):
     """dgrad epilogue also produces the previous block's BN-backward sums; the apply pass finishes the job."""
     if tile_n and not _tile_ok(tile_n, cin, hw):

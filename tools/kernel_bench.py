@@ -12,6 +12,8 @@ import torch
 def tile_ok(code, channels, hw):
     if code < 1000:
         return channels % code == 0
+    if code > 60000:          # CTA pairs: 6<splits><tile>
+        return channels % (code % 1000) == 0
     if code > 4000:           # cluster split-K: 4<splits><tile>
         return channels % (64 if code % 100 == 64 else 128) == 0
     if code > 2000:
@@ -23,7 +25,7 @@ def tile_ok(code, channels, hw):
     return bn % nc == 0 or (bn == 1 and bh % nc == 0)
 
 
-TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256, 4264, 4464, 4228, 4428]
+TILE_CODES = [64, 128, 1264, 1464, 1864, 1228, 1428, 2128, 2256, 4264, 4464, 4228, 4428, 61128, 61256, 62128, 62256]
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cs744_ddp_b200.models.vgg import conv_blocks  # noqa: E402
