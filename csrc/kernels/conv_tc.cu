@@ -648,8 +648,26 @@ static bool pair_tiles_enabled() {
   return v == 1;
 }
 
+// DDPB_CONV_PAIR: which layers the automatic choice gives to the CTA-pair tiles of THIS file (0 = none).
+static int pair_mode() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DDPB_CONV_PAIR"); v = e ? atoi(e) : 0; }
+  return v;
+}
+
 static int auto_tile(int B, int H, int W, int n_channels, int k_channels) {
   const long long pixels = (long long)B * H * W;
+  if (pair_mode() > 0 && pixels >= 2 * TILE_M) {
+    const long long m_pairs = (pixels + 2 * TILE_M - 1) / (2 * TILE_M);
+    const int k_total9 = 9 * (k_channels / KCHUNK);
+    const int mode = pair_mode();
+    const long long min_ctas = 128;
+    // CTAs = 2 per pair x n-tiles x split-K
+    if ((mode == 1 || mode == 4) && n_channels % 256 == 0 && k_total9 >= 18 && m_pairs * (n_channels / 256) * 4 >= min_ctas) return 62256;
+    if ((mode == 2 || mode == 4) && n_channels % 128 == 0 && k_total9 >= 18 && m_pairs * (n_channels / 128) * 4 >= min_ctas) return 62128;
+    if (mode == 3 && n_channels % 256 == 0 && m_pairs * (n_channels / 256) * 2 >= min_ctas) return 61256;
+    if ((mode == 3 || mode == 5) && n_channels % 128 == 0 && m_pairs * (n_channels / 128) * 2 >= 2 * min_ctas) return 61128;
+  }
   if (pair_tiles_enabled() && pixels >= 2 * TILE_M) {
     // a pair tile is worth it when it still leaves >= ~1 CTA per SM
     if (n_channels % 256 == 0 && (pixels / TILE_M) * (n_channels / 256) >= 120) return 2256;
