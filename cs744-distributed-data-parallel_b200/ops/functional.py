@@ -287,3 +287,18 @@ def p2p_sync(mode: int, grad_ptrs: Sequence[int], master_ptrs: Optional[Sequence
                                       _ptr_table(flag_ptrs), ptr(mom), ptr(epochs), rank, world, slot, cll(off), cll(n),
                                       cf(lr), cf(momentum), cf(wd), blocks, tab, n_sh, stream_handle(stream)),
           "p2p_sync")
+
+
+def first_layer_bwd_fused(dout, y, x_cols, save_mean, save_invstd, gamma, beta, sums, ctas: int = 0):
+    """Block 0 backward in one kernel (BN + ReLU + pool backward apply fused with the 3 -> 64 weight gradient).
+    Returns (dw [64, 27] fp32, dgamma, dbeta, dbias)."""
+    b, h, w_, c = y.shape
+    dev = y.device
+    dw = torch.zeros((c, 27), dtype=torch.float32, device=dev)
+    dgamma = torch.empty(c, dtype=torch.float32, device=dev)
+    dbeta = torch.empty(c, dtype=torch.float32, device=dev)
+    dbias = torch.zeros(c, dtype=torch.float32, device=dev)
+    check(lib().ddpb_first_layer_bwd_fused(ptr(dout), ptr(y), ptr(x_cols), ptr(save_mean), ptr(save_invstd), ptr(gamma),
+                                           ptr(beta), ptr(sums), ptr(dw), ptr(dgamma), ptr(dbeta), ptr(dbias), b, h, w_, c,
+                                           27, 27, ctas, stream_handle()), "first_layer_bwd_fused")
+    return dw, dgamma, dbeta, dbias

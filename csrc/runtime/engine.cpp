@@ -77,6 +77,7 @@ struct Engine {
   bool fuse_bn_fwd = false;                   // DDPB_FUSE_BN_FWD=1: conv + grid barrier + BatchNorm forward in one kernel
                                               // (measured ~10 us per step SLOWER than the separate, PDL-launched kernel: off)
   bool fuse_bn_reduce = true;                 // DDPB_FUSE_BN_REDUCE=0: keep the separate reduction kernel
+  bool fuse_first_bwd = true;                 // DDPB_FUSE_FIRST_BWD=0: block 0 backward as BN-apply + weight-gradient kernels
   void *x0cols = nullptr, *w0pad = nullptr;   // first layer as a GEMM: patch matrix [B*1024][64], weights [64][64]
   std::vector<Bucket> buckets;
   std::vector<long long> shard;          // [lo, hi) arena ranges of the conv weights: fp32 master stays with its owner
@@ -124,7 +125,7 @@ static constexpr int kTraceSlots = 512 * 32;      // 512 trace ids x KTRACE_LANE
 extern "C" {
 int ddpb_ktrace_set_conv_tc(void*); int ddpb_ktrace_set_wgrad_tc(void*); int ddpb_ktrace_set_gemm_rows_tc(void*);
 int ddpb_ktrace_set_bn_relu_pool(void*); int ddpb_ktrace_set_fc_ce(void*); int ddpb_ktrace_set_elementwise(void*);
-int ddpb_ktrace_set_sync_p2p(void*);
+int ddpb_ktrace_set_sync_p2p(void*); int ddpb_ktrace_set_first_layer_bwd(void*);
 }
 
 static int trace_mark(Engine* e, cudaStream_t stream, const char* call_text) {
@@ -547,6 +548,20 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
     const void* x_in = i == 0 ? e->input : e->blocks[i - 1].act;
     void* dy = e->dy_buf2[i & 1];
     if (i + 2 < L) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->ev_wg[i + 2], 0));   // previous reader of this dY buffer
+    if (i == 0 && reduced_by_dgrad && e->fuse_first_bwd && use_tc_first(e, b) && b.pool && b.cout == 64) {
+      // Block 0 has no data gradient: its BatchNorm-backward apply pass and its weight gradient run as ONE kernel
+      // and the gradient of its conv output (the largest tensor of the backward pass) never touches HBM
+      LAUNCH(e, s, ddpb_first_layer_bwd_fused(e->dact, b.y, e->x0cols, e->mean + b.ch_off, e->invstd + b.ch_off,
+                                              e->master + b.bn_w.off, e->master + b.bn_b.off, bsums + b.stat_off,
+                                              e->grad + b.conv_w.off, e->grad + b.bn_w.off, e->grad + b.bn_b.off,
+                                              e->grad + b.conv_b.off, B, b.hw, b.hw, b.cout, 27, 27, 0, s));
+      DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dy[0], s));
+      DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[0], s));
+      DDPB_CUDA_CHECK(cudaEventRecord(e->ev_wg[0], s));
+      ECHECK(buckets_ready(e, 0, e->ev_wg[0], nullptr));
+      reduced_by_dgrad = false;
+      continue;
+    }
     if (reduced_by_dgrad) {
       // the reduction pass already ran in the epilogue of dgrad(i + 1)
       LAUNCH(e, s, ddpb_bn_relu_pool_bwd_apply(e->dact, b.y, e->mean + b.ch_off, e->invstd + b.ch_off,
@@ -737,6 +752,7 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   if (const char* fb = getenv("DDPB_FUSE_BN_REDUCE")) e->fuse_bn_reduce = fb[0] != '0';
   if (const char* tc = getenv("DDPB_TWO_COMM")) e->two_comm = tc[0] != '0';
   if (const char* ff = getenv("DDPB_FUSE_BN_FWD")) e->fuse_bn_fwd = ff[0] != '0';
+  if (const char* f0 = getenv("DDPB_FUSE_FIRST_BWD")) e->fuse_first_bwd = f0[0] != '0';
   if (const char* sm = getenv("DDPB_SHARD_MASTER")) e->shard_master = sm[0] != '0';
   if (const char* za = getenv("DDPB_ZERO_ASYNC")) e->zero_async = za[0] != '0';
   if (const char* no = getenv("DDPB_NVLS_ONESHOT")) e->nvls_oneshot = no[0] != '0';
@@ -948,7 +964,7 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
     void* p = e->ktrace_buf;
     int bad = ddpb_ktrace_set_conv_tc(p) | ddpb_ktrace_set_wgrad_tc(p) | ddpb_ktrace_set_gemm_rows_tc(p) |
               ddpb_ktrace_set_bn_relu_pool(p) | ddpb_ktrace_set_fc_ce(p) | ddpb_ktrace_set_elementwise(p) |
-              ddpb_ktrace_set_sync_p2p(p);
+              ddpb_ktrace_set_sync_p2p(p) | ddpb_ktrace_set_first_layer_bwd(p);
     DDPB_REQUIRE(!bad, "engine_trace_step: could not publish the trace buffer to the kernels");
   }
   cudaGraph_t graph = nullptr;

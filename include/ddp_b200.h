@@ -187,6 +187,16 @@ int ddpb_gemm_rows_fwd_tc(const void* x, const void* w_bf16, const float* bias, 
 int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw, int B, int H, int W, int Cout, int ld, int cols,
                         int split_k, cudaStream_t stream);
 
+/* Backward of block 0 (ref Part 1/model.py:16,18-25 for the first conv / BN / ReLU / pool) in one launch: the
+ * BatchNorm + ReLU + max-pool backward apply pass fused with the 3 -> 64 convolution's weight gradient, so that
+ * the 33.5 MB gradient of the conv output never goes through global memory.  dout [B,16,16,64] bf16, y
+ * [B,32,32,64] bf16, x_cols [B*1024][64] bf16, sums [128] (BN-backward reduction).  dw (fp32 [64][ld], columns <
+ * cols <= 32) and dbias (nullable) accumulate; dgamma / dbeta are written.  ctas = 0 picks. */
+int ddpb_first_layer_bwd_fused(const void* dout, const void* y, const void* x_cols, const float* save_mean,
+                               const float* save_invstd, const float* gamma, const float* beta, const float* sums,
+                               float* dw, float* dgamma, float* dbeta, float* dbias, int B, int H, int W, int C, int ld,
+                               int cols, int ctas, cudaStream_t stream);
+
 /* Allow (1) / forbid (0) programmatic dependent launches (default: on unless DDPB_PDL=0); returns the
  * previous setting.  They are only ever used while the launching stream is being captured. */
 int ddpb_set_pdl(int on);

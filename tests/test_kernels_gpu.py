@@ -380,3 +380,39 @@ def test_p2p_sharded_master_single_gpu_emulation(F, mode_name, world):
     for r in range(world):
         assert torch.allclose(masters[r][off:off + n], ref[off:off + n], rtol=1e-5, atol=1e-6), (mode_name, r)
         assert torch.equal(masters[r], masters[0])
+
+
+@pytest.mark.parametrize("b", [16, 5, 37])
+def test_first_layer_backward_fused(F, R, b):
+    """BN/ReLU/pool backward apply + 3 -> 64 weight gradient in one kernel == the two separate kernels, and both
+    close to a plain fp32 torch autograd of conv -> BN -> ReLU -> max-pool (ref Part 1/model.py:16,18-25)."""
+    torch.manual_seed(31)
+    x = torch.randn(b, 32, 32, 3, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(64, 3, 3, 3, device=DEV) * 0.2).to(torch.bfloat16)
+    bias = torch.zeros(64, device=DEV)
+    gamma = torch.rand(64, device=DEV) + 0.5
+    beta = torch.randn(64, device=DEV) * 0.2
+    y, stats, cols = F.first_layer_fwd_tc(x, w, bias, True)
+    rm, rv = torch.zeros(64, device=DEV), torch.ones(64, device=DEV)
+    out, mean, invstd = F.bn_relu_pool_fwd(y, stats, gamma, beta, rm, rv, None, True, True)
+    dout = torch.randn_like(out)
+    # the two-kernel path (its own reduction pass produces the sums the fused kernel is given)
+    dbias_ref = torch.zeros(64, device=DEV)
+    dy, dgamma_ref, dbeta_ref = F.bn_relu_pool_bwd(dout, y, mean, invstd, gamma, beta, True, dbias_ref)
+    dw_ref = F.first_layer_wgrad_tc(dy, cols).reshape(64, 27)
+    sums = torch.cat([dbeta_ref, dgamma_ref]).contiguous()
+    for ctas in (0, 1, 7):
+        dw, dgamma, dbeta, dbias = F.first_layer_bwd_fused(dout, y, cols, mean, invstd, gamma, beta, sums, ctas)
+        torch.cuda.synchronize()
+        _report(f"first_bwd_fused b{b} ctas{ctas} dw", dw, dw_ref, 2e-3)
+        assert torch.equal(dgamma, dgamma_ref) and torch.equal(dbeta, dbeta_ref)
+        scale = max(1.0, float(dy.float().abs().sum(dim=(0, 1, 2)).max()))
+        assert float((dbias - dbias_ref).abs().max()) < 1e-2 * scale
+    # fp32 torch oracle of the whole block
+    xt = x.float().permute(0, 3, 1, 2).requires_grad_(False)
+    wt = w.float().permute(0, 3, 1, 2).clone().requires_grad_(True)       # KRSC -> OIHW
+    yt = torch.nn.functional.conv2d(xt, wt, None, 1, 1)
+    ot = torch.nn.functional.max_pool2d(torch.relu(torch.nn.functional.batch_norm(yt, None, None, gamma, beta, True, 0.1, 1e-5)), 2)
+    ot.backward(dout.float().permute(0, 3, 1, 2))
+    # (y, dY and the patch matrix are bf16 in the kernel: ~2^-8 relative rounding on each factor of a long sum)
+    _report(f"first_bwd_fused b{b} dw vs torch", dw, wt.grad.permute(0, 2, 3, 1).reshape(64, 27), 8e-2)
