@@ -302,3 +302,32 @@ def first_layer_bwd_fused(dout, y, x_cols, save_mean, save_invstd, gamma, beta, 
                                            ptr(beta), ptr(sums), ptr(dw), ptr(dgamma), ptr(dbeta), ptr(dbias), b, h, w_, c,
                                            27, 27, ctas, stream_handle()), "first_layer_bwd_fused")
     return dw, dgamma, dbeta, dbias
+
+
+# ---- fp32 convolutions on the tensor cores (tcgen05 kind::tf32) ---------------------------------------------
+def conv_fwd_tf32(x, w_krsc, bias, want_stats: bool = False):
+    b, h, w_, cin = x.shape
+    cout = w_krsc.shape[0]
+    y = torch.empty((b, h, w_, cout), dtype=torch.float32, device=x.device)
+    stats = torch.zeros(2 * cout, dtype=torch.float32, device=x.device) if want_stats else None
+    check(lib().ddpb_conv3x3_fwd_tf32(ptr(x), ptr(w_krsc), ptr(bias), ptr(y), ptr(stats), b, h, w_, cin, cout,
+                                      stream_handle()), "conv_fwd_tf32")
+    return (y, stats) if want_stats else y
+
+
+def conv_dgrad_tf32(dy, w_krsc):
+    b, h, w_, cout = dy.shape
+    cin = w_krsc.shape[3]
+    dx = torch.empty((b, h, w_, cin), dtype=torch.float32, device=dy.device)
+    check(lib().ddpb_conv3x3_dgrad_tf32(ptr(dy), ptr(w_krsc), ptr(dx), b, h, w_, cin, cout, stream_handle()),
+          "conv_dgrad_tf32")
+    return dx
+
+
+def conv_wgrad_tf32(dy, x, split_k: int = 0):
+    b, h, w_, cout = dy.shape
+    cin = x.shape[3]
+    dw = torch.zeros((cout, 3, 3, cin), dtype=torch.float32, device=dy.device)
+    check(lib().ddpb_conv3x3_wgrad_tf32(ptr(dy), ptr(x), ptr(dw), b, h, w_, cin, cout, split_k, stream_handle()),
+          "conv_wgrad_tf32")
+    return dw

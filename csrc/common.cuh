@@ -373,6 +373,16 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// D[tmem] (+)= A[smem] * B[smem]; fp32 storage read as TF32 (10-bit mantissa), fp32 accumulate; K = 8 per instruction.
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // mbarrier arrive once all previously issued MMAs of this thread have completed.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -500,6 +510,17 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_b
   d |= (uint64_t)2 << 61;
   return d;
 }
+// MN-major 32-bit (tf32) operands: layout type 1 = SWIZZLE_128B_BASE32B, written by TMA with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.  Atom = 4 K-rows x 128 bytes; SBO = distance between 4-row groups.
+__device__ __forceinline__ uint64_t umma_desc_base32(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)1 << 61;
+  return d;
+}
 // Instruction descriptor for kind::f16 with bf16 A/B and fp32 D (InstrDescriptor bitfield).
 __device__ __forceinline__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool a_mn_major, bool b_mn_major) {
   return (1u << 4)                         // D format: F32
@@ -509,6 +530,12 @@ __device__ __forceinline__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool
          | ((b_mn_major ? 1u : 0u) << 16)  // B major
          | ((uint32_t)(N >> 3) << 17)      // N / 8
          | ((uint32_t)(M >> 4) << 24);     // M / 16
+}
+
+// Instruction descriptor for kind::tf32 (fp32 operands in shared memory, fp32 D).
+__device__ __forceinline__ constexpr uint32_t umma_idesc_tf32(int M, int N, bool a_mn_major, bool b_mn_major) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {

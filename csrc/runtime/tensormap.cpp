@@ -94,7 +94,8 @@ static EncodeTiledFn encode_fn() {
 }
 
 static int encode(CUtensorMap* out, const void* ptr, int rank, const cuuint64_t* dims, const cuuint64_t* strides,
-                  const cuuint32_t* box, CUtensorMapDataType dtype = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16) {
+                  const cuuint32_t* box, CUtensorMapDataType dtype = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                  CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_last_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -102,7 +103,7 @@ static int encode(CUtensorMap* out, const void* ptr, int rank, const cuuint64_t*
   }
   cuuint32_t ones[5] = {1, 1, 1, 1, 1};
   CUresult r = fn(out, dtype, rank, const_cast<void*>(ptr), dims, strides, box, ones,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_last_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d, dims %llu %llu %llu %llu, box %u %u %u %u)",
@@ -126,6 +127,19 @@ int make_tmap_nhwc_bf16(CUtensorMap* out, const void* ptr, int N, int H, int W, 
   return encode(out, ptr, 4, dims, strides, box);
 }
 
+int make_tmap_nhwc_f32(CUtensorMap* out, const void* ptr, int N, int H, int W, int C, int box_c, int box_w, int box_h,
+                       int box_n, bool atom32) {
+  if (box_c != 32 || C % 32 != 0) {
+    set_last_error("tensor map: fp32 channel box must be 32 and C a multiple of 32 (C=%d box=%d)", C, box_c);
+    return DDPB_ERR_ARG;
+  }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+  cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)box_w, (cuuint32_t)box_h, (cuuint32_t)box_n};
+  return encode(out, ptr, 4, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
 int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, long long rows, long long cols, int box_cols,
                       int box_rows) {
   if (box_cols != 64 || cols % 8 != 0) {
@@ -139,7 +153,7 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, long long rows, long lo
 }
 
 int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, long long rows, long long cols, int box_cols,
-                     int box_rows) {
+                     int box_rows, bool atom32) {
   if (box_cols != 32 || cols % 4 != 0) {
     set_last_error("tensor map: fp32 2-D box must be 32 columns (128 bytes) wide, row pitch 16-byte aligned");
     return DDPB_ERR_ARG;
@@ -147,7 +161,8 @@ int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, long long rows, long lon
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
   cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
-  return encode(out, ptr, 2, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32);
+  return encode(out, ptr, 2, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 }  // namespace ddpb

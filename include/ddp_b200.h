@@ -187,6 +187,16 @@ int ddpb_gemm_rows_fwd_tc(const void* x, const void* w_bf16, const float* bias, 
 int ddpb_patch_wgrad_tc(const void* dy, const void* x_cols, float* dw, int B, int H, int W, int Cout, int ld, int cols,
                         int split_k, cudaStream_t stream);
 
+/* fp32 convolutions on the tensor cores (csrc/kernels/conv_tf32.cu): tcgen05.mma kind::tf32, fp32 NHWC in / out,
+ * fp32 KRSC weights, fp32 accumulation.  The engine's fp32 path (the reference is fp32 throughout,
+ * ref Part 1/main.py:10; Part 1/model.py:18-23).  Channels multiples of 64 (wgrad: Cout multiple of 128). */
+int ddpb_conv3x3_fwd_tf32(const float* x, const float* w, const float* bias, float* y, float* stats, int B, int H, int W,
+                          int Cin, int Cout, cudaStream_t stream);
+int ddpb_conv3x3_dgrad_tf32(const float* dy, const float* w, float* dx, int B, int H, int W, int Cin, int Cout,
+                            cudaStream_t stream);
+int ddpb_conv3x3_wgrad_tf32(const float* dy, const float* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                            int split_k, cudaStream_t stream);
+
 /* Backward of block 0 (ref Part 1/model.py:16,18-25 for the first conv / BN / ReLU / pool) in one launch: the
  * BatchNorm + ReLU + max-pool backward apply pass fused with the 3 -> 64 convolution's weight gradient, so that
  * the 33.5 MB gradient of the conv output never goes through global memory.  dout [B,16,16,64] bf16, y

@@ -416,3 +416,26 @@ def test_first_layer_backward_fused(F, R, b):
     ot.backward(dout.float().permute(0, 3, 1, 2))
     # (y, dY and the patch matrix are bf16 in the kernel: ~2^-8 relative rounding on each factor of a long sum)
     _report(f"first_bwd_fused b{b} dw vs torch", dw, wt.grad.permute(0, 2, 3, 1).reshape(64, 27), 8e-2)
+
+
+@pytest.mark.parametrize("b", [16, 10])
+@pytest.mark.parametrize("hw,cin,cout", TC_SHAPES)
+def test_conv_tf32(F, R, b, hw, cin, cout):
+    """fp32 convolutions on tcgen05 kind::tf32 (10-bit mantissa inputs, fp32 accumulation) against the fp64-based
+    reference: forward (+ BatchNorm statistics), data gradient, weight gradient."""
+    torch.manual_seed(5)
+    x = torch.randn(b, hw, hw, cin, device=DEV)
+    dy = torch.randn(b, hw, hw, cout, device=DEV)
+    w = torch.randn(cout, 3, 3, cin, device=DEV) * 0.05
+    bias = torch.randn(cout, device=DEV) * 0.1
+    y, stats = F.conv_fwd_tf32(x, w, bias, want_stats=True)
+    dx = F.conv_dgrad_tf32(dy, w)
+    torch.cuda.synchronize()
+    _report(f"tf32_fwd hw{hw} {cin}->{cout} b{b}", y, R.conv_fwd(x, w, bias), 2e-3)
+    _report("tf32_fwd_stats", stats, R.channel_stats(y), 1e-4)
+    _report(f"tf32_dgrad hw{hw} {cin}->{cout} b{b}", dx, R.conv_dgrad(dy, w), 2e-3)
+    if cout % 128 == 0:
+        for sk in (0, 1, 3):
+            dw = F.conv_wgrad_tf32(dy, x, sk)
+            torch.cuda.synchronize()
+            _report(f"tf32_wgrad hw{hw} {cin}->{cout} b{b} split{sk}", dw, R.conv_wgrad(dy, x), 2e-3)
