@@ -77,6 +77,7 @@ struct Engine {
   bool fuse_bn_fwd = false;                   // DDPB_FUSE_BN_FWD=1: conv + grid barrier + BatchNorm forward in one kernel
                                               // (measured ~10 us per step SLOWER than the separate, PDL-launched kernel: off)
   bool fuse_bn_reduce = true;                 // DDPB_FUSE_BN_REDUCE=0: keep the separate reduction kernel
+  bool tf32 = true;                           // DDPB_TF32=0: fp32 engine on the SIMT kernels (exact fp32 products)
   bool fuse_first_bwd = true;                 // DDPB_FUSE_FIRST_BWD=0: block 0 backward as BN-apply + weight-gradient kernels
   void *x0cols = nullptr, *w0pad = nullptr;   // first layer as a GEMM: patch matrix [B*1024][64], weights [64][64]
   std::vector<Bucket> buckets;
@@ -125,7 +126,7 @@ static constexpr int kTraceSlots = 512 * 32;      // 512 trace ids x KTRACE_LANE
 extern "C" {
 int ddpb_ktrace_set_conv_tc(void*); int ddpb_ktrace_set_wgrad_tc(void*); int ddpb_ktrace_set_gemm_rows_tc(void*);
 int ddpb_ktrace_set_bn_relu_pool(void*); int ddpb_ktrace_set_fc_ce(void*); int ddpb_ktrace_set_elementwise(void*);
-int ddpb_ktrace_set_sync_p2p(void*); int ddpb_ktrace_set_first_layer_bwd(void*);
+int ddpb_ktrace_set_sync_p2p(void*); int ddpb_ktrace_set_first_layer_bwd(void*); int ddpb_ktrace_set_conv_tf32(void*);
 }
 
 static int trace_mark(Engine* e, cudaStream_t stream, const char* call_text) {
@@ -371,6 +372,10 @@ static int alloc_all(Engine* e) {
 static bool use_tc(const Engine* e, const Block& b) {
   return e->cfg.dtype == DDPB_BF16 && e->cfg.use_tc && b.cin % 64 == 0 && b.cout % 64 == 0;
 }
+// fp32 engine: the same layers on tcgen05 kind::tf32 (conv_tf32.cu); DDPB_TF32=0 keeps the SIMT oracle kernels
+static bool use_tf32(const Engine* e, const Block& b) {
+  return e->cfg.dtype == DDPB_F32 && e->cfg.use_tc && e->tf32 && b.cin % 64 == 0 && b.cout % 64 == 0;
+}
 static bool use_tc_wgrad(const Engine* e, const Block& b) {
   return use_tc(e, b) && b.cout % 128 == 0;
 }
@@ -422,6 +427,9 @@ static int forward(Engine* e, int B, int training, cudaStream_t s, bool zero_gra
                                        e->rvar + b.ch_off, e->nbt + i, b.pool, 1e-5f, 0.1f, barrier, &bn_fused, s));
     } else if (use_tc(e, b))
       LAUNCH(e, s, ddpb_conv3x3_fwd_tc(x, e->shadow + b.conv_w.off, bias, b.y, st, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+    else if (use_tf32(e, b))
+      LAUNCH(e, s, ddpb_conv3x3_fwd_tf32((const float*)x, e->master + b.conv_w.off, bias, (float*)b.y, st, B, b.hw, b.hw, b.cin,
+                                         b.cout, s));
     else if (use_tc_first(e, b)) {
       LAUNCH(e, s, ddpb_im2col3x3_c3(x, e->shadow + b.conv_w.off, e->x0cols, e->w0pad, B, b.hw, b.hw, b.cout, 0, s));
       LAUNCH(e, s, ddpb_gemm_rows_fwd_tc(e->x0cols, e->w0pad, bias, b.y, st, (long long)B * b.hw * b.hw, b.cout, s));
@@ -590,6 +598,9 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
         reduced_by_dgrad = true;
       } else if (use_tc(e, b))
         LAUNCH(e, s, ddpb_conv3x3_dgrad_tc(dy, e->shadow + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, 0, s));
+      else if (use_tf32(e, b))
+        LAUNCH(e, s, ddpb_conv3x3_dgrad_tf32((const float*)dy, e->master + b.conv_w.off, (float*)e->dact, B, b.hw, b.hw, b.cin,
+                                             b.cout, s));
       else
         LAUNCH(e, s, ddpb_conv3x3_dgrad_simt(dy, e->master + b.conv_w.off, e->dact, B, b.hw, b.hw, b.cin, b.cout, dt, s));
     }
@@ -597,6 +608,9 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
     DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->ev_dy[i], 0));
     if (use_tc_wgrad(e, b))
       LAUNCH(e, e->wg, ddpb_conv3x3_wgrad_tc(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, e->wg));
+    else if (use_tf32(e, b) && b.cout % 128 == 0)
+      LAUNCH(e, e->wg, ddpb_conv3x3_wgrad_tf32((const float*)dy, (const float*)x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin,
+                                               b.cout, 0, e->wg));
     else if (use_tc_first(e, b))
       LAUNCH(e, e->wg, ddpb_patch_wgrad_tc(dy, e->x0cols, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cout, 27, 27, 0, e->wg));
     else
@@ -753,6 +767,7 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   if (const char* tc = getenv("DDPB_TWO_COMM")) e->two_comm = tc[0] != '0';
   if (const char* ff = getenv("DDPB_FUSE_BN_FWD")) e->fuse_bn_fwd = ff[0] != '0';
   if (const char* f0 = getenv("DDPB_FUSE_FIRST_BWD")) e->fuse_first_bwd = f0[0] != '0';
+  if (const char* tf = getenv("DDPB_TF32")) e->tf32 = tf[0] != '0';
   if (const char* sm = getenv("DDPB_SHARD_MASTER")) e->shard_master = sm[0] != '0';
   if (const char* za = getenv("DDPB_ZERO_ASYNC")) e->zero_async = za[0] != '0';
   if (const char* no = getenv("DDPB_NVLS_ONESHOT")) e->nvls_oneshot = no[0] != '0';
@@ -964,7 +979,7 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
     void* p = e->ktrace_buf;
     int bad = ddpb_ktrace_set_conv_tc(p) | ddpb_ktrace_set_wgrad_tc(p) | ddpb_ktrace_set_gemm_rows_tc(p) |
               ddpb_ktrace_set_bn_relu_pool(p) | ddpb_ktrace_set_fc_ce(p) | ddpb_ktrace_set_elementwise(p) |
-              ddpb_ktrace_set_sync_p2p(p) | ddpb_ktrace_set_first_layer_bwd(p);
+              ddpb_ktrace_set_sync_p2p(p) | ddpb_ktrace_set_first_layer_bwd(p) | ddpb_ktrace_set_conv_tf32(p);
     DDPB_REQUIRE(!bad, "engine_trace_step: could not publish the trace buffer to the kernels");
   }
   cudaGraph_t graph = nullptr;

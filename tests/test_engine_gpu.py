@@ -48,13 +48,24 @@ def no_tf32():
     torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
 
 
-def _pair(dtype, graph, b=16):
+def _pair(dtype, graph, b=16, tf32=False):
+    """torch fp32 oracle + native engine with the same weights.  ``tf32`` selects, for the fp32 engine, the
+    tensor-core kernels (tcgen05 kind::tf32, the default) or the exact-fp32 SIMT kernels (DDPB_TF32=0)."""
+    import os
     from cs744_ddp_b200.backends import TorchBackend
     from cs744_ddp_b200.engine import NativeBackend
     torch.manual_seed(0)
     tb = TorchBackend(_cfg(backend="torch", dtype="fp32", global_batch=b), DEV)
-    nb = NativeBackend(_cfg(backend="native", dtype=dtype, use_cuda_graph=graph, global_batch=b), DEV,
-                       init_state=tb.state_dict())
+    old = os.environ.get("DDPB_TF32")
+    os.environ["DDPB_TF32"] = "1" if tf32 else "0"
+    try:
+        nb = NativeBackend(_cfg(backend="native", dtype=dtype, use_cuda_graph=graph, global_batch=b), DEV,
+                           init_state=tb.state_dict())
+    finally:
+        if old is None:
+            os.environ.pop("DDPB_TF32", None)
+        else:
+            os.environ["DDPB_TF32"] = old
     return tb, nb
 
 
@@ -62,9 +73,14 @@ def _rel(a, b):
     return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))
 
 
+@pytest.mark.parametrize("tf32", [False, True])
 @pytest.mark.parametrize("graph", [False, True])
-def test_fp32_engine_matches_torch_training(no_tf32, graph):
-    tb, nb = _pair("fp32", graph)
+def test_fp32_engine_matches_torch_training(no_tf32, graph, tf32):
+    """fp32 engine against torch in strict fp32.  With the exact SIMT kernels the two differ by summation order
+    only; with the tensor-core kernels every convolution reads its operands as TF32 (10-bit mantissa, ~8e-4
+    relative per product sum, measured in test_conv_tf32) - the loss bounds below are those of the exact path
+    widened by that amount per layer on the way forward and back."""
+    tb, nb = _pair("fp32", graph, tf32=tf32)
     tb.set_train(True)
     for step, raw in enumerate(_batches(4, 16)):
         lt = tb.train_step(*tb.prepare(raw), _T())
@@ -72,7 +88,7 @@ def test_fp32_engine_matches_torch_training(no_tf32, graph):
         print(f"[eng] fp32 graph={graph} step {step}: torch {float(lt):.6f} native {float(ln):.6f}")
         # training is chaotic: rounding-level differences grow step by step (torch itself is not
         # run-to-run reproducible at the 1e-3 level by step 3)
-        tol = 2e-3 if step < 2 else 3e-2
+        tol = (2e-3 if step < 2 else 3e-2) if not tf32 else (1e-2 if step < 2 else 5e-2)
         if step == 0:       # diagnostic: which tensors differ most after the first update
             sd_t, sd_n = tb.state_dict(), nb.state_dict()
             worst = sorted(((_rel(sd_n[k], sd_t[k]), k) for k in sd_t if "num_batches" not in k), reverse=True)[:3]
@@ -88,18 +104,37 @@ def test_fp32_engine_matches_torch_training(no_tf32, graph):
         # conv biases sit in front of a BN: their gradient is numerical noise.  BatchNorm
         # biases start at zero and one borderline ReLU decision (see
         # test_first_update_is_reproducible_across_fresh_engines) moves them by ~10 % after four steps.
-        tol = 0.2 if (k.endswith(".bias") and sd_t[k].numel() > 10 and "layers" in k) else 2e-2
+        small = k.endswith(".bias") and sd_t[k].numel() > 10 and "layers" in k
+        # TF32 perturbs every pre-activation by ~1e-3, which flips the ReLU decision of the elements that close to
+        # zero: BatchNorm biases (which start at 0, so their value IS the accumulated gradient) move by tens of per
+        # cent, weights by a few per cent after four steps; the per-kernel bound is test_conv_tf32's 2e-3
+        tol = (0.2 if small else 2e-2) if not tf32 else (1.0 if small else 0.1)
         assert err < tol, (k, err)
 
 
-def test_fp32_gradients_match_autograd(no_tf32):
-    tb, nb = _pair("fp32", False)
+@pytest.mark.parametrize("tf32", [False, True])
+def test_fp32_gradients_match_autograd(no_tf32, tf32):
+    """Exact-fp32 kernels: gradients equal strict-fp32 autograd up to summation order.  TF32 kernels: judged
+    against what torch's OWN TF32 convolutions (cudnn.allow_tf32) achieve on the same batch - the early layers
+    are ill-conditioned at initialisation, so any TF32 path is a few per cent off there."""
+    import copy
+    tb, nb = _pair("fp32", False, tf32=tf32)
     raw = _batches(1, 16, seed=3)[0]
     data, target = tb.prepare(raw)
     tb.optimizer.zero_grad()
     loss = tb.criterion(tb.model(data), target)
     loss.backward()
     ref = {n: p.grad.clone() for n, p in tb.model.named_parameters()}
+    theirs = {}
+    if tf32:
+        m2 = copy.deepcopy(tb.model)
+        m2.zero_grad()
+        torch.backends.cudnn.allow_tf32 = True
+        try:
+            tb.criterion(m2(data), target).backward()
+        finally:
+            torch.backends.cudnn.allow_tf32 = False
+        theirs = {n: _rel(p.grad, ref[n]) for n, p in m2.named_parameters()}
     # run only forward + backward on the engine (lr 0 keeps the weights, gradients stay in the arena)
     nb.cfg.lr = 0.0
     from cs744_ddp_b200.ops.native import check, stream_handle
@@ -110,8 +145,12 @@ def test_fp32_gradients_match_autograd(no_tf32):
         if name.endswith(".bias") and "layers" in name and g.abs().max() < 1e-5:
             continue                                   # conv bias before BN: pure noise
         err = _rel(got[name], g)
-        print(f"[eng] grad {name}: rel {err:.2e}")
-        assert err < 2e-3, (name, err)
+        if not tf32:
+            print(f"[eng] grad {name}: rel {err:.2e}")
+            assert err < 2e-3, (name, err)
+        else:
+            print(f"[eng] grad tf32 {name}: native {err:.2e}  torch allow_tf32 {theirs[name]:.2e}")
+            assert err < max(2e-2, 3.0 * theirs[name]), (name, err, theirs[name])
 
 
 @pytest.mark.parametrize("graph", [False, True])
@@ -355,7 +394,7 @@ def test_staged_batches_and_async_loss_match_the_direct_path():
         assert abs(a - b) < tol * max(1.0, abs(a)), (step, a, b)
 
 
-def test_first_update_is_reproducible_across_fresh_engines(no_tf32):
+def test_first_update_is_reproducible_across_fresh_engines(no_tf32, monkeypatch):
     """Same weights + same batch on fresh engines: the first update must be the same every time up to the
     order of the floating-point atomics.  That order can move a BatchNorm mean by one ulp, and this
     batch has an element whose pre-ReLU value sits within an ulp of zero (channel 302 of block 6): in
@@ -369,6 +408,7 @@ def test_first_update_is_reproducible_across_fresh_engines(no_tf32):
     init = {k: v.clone() for k, v in tb.state_dict().items()}
     raw = _batches(1, 16)[0]
     ref, flips = None, 0
+    monkeypatch.setenv("DDPB_TF32", "0")        # the exact-fp32 kernels: this test is about the order of fp32 atomics
     for it in range(8):
         nb = NativeBackend(_cfg(backend="native", dtype="fp32", use_cuda_graph=False, global_batch=16), DEV,
                            init_state=init)

@@ -42,7 +42,8 @@ def test_library_targets_sm100a_only():
     assert archs == {"sm_100a"}, archs
 
 
-@pytest.mark.parametrize("kernel", ["conv3x3_tc_kernel", "wgrad_tc_kernel", "gemm_rows_tc_kernel", "conv3x3_tc2_kernel"])
+@pytest.mark.parametrize("kernel", ["conv3x3_tc_kernel", "wgrad_tc_kernel", "gemm_rows_tc_kernel", "conv3x3_tc2_kernel",
+                                    "conv3x3_tf32_kernel", "wgrad_tf32_kernel", "first_layer_bwd_kernel"])
 def test_tensor_core_kernels_use_tcgen05_tma_and_tmem(sass, kernel):
     ks = _with(sass, kernel)
     assert ks, f"no kernel named {kernel} in the library"
@@ -60,7 +61,7 @@ def test_wgrad_epilogue_uses_tma_reduce_add(sass):
 
 
 def test_split_k_variants_use_cluster_barriers(sass):
-    ks = {k: v for k, v in _with(sass, "conv3x3_tc_kernel").items() if re.search(r"Li1ELi[24]EEEv", k)}
+    ks = {k: v for k, v in _with(sass, "conv3x3_tc_kernel").items() if re.search(r"Li1ELi[24]ELb[01]EEEv", k)}
     assert ks, "no cluster split-K instantiation found"
     assert all("UCGABAR_ARV" in ops for ops in ks.values())
 
@@ -74,3 +75,14 @@ def test_pdl_kernels_contain_wait_and_trigger(sass):
     for kernel in ("conv3x3_tc_kernel", "bn_fwd_kernel", "bn_bwd_apply_kernel", "fc_ce_fwd_kernel"):
         ks = _with(sass, kernel)
         assert ks and all("ACQBULK" in ops and "PREEXIT" in ops for ops in ks.values()), kernel
+
+
+def test_pair_tiles_issue_the_two_cta_mma(sass):
+    """cta_group::2 instantiations (PAIR = true): the MMA is the 2-CTA form and the commit is multicast."""
+    ks = {k: v for k, v in _with(sass, "conv3x3_tc_kernel").items() if k.endswith("ELb1EEEv14CUtensorMap_stS1_PKfPfNS_12ConvTcParamsE")}
+    assert ks, "no pair instantiation found"
+    text = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, timeout=600).stdout
+    for name in ks:
+        body = text.split("Function : " + name, 1)[1].split("Function :", 1)[0]
+        assert re.search(r"UTCHMMA\.2CTA", body), name
+        assert re.search(r"UTCBAR\.2CTA\.MULTICAST", body), name
