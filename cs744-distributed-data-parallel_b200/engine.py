@@ -35,7 +35,10 @@ from .ops import native as nv
 from .ops.native import check, lib, stream_handle
 
 MAX_BLOCKS, MAX_SLOTS = 24, 64
-NVLS_DEFAULT = "1"      # comm="auto" tries the NVSwitch-multicast (NVLS) path first; DDPB_NVLS=0 disables it
+# comm="auto" tries the NVSwitch-multicast (NVLS) path first on 3+ GPUs; between two GPUs the unicast kernels win
+# (36.9 MB reduce + SGD: 78 us against 114 us; bucketed step 0.575 ms against 0.595 ms).  DDPB_NVLS=0 / 1 overrides.
+def _nvls_default(world):
+    return "1" if world > 2 else "0"
 STRATEGY_CODE = {"none": 0, "gather_scatter": 1, "allreduce": 2, "bucketed": 3}
 PLAN_CODE = {"ddp": 0, "per_layer": 1, "single": 2}
 
@@ -114,7 +117,7 @@ class NativeBackend:
         self._comm = "none"
         want_p2p = self.world > 1 and cfg.comm in ("auto", "p2p", "nvls")
         self._vmm = None
-        if want_p2p and (cfg.comm == "nvls" or (cfg.comm == "auto" and os.environ.get("DDPB_NVLS", NVLS_DEFAULT) == "1")):
+        if want_p2p and (cfg.comm == "nvls" or (cfg.comm == "auto" and os.environ.get("DDPB_NVLS", _nvls_default(self.world)) == "1")):
             self._vmm = self._try_vmm_arena()           # NVSwitch multicast (NVLS) when the box exposes it
             if self._vmm is None and cfg.comm == "nvls":
                 raise nv.NativeError("comm=nvls requested but the multicast arena could not be set up")

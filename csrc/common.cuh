@@ -68,13 +68,24 @@ static inline int pdl_active(cudaStream_t stream, int family) {
 }
 
 // ---- in-kernel step tracer --------------------------------------------------------------------
-// Every kernel of the training step takes an int of launch flags: bit 0 = "execute
-// griddepcontrol.launch_dependents", bits 1.. = trace id (0: not traced).  A traced kernel stamps
+// Every kernel of the training step takes an int of launch flags: bits 0-1 = where to execute
+// griddepcontrol.launch_dependents (see kernel_flags), bits 2.. = trace id (0: not traced).  A traced kernel stamps
 // %globaltimer into slot 2*id (earliest CTA start) and 2*id+1 (latest warp end) of the trace buffer,
 // which gives the step's real timeline INSIDE the production CUDA graph, programmatic launches
 // included (ddpb_engine_trace_step, mode 2).  The buffer pointer lives in a per-translation-unit
 // __device__ variable (no relocatable device code here), set through DDPB_KTRACE_SETTER's function.
-int kernel_flags(cudaStream_t stream, int family);     // pdl_active(...) | next trace id << 1
+// kernel_flags: bit 0 = trigger the successor at the START of every CTA (it becomes resident at once and waits
+// in griddepcontrol.wait), bit 1 = trigger it LATE, when the CTA's main loop is done.  An early-triggered
+// successor parks its CTAs on the SMs for the whole duration of this kernel; that is free while the step has
+// the GPU to itself, but in the backward pass those parked CTAs hold the registers a bucket kernel of the
+// communication stream (or a weight-gradient CTA) needs, and the bucket kernel then starts one layer late
+// (seen with the step tracer).  DDPB_PDL_LATE is the mask of kernel families that trigger late.
+#ifndef DDPB_PDL_LATE_DEFAULT
+#define DDPB_PDL_LATE_DEFAULT 0
+#endif
+int pdl_late_mask();
+// (late_family: the bit DDPB_PDL_LATE tests when it differs from the DDPB_PDL_MASK family; 128 = dgrad)
+int kernel_flags(cudaStream_t stream, int family, int late_family = 0);     // early | late << 1 | next trace id << 2
 void ktrace_enable(int on);                             // host: start / stop handing out trace ids (restarts at 1)
 int ktrace_last_id();                                   // host: the last id handed out
 
@@ -213,11 +224,11 @@ __device__ __forceinline__ unsigned long long* ktrace_slot(int id) {
   return g_ktrace + ((size_t)id * KTRACE_LANES + (b % KTRACE_LANES)) * 2;
 }
 __device__ __forceinline__ void ktrace_begin(int flags) {
-  const int id = flags >> 1;
+  const int id = flags >> 2;
   if (id && threadIdx.x == 0 && threadIdx.y == 0 && threadIdx.z == 0) atomicMin(ktrace_slot(id), ktrace_now());
 }
 __device__ __forceinline__ void ktrace_end(int flags) {      // call where thread 0 leaves the kernel
-  const int id = flags >> 1;
+  const int id = flags >> 2;
   if (id && threadIdx.x == 0 && threadIdx.y == 0 && threadIdx.z == 0) atomicMax(ktrace_slot(id) + 1, ktrace_now());
 }
 #endif

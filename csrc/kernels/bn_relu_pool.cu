@@ -179,6 +179,7 @@ bn_fwd_kernel(const T* __restrict__ y, const float* __restrict__ stats, const fl
     // dgrad epilogue do this block's BN-backward reduction from one value per output pixel
     if (winner) store_vec<T>(winner + (size_t)op * C + c0, by);
   }
+  if (pdl & 2) pdl_launch_dependents();     // late trigger (see kernel_flags)
   ktrace_end(pdl);
 }
 
@@ -241,6 +242,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ y, const 
       }
     }
   }
+  if (pdl & 2) pdl_launch_dependents();     // late trigger (see kernel_flags)
   block_reduce_channels<V>(sm, a1, c0, pl, ppb, C, sums);
   block_reduce_channels<V>(sm, a2, c0, pl, ppb, C, sums + C);
   ktrace_end(pdl);
@@ -345,6 +347,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ y, const f
       }
     }
   }
+  if (pdl & 2) pdl_launch_dependents();     // late trigger (see kernel_flags): the main loop is done
   if (dbias) block_reduce_channels<V>(sm, ab, c0, pl, ppb, C, dbias);
   ktrace_end(pdl);
 }

@@ -258,6 +258,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tc_fence_after();
     if (trc && threadIdx.x == 64) trc[4] = global_timer_ns();         // accumulator complete
   }
+  // late trigger (see kernel_flags): every thread is past its main loop - the successor's CTAs become resident
+  // while this CTA runs its epilogue, not while it still needs the SM to itself and its neighbours
+  if (prm.pdl & 2) pdl_launch_dependents();
   // Epilogue, common to all variants.  This CTA finishes CW = BN / KS columns of the 128-row tile:
   //   0. (KS > 1) reduce-scatter of the fp32 partial tiles through distributed shared memory
   //   1. TMEM (+ partials) (+ bias) -> bf16 -> shared-memory tile (16-byte chunks, XOR-swizzled)
@@ -619,7 +622,7 @@ static int launch(const bf16* in, const bf16* w, bf16* out, const float* bias, f
       g_bnfwd.applied = true;
     }
   }
-  prm.pdl = kernel_flags(stream, 1);
+  prm.pdl = kernel_flags(stream, 1, DGRAD ? 128 : 1);
   DDPB_CUDA_CHECK(launch_ex(kern, grid, dim3(192), smem, stream, dim3(PAIR ? 2 : 1, NC, KS), 1, tmA, tmB, bias, stats, prm));
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;

@@ -172,8 +172,7 @@ enum { MODE_ONESHOT = 0, MODE_TWOSHOT = 1, MODE_ROOT = 2, MODE_BCAST = 3, MODE_A
 // The unit of work is one 16-byte access (4 elements) per thread with consecutive lanes on consecutive
 // addresses: a warp's load instruction covers 512 contiguous bytes.  (Two adjacent 16-byte loads per thread
 // - a 32-byte stride between lanes - ran at HALF the NVLink read rate: 360 instead of 690 GB/s, measured
-// with tools/peer_read_probe.py.)  Shapes as for the NVLS kernel below: THREADS = 64 runs next to the
-// backward kernels; THREADS = 512 is for a caller that owns the GPU.  U units are in flight per thread.
+// with tools/peer_read_probe.py.)  Shapes as for the NVLS kernel below; U units are in flight per thread.
 template <int MODE, int U, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 p2p_kernel(const P2PArgs a) {
@@ -300,9 +299,9 @@ struct NvlsArgs {
 
 // U units (one 16-byte access each, lanes contiguous) per thread and iteration.  ALL loads of an iteration -
 // the switch-reduced gradients and the local master weights and momentum - are issued before anything is
-// consumed, so one round trip covers them all.  Two shapes: THREADS = 64 is the one that runs next to the
-// backward kernels (under 5 K registers per CTA, two per SM: they fit beside two convolution CTAs, whose
-// ~29 K registers each leave no room for anything bigger, instead of evicting one); THREADS = 512 is for a caller that owns the GPU (the bandwidth sweep).
+// consumed, so one round trip covers them all.  Two shapes: the lean one runs next to the
+// backward kernels (see lean_threads: the cap is on requests in flight); THREADS = 512 on a caller-chosen grid is
+// for a caller that owns the GPU (the bandwidth sweep).
 template <int U, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 p2p_nvls_kernel(const NvlsArgs n) {
@@ -418,14 +417,41 @@ static unsigned int* err_record() {
   return g_err_host;        // unified addressing: the host pointer is valid on the device
 }
 
-// threads per CTA of the in-step ("lean") shape: DDPB_SYNC_THREADS = 64 or 128 (default, measured faster)
-static int lean_threads() {
-  static int v = 0;
-  if (!v) {
+// The in-step ("lean") shape.  What matters next to the backward pass is how many NVLink requests are IN FLIGHT,
+// not how many SMs the kernel touches: with ~150 K sixteen-byte requests queued (148 CTAs x 128 threads x 4 units x
+// 2) every kernel boundary of EVERY other stream took 8-11 us instead of 1.3 us - its completion has to travel
+// through the same queues - while 8 CTAs x 512 threads (32 K requests) moved the same bytes per second through the
+// switch and left the boundaries at 1.5 us (tools/launch_lag_probe.py, profiles/r2/launch_lag_w2.txt).
+// In the step itself the two kernels want different shapes (bench.py at 2 GPUs, 100 steps: the unicast kernel
+// 0.581 ms with 32 x 256 against 0.594 with 148 x 128; the NVLS kernel 0.599 with 148 x 128 against 0.625 with
+// 32 x 256 - its switch-reduced loads are the slow ones and need the requests): those are the defaults.
+// DDPB_SYNC_THREADS = 128 | 256 | 512 per CTA and DDPB_SYNC_MAX_BLOCKS = CTA cap override both.
+static int lean_threads(bool nvls) {
+  static int v = -1;
+  if (v < 0) {
     const char* e = getenv("DDPB_SYNC_THREADS");
-    v = (e && atoi(e) == 64) ? 64 : 128;
+    const int t = e ? atoi(e) : 0;
+    v = (t == 128 || t == 256 || t == 512) ? t : 0;
   }
-  return v;
+  return v ? v : (nvls ? 128 : 256);
+}
+static int lean_cap(bool nvls) {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DDPB_SYNC_MAX_BLOCKS");
+    v = e ? atoi(e) : 0;
+    if (v < 1 || v > P2P_MAX_BLOCKS) v = 0;
+  }
+  if (v) return v;
+  const int sms = sm_count();
+  return nvls ? (sms < P2P_MAX_BLOCKS ? sms : P2P_MAX_BLOCKS) : 32;
+}
+// CTAs for `units` 16-byte units per rank: at least two iterations of 4 units per thread before adding a CTA
+static int lean_blocks(long long units, bool nvls) {
+  const long long per_cta = (long long)lean_threads(nvls) * 8;
+  const long long want = (units + per_cta - 1) / per_cta;
+  const int cap = lean_cap(nvls);
+  return (int)(want < 1 ? 1 : (want > cap ? cap : want));
 }
 
 static unsigned long long timeout_ns() {
@@ -483,17 +509,10 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
   memset(&a, 0, sizeof(a));
   int rc = fill_common(a, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
   if (rc) return rc;
-  // blocks = 0: the lean shape (128 threads, at most one CTA per SM) that runs next to the backward kernels;
-  // blocks > 0: the caller owns the GPU and gets 512-thread CTAs with two units in flight per thread
+  // blocks = 0: the lean shape that runs next to the backward kernels (see lean_threads);
+  // blocks > 0: the caller owns the GPU and gets 512-thread CTAs on the grid it asks for
   const bool lean = blocks <= 0;
-  if (lean) {
-    const long long per_rank = n / 4 / ((mode & ~DDPB_P2P_NO_EXIT_BARRIER) == DDPB_P2P_TWOSHOT ? world : 1);
-    const int thr = lean_threads();
-    long long want = (per_rank + thr * 8 - 1) / (thr * 8);          // >= 2 iterations of 4 units per thread before adding CTAs
-    const int per_sm = thr == 64 ? 2 : 1;
-    const int cap = per_sm * sm_count() < P2P_MAX_BLOCKS ? per_sm * sm_count() : P2P_MAX_BLOCKS;
-    blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
-  }
+  if (lean) blocks = lean_blocks(n / 4 / ((mode & ~DDPB_P2P_NO_EXIT_BARRIER) == DDPB_P2P_TWOSHOT ? world : 1), false);
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "p2p: at most %d blocks", P2P_MAX_BLOCKS);
   for (int r = 0; r < world; ++r) {
     a.grad[r] = (float*)grad[r];
@@ -505,8 +524,8 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
   mode &= ~DDPB_P2P_NO_EXIT_BARRIER;
 #define DDPB_P2P_LAUNCH(M)                                                          \
   do {                                                                              \
-    if (lean && lean_threads() == 64) p2p_kernel<M, 4, 64><<<blocks, 64, 0, stream>>>(a);   \
-    else if (lean) p2p_kernel<M, 4, 128><<<blocks, 128, 0, stream>>>(a);            \
+    if (lean && lean_threads(false) == 128) p2p_kernel<M, 4, 128><<<blocks, 128, 0, stream>>>(a);   \
+    else if (lean && lean_threads(false) == 256) p2p_kernel<M, 4, 256><<<blocks, 256, 0, stream>>>(a);   \
     else p2p_kernel<M, 4, 512><<<blocks, 512, 0, stream>>>(a);                      \
   } while (0)
   switch (mode) {
@@ -550,21 +569,10 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   memset(&a, 0, sizeof(a));
   int rc = fill_common(a.base, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
   if (rc) return rc;
-  // blocks = 0: the lean shape that runs next to the backward kernels, at most one CTA per SM
-  // (DDPB_NVLS_MAX_BLOCKS overrides the cap); blocks > 0: the caller owns the GPU and gets the fat shape.
-  static int cap = 0;
-  if (!cap) {
-    const char* c = getenv("DDPB_NVLS_MAX_BLOCKS");
-    const int dflt = (lean_threads() == 64 ? 2 : 1) * sm_count();
-    cap = c ? atoi(c) : dflt;
-    if (cap < 1 || cap > P2P_MAX_BLOCKS) cap = dflt < P2P_MAX_BLOCKS ? dflt : P2P_MAX_BLOCKS;
-  }
+  // blocks = 0: the lean shape that runs next to the backward kernels (see lean_threads);
+  // blocks > 0: the caller owns the GPU and gets the fat shape on the grid it asks for
   const bool lean = blocks <= 0;
-  const long long units = n / 4 / (mode == DDPB_P2P_ONESHOT ? 1 : world);
-  if (lean) {
-    long long want = (units + lean_threads() * 8 - 1) / (lean_threads() * 8);      // >= 2 iterations of 4 units per thread
-    blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
-  }
+  if (lean) blocks = lean_blocks(n / 4 / (mode == DDPB_P2P_ONESHOT ? 1 : world), true);
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "nvls: at most %d blocks", P2P_MAX_BLOCKS);
   a.base.master[rank] = master_local;
   a.base.shadow[rank] = (bf16*)shadow_local;
@@ -572,8 +580,8 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
   a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
   a.one_shot = mode == DDPB_P2P_ONESHOT ? 1 : 0;
   a.base.kflags = kernel_flags(stream, 0);
-  if (lean && lean_threads() == 64) p2p_nvls_kernel<4, 64><<<blocks, 64, 0, stream>>>(a);
-  else if (lean) p2p_nvls_kernel<4, 128><<<blocks, 128, 0, stream>>>(a);
+  if (lean && lean_threads(true) == 128) p2p_nvls_kernel<4, 128><<<blocks, 128, 0, stream>>>(a);
+  else if (lean && lean_threads(true) == 256) p2p_nvls_kernel<4, 256><<<blocks, 256, 0, stream>>>(a);
   else p2p_nvls_kernel<4, 512><<<blocks, 512, 0, stream>>>(a);
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;

@@ -456,6 +456,12 @@ static int loss_fwd(Engine* e, int B, int training, cudaStream_t s) {
   return DDPB_OK;
 }
 
+static bool overlapped(const Engine* e);
+// how many communication streams the step's bucket kernels alternate between
+static int bucket_streams(const Engine* e) {
+  return (e->cfg.world > 1 && e->peers_set && e->two_comm && overlapped(e)) ? 2 : 1;
+}
+
 static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   const auto& c = e->cfg;
   const Bucket& b = e->buckets[bi];
@@ -470,10 +476,12 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   void *g[DDPB_MAX_RANKS], *m[DDPB_MAX_RANKS], *sh[DDPB_MAX_RANKS], *f[DDPB_MAX_RANKS];
   peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
   peer_table(e, e->off_shadow, sh); peer_table(e, e->off_flags, f);
-  // Only the last bucket of the step needs the closing barrier: it is reached after every earlier
-  // bucket kernel of this rank has finished (same stream), so passing it proves that all peers are
-  // done reading our gradients and that all their weight pushes into our arena have landed.
-  const bool last = bi + 1 == (int)e->buckets.size();
+  // Only the last bucket kernel of each communication stream needs the closing barrier: it is reached after
+  // every earlier bucket kernel of that stream on this rank, so passing it proves that all peers are done
+  // reading our gradients of those buckets and that all their weight pushes into our arena have landed.
+  // (Buckets alternate between two streams, see buckets_ready: the last TWO kernels close, and they overlap.)
+  const int nb = (int)e->buckets.size();
+  const bool last = bi + 1 == nb || (bucket_streams(e) == 2 && bi + 2 == nb);
   const int mode = b.mode | (last ? 0 : DDPB_P2P_NO_EXIT_BARRIER);
   const int blocks = 0;     // the launcher's lean shape: it runs next to the backward kernels
   const long long* sh_tab = e->shard.empty() ? nullptr : e->shard.data();
@@ -494,6 +502,69 @@ static int launch_bucket(Engine* e, int bi, cudaStream_t s) {
   return DDPB_OK;
 }
 
+// The captured step graph, before it is instantiated.  The bucket kernels (reduce + SGD) must win the CTA
+// scheduler whenever an SM has room: they are short, and a peer may be waiting inside the same kernel.  The
+// priority of the communication streams is written onto their kernel nodes explicitly here (DDPB_COMM_PRIO=0
+// leaves the nodes as captured); DDPB_GRAPH_DUMP=1 lists every kernel node with its priority, grid and the
+// kernels it depends on.
+static void tune_graph(Engine* e, cudaGraph_t graph) {
+  static const bool dump = getenv("DDPB_GRAPH_DUMP") && atoi(getenv("DDPB_GRAPH_DUMP")) != 0;
+  static const bool set_prio = !(getenv("DDPB_COMM_PRIO") && atoi(getenv("DDPB_COMM_PRIO")) == 0);
+  size_t n = 0;
+  if (cudaGraphGetNodes(graph, nullptr, &n) != cudaSuccess || n == 0) { (void)cudaGetLastError(); return; }
+  std::vector<cudaGraphNode_t> nodes(n);
+  if (cudaGraphGetNodes(graph, nodes.data(), &n) != cudaSuccess) { (void)cudaGetLastError(); return; }
+  auto name_of = [](cudaGraphNode_t nd, cudaKernelNodeParams* kp) -> std::string {
+    cudaGraphNodeType t;
+    if (cudaGraphNodeGetType(nd, &t) != cudaSuccess) { (void)cudaGetLastError(); return "?"; }
+    if (t != cudaGraphNodeTypeKernel) return t == cudaGraphNodeTypeMemset ? "(memset)" : "(other)";
+    cudaKernelNodeParams local;
+    if (!kp) kp = &local;
+    if (cudaGraphKernelNodeGetParams(nd, kp) != cudaSuccess) { (void)cudaGetLastError(); return "?"; }
+    const char* nm = nullptr;
+    if (cudaFuncGetName(&nm, kp->func) != cudaSuccess || !nm) { (void)cudaGetLastError(); return "?"; }
+    return nm;
+  };
+  int lo = 0, hi = 0;
+  cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  for (size_t i = 0; i < n; ++i) {
+    cudaKernelNodeParams kp;
+    memset(&kp, 0, sizeof(kp));
+    const std::string nm = name_of(nodes[i], &kp);
+    if (nm[0] == '(' || nm[0] == '?') continue;
+    const bool comm = nm.find("p2p_") != std::string::npos || nm.find("sgd_") != std::string::npos;
+    cudaKernelNodeAttrValue v;
+    memset(&v, 0, sizeof(v));
+    int before = 0;
+    if (cudaGraphKernelNodeGetAttribute(nodes[i], cudaKernelNodeAttributePriority, &v) == cudaSuccess) before = v.priority;
+    else (void)cudaGetLastError();
+    if (comm && set_prio && e->cfg.world > 1) {
+      v.priority = hi;
+      if (cudaGraphKernelNodeSetAttribute(nodes[i], cudaKernelNodeAttributePriority, &v) != cudaSuccess) (void)cudaGetLastError();
+    }
+    if (dump) {
+      int after = before;
+      if (cudaGraphKernelNodeGetAttribute(nodes[i], cudaKernelNodeAttributePriority, &v) == cudaSuccess) after = v.priority;
+      else (void)cudaGetLastError();
+      fprintf(stderr, "[ddpb graph] %-3zu %-40.40s grid %5u x %-3u prio %d -> %d   after:", i, nm.c_str() + (nm.compare(0, 8, "_ZN4ddpb") == 0 ? 10 : 0),
+              kp.gridDim.x, kp.blockDim.x, before, after);
+      size_t nd = 0;
+      if (cudaGraphNodeGetDependencies_v2(nodes[i], nullptr, nullptr, &nd) == cudaSuccess && nd) {
+        std::vector<cudaGraphNode_t> deps(nd);
+        std::vector<cudaGraphEdgeData> ed(nd);
+        if (cudaGraphNodeGetDependencies_v2(nodes[i], deps.data(), ed.data(), &nd) == cudaSuccess)
+          for (size_t k = 0; k < nd; ++k) {
+            size_t idx = 0;
+            while (idx < n && nodes[idx] != deps[k]) ++idx;
+            fprintf(stderr, " %zu%s", idx, ed[k].type == cudaGraphDependencyTypeProgrammatic ? "p" : "");
+          }
+        else (void)cudaGetLastError();
+      } else (void)cudaGetLastError();
+      fprintf(stderr, "\n");
+    }
+  }
+}
+
 // Is the optimizer / gradient-sync work overlapped with backward?  The bucketed strategy by
 // definition; a single process as well (its optimizer step has no cross-rank dependency, so stepping
 // a layer as soon as its gradients are final is observably identical to stepping after backward).
@@ -511,18 +582,11 @@ static int buckets_ready(Engine* e, int blk, cudaEvent_t ev_a, cudaEvent_t ev_b)
   for (size_t i = 0; i < e->buckets.size(); ++i) {
     if (e->buckets[i].last_block != blk) continue;
     // Multi-GPU: a bucket kernel is mostly NVLink latency (cross-rank barrier, first loads), so two of
-    // them in flight on alternating streams overlap their latencies.  The step's last bucket carries the
-    // closing barrier and therefore has to follow ALL earlier buckets: it runs on `comm` after a join.
-    const bool last = i + 1 == e->buckets.size();
-    const bool multi = e->cfg.world > 1 && e->peers_set && e->two_comm;
-    cudaStream_t cs = (multi && !last && (i & 1)) ? e->comm2 : e->comm;
+    // them in flight on alternating streams overlap their latencies.  Each stream's last kernel carries the
+    // closing barrier for the buckets of its stream (launch_bucket); the step joins both streams at its end.
+    cudaStream_t cs = (bucket_streams(e) == 2 && (i & 1)) ? e->comm2 : e->comm;
     if (ev_a) DDPB_CUDA_CHECK(cudaStreamWaitEvent(cs, ev_a, 0));
     if (ev_b) DDPB_CUDA_CHECK(cudaStreamWaitEvent(cs, ev_b, 0));
-    if (last && e->comm2_used) {
-      DDPB_CUDA_CHECK(cudaEventRecord(e->fork_ev, e->comm2));
-      DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, e->fork_ev, 0));
-      e->comm2_used = false;
-    }
     if (cs == e->comm2) e->comm2_used = true;
     if (e->prof_on) DDPB_CUDA_CHECK(cudaEventRecord(e->prof_ready[i], cs));
     ECHECK(launch_bucket(e, (int)i, cs));
@@ -626,7 +690,7 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
   const bool p2p = c.world > 1 && e->peers_set;
   if (overlapped(e)) {
     // join: the step is complete when every bucket kernel has finished
-    if (e->comm2_used) {       // (the last bucket normally joined it already)
+    if (e->comm2_used) {
       DDPB_CUDA_CHECK(cudaEventRecord(e->fork_ev, e->comm2));
       DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->comm, e->fork_ev, 0));
       e->comm2_used = false;
@@ -721,6 +785,7 @@ static int run_graphed(Engine* e, int kind, int B, cudaStream_t s) {
       return DDPB_OK;
     }
     g.launches = e->counting; g.by_name = e->counting_by_name;
+    tune_graph(e, graph);
     ce = cudaGraphInstantiate(&g.exec, graph, 0);
     cudaGraphDestroy(graph);
     if (ce != cudaSuccess) {
@@ -1011,6 +1076,7 @@ extern "C" int ddpb_engine_trace_step(void* handle, int batch, cudaStream_t s, i
       if (rc) return rc;
       DDPB_REQUIRE(false, "engine_trace_step: capture failed (%s)", cudaGetErrorString(ce));
     }
+    tune_graph(e, graph);
     ce = cudaGraphInstantiate(&exec, graph, 0);
     cudaGraphDestroy(graph);
     DDPB_REQUIRE(ce == cudaSuccess, "engine_trace_step: cudaGraphInstantiate failed (%s)", cudaGetErrorString(ce));

@@ -44,10 +44,20 @@ int pdl_mask() {
 static int g_ktrace_on = 0, g_ktrace_id = 0;
 void ktrace_enable(int on) { g_ktrace_on = on ? 1 : 0; g_ktrace_id = 0; }
 int ktrace_last_id() { return g_ktrace_id; }
-int kernel_flags(cudaStream_t stream, int family) {
-  const int pdl = pdl_active(stream, family) ? 1 : 0;
+int pdl_late_mask() {
+  static int m = -2;
+  if (m == -2) {
+    const char* e = getenv("DDPB_PDL_LATE");
+    m = e ? atoi(e) : DDPB_PDL_LATE_DEFAULT;
+  }
+  return m;
+}
+
+int kernel_flags(cudaStream_t stream, int family, int late_family) {
+  int pdl = pdl_active(stream, family) ? 1 : 0;
+  if (pdl && (pdl_late_mask() & (late_family ? late_family : family))) pdl = 2;       // trigger the successor near the end of the CTA's work
   if (!g_ktrace_on) return pdl;
-  return pdl | (++g_ktrace_id << 1);
+  return pdl | (++g_ktrace_id << 2);
 }
 
 int sm_count() {

@@ -43,6 +43,8 @@ def _worker(rank, world, port, sync, comm, dtype, outdir, plan, b):
     from cs744_ddp_b200.engine import NativeBackend
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
+    if dtype == "fp32":
+        os.environ["DDPB_TF32"] = "0"       # exact fp32 kernels: these tests pin the SYNCHRONISATION arithmetic
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     torch.manual_seed(0)
@@ -104,7 +106,7 @@ def _torch_oracle(world, b, steps=STEPS):
                 model.zero_grad(set_to_none=True)
                 loss = crit(model(x), raw.labels)
                 loss.backward()
-                losses[r].append(float(loss))
+                losses[r].append(float(loss.detach()))
                 g = [p.grad.detach().clone() for p in model.parameters()]
                 acc = g if acc is None else [a + q for a, q in zip(acc, g)]
             for p, a in zip(model.parameters(), acc):
@@ -247,10 +249,15 @@ def test_trainer_fit_writes_a_checkpoint_on_a_multi_gpu_native_run(comm):
     _need(2)
     import json
     import torch.multiprocessing as mp
-    with tempfile.TemporaryDirectory() as d:
-        mp.spawn(_fit_worker, args=(2, _free_port(), d, comm), nprocs=2, join=True)
-        blob = torch.load(os.path.join(d, "ck.pt"), weights_only=True)
-        res = [torch.load(os.path.join(d, f"fit_{r}.pt"), weights_only=False) for r in range(2)]
+    if comm == "auto":
+        os.environ["DDPB_NVLS"] = "1"          # "auto" prefers the unicast kernels between two GPUs: ask for the switch
+    try:
+        with tempfile.TemporaryDirectory() as d:
+            mp.spawn(_fit_worker, args=(2, _free_port(), d, comm), nprocs=2, join=True)
+            blob = torch.load(os.path.join(d, "ck.pt"), weights_only=True)
+            res = [torch.load(os.path.join(d, f"fit_{r}.pt"), weights_only=False) for r in range(2)]
+    finally:
+        os.environ.pop("DDPB_NVLS", None)
     assert len(blob["model"]) == 58 and blob["epoch"] == 1 and len(blob["optimizer"]["state"]) == 34
     for i, st in blob["optimizer"]["state"].items():
         assert torch.equal(st["momentum_buffer"], res[0]["mom"][int(i)])          # the FULL state, not rank 0's shard

@@ -27,7 +27,9 @@ if [[ $WHAT == bench || $WHAT == all ]]; then
   done
 fi
 if [[ $WHAT == bench || $WHAT == all ]]; then
-  CUT=1500 TAILN=1 run bench_w${N}_p3_ours_p2p 600 env DDPB_NVLS=0 $TR --master-port 29650 bench.py --gpus $N --steps ${STEPS:-50} --warmup 10 --part 3
+  # the other transport: unicast P2P where "auto" picked the switch (3+ GPUs), NVLS where it picked unicast (2 GPUs)
+  ALT=0; ALTNAME=p2p; [[ $N == 2 ]] && { ALT=1; ALTNAME=nvls; }
+  CUT=1500 TAILN=1 run bench_w${N}_p3_ours_$ALTNAME 600 env DDPB_NVLS=$ALT $TR --master-port 29650 bench.py --gpus $N --steps ${STEPS:-50} --warmup 10 --part 3
   TAILN=3 run timeline_w$N 300 $TR --master-port 29651 tools/step_timeline.py --out $OUT/step_timeline_w$N.txt
 fi
 echo done
