@@ -63,8 +63,83 @@ def per_gpu_batch(part: str, world: int, override: int = 0) -> int:
 
 
 # ------------------------------------------------------------------------------------------------
-# clocks sampler (nvidia-smi, rank 0 only, during the timed region)
+# clocks sampler (rank 0 only, during the timed region): NVML polled in-process every millisecond - the timed
+# region of a short run is tens of milliseconds, less than one nvidia-smi -lms period - with the recipe's
+# nvidia-smi query as the fall-back when NVML cannot be loaded
 # ------------------------------------------------------------------------------------------------
+class NvmlSampler:
+    """NVML polled every 5 ms by a CHILD process (polling it from a thread of the benchmark process itself cost
+    the launch loop 5-8 % at 4 GPUs: the GIL and the driver lock).  The child is started before the warm-up, so
+    its start-up is outside the timed region; only samples stamped inside [start(), stop()] are kept."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
+    CHILD = r'''
+import sys, time, pynvml as nv
+nv.nvmlInit()
+key = sys.argv[1]
+h = nv.nvmlDeviceGetHandleByUUID(key.encode()) if key.startswith("GPU-") else nv.nvmlDeviceGetHandleByIndex(int(key))
+reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+print("ready", nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM), flush=True)
+while True:
+    print(time.time(), nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), int(reasons(h)), nv.nvmlDeviceGetPowerUsage(h) / 1000.0, flush=True)
+    time.sleep(0.005)
+'''
+
+    def __init__(self, device_index: int = 0) -> None:
+        try:
+            key = "GPU-" + str(torch.cuda.get_device_properties(device_index).uuid)
+        except Exception:
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = visible.split(",") if visible else []
+            key = ids[device_index] if device_index < len(ids) and ids[device_index].isdigit() else str(device_index)
+        self.proc = subprocess.Popen([sys.executable, "-c", self.CHILD, key], stdout=subprocess.PIPE,
+                                     stderr=subprocess.DEVNULL, text=True)
+        first = self.proc.stdout.readline().split()
+        if len(first) != 2 or first[0] != "ready":
+            self.proc.kill()
+            raise RuntimeError("NVML sampler child did not start")
+        self.max_mhz = float(first[1])
+        self.rows = []
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+        self.t0 = self.t1 = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            parts = line.split()
+            if len(parts) == 4:
+                try:
+                    self.rows.append((float(parts[0]), float(parts[1]), int(parts[2]), float(parts[3])))
+                except ValueError:
+                    pass
+
+    def start(self) -> None:
+        self.t0 = time.time()
+
+    def stop(self) -> dict:
+        self.t1 = time.time()
+        time.sleep(0.02)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        self.thread.join(timeout=2)
+        rows = [r for r in self.rows if self.t0 <= r[0] <= self.t1] if self.t0 is not None else []
+        mask = 0
+        for r in rows:
+            mask |= r[2]
+        return {"sm_mhz": statistics.median([r[1] for r in rows]) if rows else None, "sm_max_mhz": self.max_mhz,
+                "reasons": [n for bit, n in self.REASONS if mask & bit], "samples": len(rows),
+                "power_w": round(statistics.median([r[3] for r in rows]), 1) if rows else None, "source": "nvml"}
+
+
+def make_sampler(device_index: int):
+    try:
+        return NvmlSampler(device_index)
+    except Exception:
+        return ClockSampler(device_index)
+
+
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -218,7 +293,7 @@ def run_reference(args) -> dict:
             g = torch.Generator(device="cuda").manual_seed(7 + rank)
             dev_batches = [(torch.randn(PER_GPU_BATCH, 3, 32, 32, device="cuda", generator=g),
                             torch.randint(0, 10, (PER_GPU_BATCH,), device="cuda", generator=g)) for _ in range(4)]
-        sampler = ClockSampler(local) if rank == 0 else None
+        sampler = make_sampler(local) if rank == 0 else None
 
         def loader():
             for i in range(total):
@@ -336,9 +411,9 @@ def run_ours(args) -> dict:
         return last
 
     def timed(e2e):
+        sampler = make_sampler(local) if (rank == 0 and not e2e) else None      # (its start-up: before the warm-up)
         steps(args.warmup, e2e)
         barrier_sync(world)
-        sampler = ClockSampler(local) if (rank == 0 and not e2e) else None
         if sampler:
             sampler.start()
         l0, k0 = be.launch_count(), be.launch_counts()

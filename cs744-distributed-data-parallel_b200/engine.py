@@ -111,7 +111,7 @@ class NativeBackend:
         self.training = True
         # The engine runs on its own stream: the legacy default stream cannot be captured into a
         # CUDA graph.  ``on_stream()`` orders it after/before the caller's current stream.
-        self.stream = torch.cuda.Stream(device)
+        self.stream = torch.cuda.Stream(device, priority=int(os.environ.get("DDPB_PRIO_MAIN", "0")))
         self._lib = lib()
         self._handle = ctypes.c_void_p()
         self._comm = "none"

@@ -295,6 +295,7 @@ struct NvlsArgs {
   float* mc_master;
   bf16* mc_shadow;         // may be null (fp32 compute)
   int one_shot;            // 1: every rank reduces the WHOLE range through the switch and updates its own replica
+  int root;                // 1: rank 0 reduces and updates the whole range and multicasts the result (Part 2a's data flow)
 };
 
 // U units (one 16-byte access each, lanes contiguous) per thread and iteration.  ALL loads of an iteration -
@@ -313,7 +314,8 @@ p2p_nvls_kernel(const NvlsArgs n) {
   const long long nthr = (long long)gridDim.x * THREADS;
   const float inv_w = 1.f / (float)a.world;
   long long lo = 0, hi = n4;
-  if (!n.one_shot) slice_of(n4, a.world, a.rank, &lo, &hi);
+  if (n.root) { if (a.rank != 0) hi = lo; }
+  else if (!n.one_shot) slice_of(n4, a.world, a.rank, &lo, &hi);
   float* const master = a.master[a.rank];
   for (long long i0 = lo + tid; i0 < hi; i0 += nthr * U) {
     float4 s[U], p[U], m[U];
@@ -454,6 +456,15 @@ static int lean_blocks(long long units, bool nvls) {
   return (int)(want < 1 ? 1 : (want > cap ? cap : want));
 }
 
+// blocks < 0: the fat shape (512 threads) on a grid sized by the data - a caller that owns the GPU but has little
+// to move should not pay a 148-CTA cross-GPU barrier (4 MB over 8 GPUs: 65 us with 148 CTAs)
+static int fat_blocks(long long units) {
+  const long long per_cta = 512 * 8;
+  const long long want = (units + per_cta - 1) / per_cta;
+  const int cap = sm_count() < P2P_MAX_BLOCKS ? sm_count() : P2P_MAX_BLOCKS;
+  return (int)(want < 1 ? 1 : (want > cap ? cap : want));
+}
+
 static unsigned long long timeout_ns() {
   static unsigned long long v = 0;
   if (!v) {
@@ -510,9 +521,12 @@ extern "C" int ddpb_p2p_sync_sharded(int mode, void* const* grad, void* const* m
   int rc = fill_common(a, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
   if (rc) return rc;
   // blocks = 0: the lean shape that runs next to the backward kernels (see lean_threads);
-  // blocks > 0: the caller owns the GPU and gets 512-thread CTAs on the grid it asks for
-  const bool lean = blocks <= 0;
-  if (lean) blocks = lean_blocks(n / 4 / ((mode & ~DDPB_P2P_NO_EXIT_BARRIER) == DDPB_P2P_TWOSHOT ? world : 1), false);
+  // blocks > 0: the caller owns the GPU and gets 512-thread CTAs on the grid it asks for; blocks < 0: the same
+  // CTAs on a grid sized by the data (fat_blocks)
+  const bool lean = blocks == 0;
+  const long long units = n / 4 / ((mode & ~DDPB_P2P_NO_EXIT_BARRIER) == DDPB_P2P_TWOSHOT ? world : 1);
+  if (lean) blocks = lean_blocks(units, false);
+  else if (blocks < 0) blocks = fat_blocks(units);
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "p2p: at most %d blocks", P2P_MAX_BLOCKS);
   for (int r = 0; r < world; ++r) {
     a.grad[r] = (float*)grad[r];
@@ -563,22 +577,26 @@ extern "C" int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_mast
                                           const long long* shard, int n_shard, cudaStream_t stream) {
   DDPB_REQUIRE(world >= 2 && world <= P2P_MAX_RANKS && rank >= 0 && rank < world, "nvls: bad rank/world %d/%d", rank,
                world);
-  DDPB_REQUIRE(mode == DDPB_P2P_TWOSHOT || mode == DDPB_P2P_ONESHOT, "nvls: mode must be two-shot or one-shot");
+  DDPB_REQUIRE(mode == DDPB_P2P_TWOSHOT || mode == DDPB_P2P_ONESHOT || mode == DDPB_P2P_ROOT,
+               "nvls: mode must be two-shot, one-shot or root");
   DDPB_REQUIRE(mc_grad && mc_master && master_local && mom && flags, "nvls: null pointer");
   NvlsArgs a;
   memset(&a, 0, sizeof(a));
   int rc = fill_common(a.base, flags, mom, epochs, rank, world, slot, off, n, lr, momentum, wd, shard, n_shard);
   if (rc) return rc;
   // blocks = 0: the lean shape that runs next to the backward kernels (see lean_threads);
-  // blocks > 0: the caller owns the GPU and gets the fat shape on the grid it asks for
-  const bool lean = blocks <= 0;
-  if (lean) blocks = lean_blocks(n / 4 / (mode == DDPB_P2P_ONESHOT ? 1 : world), true);
+  // blocks > 0: the caller owns the GPU and gets the fat shape on the grid it asks for; blocks < 0: fat, grid by size
+  const bool lean = blocks == 0;
+  const long long units = n / 4 / (mode == DDPB_P2P_TWOSHOT ? world : 1);
+  if (lean) blocks = lean_blocks(units, true);
+  else if (blocks < 0) blocks = fat_blocks(units);
   DDPB_REQUIRE(blocks <= P2P_MAX_BLOCKS, "nvls: at most %d blocks", P2P_MAX_BLOCKS);
   a.base.master[rank] = master_local;
   a.base.shadow[rank] = (bf16*)shadow_local;
   a.base.skip_exit_barrier = skip_exit_barrier;
   a.mc_grad = (float*)mc_grad; a.mc_master = (float*)mc_master; a.mc_shadow = (bf16*)mc_shadow;
   a.one_shot = mode == DDPB_P2P_ONESHOT ? 1 : 0;
+  a.root = mode == DDPB_P2P_ROOT ? 1 : 0;
   a.base.kflags = kernel_flags(stream, 0);
   if (lean && lean_threads(true) == 128) p2p_nvls_kernel<4, 128><<<blocks, 128, 0, stream>>>(a);
   else if (lean && lean_threads(true) == 256) p2p_nvls_kernel<4, 256><<<blocks, 256, 0, stream>>>(a);

@@ -83,6 +83,8 @@ struct Engine {
   std::vector<Bucket> buckets;
   std::vector<long long> shard;          // [lo, hi) arena ranges of the conv weights: fp32 master stays with its owner
   bool shard_master = true;              // DDPB_SHARD_MASTER=0: publish the fp32 master of every element
+  bool nvls_after_bwd = true;            // Parts 2a / 2b on a multicast arena: in-switch reduction (DDPB_NVLS_AFTER_BWD=0: unicast)
+  bool fat_after_bwd = true;             // Parts 2a / 2b: 512-thread CTAs, grid by size (DDPB_FAT_AFTER_BWD=0: the in-step shape)
   bool zero_async = true;                // DDPB_ZERO_ASYNC=0: clear the gradients at the start of backward, on its stream
   bool nvls_oneshot = true;              // DDPB_NVLS_ONESHOT=0: small buckets use the unicast one-shot kernel
   cudaStream_t comm = nullptr, comm2 = nullptr, wg = nullptr;
@@ -347,9 +349,19 @@ static int alloc_all(Engine* e) {
   // the bucket kernels are few, small CTAs on the step's critical tail: give them scheduling priority
   int prio_lo = 0, prio_hi = 0;
   DDPB_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-  DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->comm, cudaStreamNonBlocking, prio_hi));
-  DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->comm2, cudaStreamNonBlocking, prio_hi));
-  DDPB_CUDA_CHECK(cudaStreamCreateWithFlags(&e->wg, cudaStreamNonBlocking));
+  // (DDPB_PRIO_COMM / DDPB_PRIO_WG override, clamped to the device's range; the caller's stream is the engine's
+  // main stream: cs744_ddp_b200/engine.py creates it, DDPB_PRIO_MAIN)
+  auto prio_env = [&](const char* name, int dflt) {
+    const char* v = getenv(name);
+    int p = v ? atoi(v) : dflt;
+    if (p < prio_hi) p = prio_hi;
+    if (p > prio_lo) p = prio_lo;
+    return p;
+  };
+  const int prio_comm = prio_env("DDPB_PRIO_COMM", prio_hi), prio_wg = prio_env("DDPB_PRIO_WG", prio_lo);
+  DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->comm, cudaStreamNonBlocking, prio_comm));
+  DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->comm2, cudaStreamNonBlocking, prio_comm));
+  DDPB_CUDA_CHECK(cudaStreamCreateWithPriority(&e->wg, cudaStreamNonBlocking, prio_wg));
   e->ev_dy.resize(c.num_blocks + 1); e->ev_dg.resize(c.num_blocks + 1); e->ev_wg.resize(c.num_blocks + 1);
   for (int i = 0; i <= c.num_blocks; ++i) {
     DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->ev_dy[i], cudaEventDisableTiming));
@@ -703,10 +715,23 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
       void *g[DDPB_MAX_RANKS], *m[DDPB_MAX_RANKS], *sh[DDPB_MAX_RANKS], *f[DDPB_MAX_RANKS];
       peer_table(e, e->off_grad, g); peer_table(e, e->off_master, m);
       peer_table(e, e->off_shadow, sh); peer_table(e, e->off_flags, f);
+      // nothing else runs any more: the fat CTA shape on a grid sized by the data (blocks = -1), and the
+      // in-switch reduction where the arena is bound to a multicast object
       int mode = c.strategy == 1 ? DDPB_P2P_ROOT : DDPB_P2P_TWOSHOT;
-      LAUNCH(e, s, ddpb_p2p_sync_sharded(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1,
-                                         0, e->arena_elems, c.lr, c.momentum, c.wd, 0,
-                                         e->shard.empty() ? nullptr : e->shard.data(), (int)e->shard.size() / 2, s));
+      const long long* sh_tab = e->shard.empty() ? nullptr : e->shard.data();
+      const int n_sh = (int)e->shard.size() / 2;
+      if (e->mc_arena && e->nvls_after_bwd) {
+        char* mc = (char*)e->mc_arena;
+        LAUNCH(e, s, ddpb_p2p_sync_nvls_sharded(mode, mc + e->off_grad, mc + e->off_master,
+                                                dt == DDPB_BF16 ? (void*)(mc + e->off_shadow) : nullptr, e->master,
+                                                dt == DDPB_BF16 ? (void*)e->shadow : nullptr, f, e->mom, e->epochs,
+                                                c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1, 0, e->arena_elems, c.lr,
+                                                c.momentum, c.wd, -1, 0, sh_tab, n_sh, s));
+      } else {
+        LAUNCH(e, s, ddpb_p2p_sync_sharded(mode, g, m, sh, f, e->mom, e->epochs, c.rank, c.world, DDPB_P2P_MAX_SLOTS - 1,
+                                           0, e->arena_elems, c.lr, c.momentum, c.wd, e->fat_after_bwd ? -1 : 0, sh_tab,
+                                           n_sh, s));
+      }
     } else {
       LAUNCH(e, s, ddpb_sgd_step(e->master, e->mom, e->grad, dt == DDPB_BF16 ? (void*)e->shadow : nullptr,
                               e->arena_elems, c.lr, c.momentum, c.wd, 1.f, s));
@@ -834,6 +859,8 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   if (const char* f0 = getenv("DDPB_FUSE_FIRST_BWD")) e->fuse_first_bwd = f0[0] != '0';
   if (const char* tf = getenv("DDPB_TF32")) e->tf32 = tf[0] != '0';
   if (const char* sm = getenv("DDPB_SHARD_MASTER")) e->shard_master = sm[0] != '0';
+  if (const char* v = getenv("DDPB_NVLS_AFTER_BWD")) e->nvls_after_bwd = v[0] != '0';
+  if (const char* v = getenv("DDPB_FAT_AFTER_BWD")) e->fat_after_bwd = v[0] != '0';
   if (const char* za = getenv("DDPB_ZERO_ASYNC")) e->zero_async = za[0] != '0';
   if (const char* no = getenv("DDPB_NVLS_ONESHOT")) e->nvls_oneshot = no[0] != '0';
   int rc = plan_layout(e);

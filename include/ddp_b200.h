@@ -222,7 +222,9 @@ int ddpb_probe_tma(int mode, int stages, int iters, int ctas, int smem_pad_kb, i
  * arenas; pointer tables have `world` entries indexed by rank.  Replaces dist.gather/scatter
  * (ref Part 2a/main.py:117-127), dist.all_reduce + divide (ref Part 2b/main.py:116-119) and DDP's
  * bucket all-reduce / broadcasts (ref Part 3/main.py:61), each fused with optimizer.step()
- * (ref Part 2a/main.py:96).  flags == null disables the cross-rank barriers.  `blocks` = 0 picks. */
+ * (ref Part 2a/main.py:96).  flags == null disables the cross-rank barriers.  `blocks` = 0: the small-footprint
+ * shape that runs next to the backward kernels; > 0: 512-thread CTAs on that grid; < 0: 512-thread CTAs, grid
+ * sized by the data (a caller that owns the GPU). */
 int ddpb_p2p_sync(int mode, void* const* grad, void* const* master, void* const* shadow, void* const* flags,
                   float* mom, void* epochs, int rank, int world, int slot, long long off, long long n, float lr,
                   float momentum, float wd, int blocks, cudaStream_t stream);
@@ -245,7 +247,9 @@ int ddpb_p2p_sync_nvls(void* mc_grad, void* mc_master, void* mc_shadow, float* m
                        float lr, float momentum, float wd, int blocks, int skip_exit_barrier, cudaStream_t stream);
 /* NVLS with sharded ranges (see ddpb_p2p_sync_sharded) and a choice of mode: DDPB_P2P_TWOSHOT as above, or
  * DDPB_P2P_ONESHOT where every rank pulls the switch-reduced sum of the whole range and updates its own
- * replica (master_local / shadow_local) without any store over NVLink - the small buckets. */
+ * replica (master_local / shadow_local) without any store over NVLink - the small buckets; or DDPB_P2P_ROOT
+ * where rank 0 alone reduces and updates the range and multicasts the result (Part 2a's gather -> mean ->
+ * scatter, ref Part 2a/main.py:117-127, as one kernel). */
 int ddpb_p2p_sync_nvls_sharded(int mode, void* mc_grad, void* mc_master, void* mc_shadow, float* master_local,
                                void* shadow_local, void* const* flags, float* mom, void* epochs, int rank, int world,
                                int slot, long long off, long long n, float lr, float momentum, float wd, int blocks,

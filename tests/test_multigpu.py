@@ -208,6 +208,25 @@ def test_nvls_multicast_reduce_matches_nccl_baseline(world):
     _check_against_oracle(got, world, B, f"nvls/w{world}")
 
 
+@pytest.mark.parametrize("world", WORLDS)
+@pytest.mark.parametrize("sync", ["gather_scatter", "allreduce"])
+def test_nvls_after_backward_strategies_match_fp32_torch_oracle(sync, world):
+    """Parts 2a / 2b on the multicast arena: ONE kernel after backward in which the switch reduces
+    (multimem.ld_reduce) - rank 0 alone updates and multicasts (2a, root mode), or every rank its slice (2b)."""
+    _need(world)
+    from cs744_ddp_b200.parallel.vmm import VmmArena
+    if not VmmArena.supported(torch.device("cuda", 0)):
+        pytest.skip("this device/driver does not report multicast support")
+    os.environ["DDPB_NVLS"] = "1"
+    try:
+        got = _run(sync, "auto", world=world)
+    finally:
+        os.environ.pop("DDPB_NVLS", None)
+    if got[0]["comm"] != "nvls":
+        pytest.skip(f"multicast arena could not be set up on this box (fell back to {got[0]['comm']})")
+    _check_against_oracle(got, world, B, f"nvls-{sync}/w{world}")
+
+
 def test_bucketed_bf16_ddp_plan_runs_and_replicas_agree():
     _need(2)
     out = _run("bucketed", "p2p", dtype="bf16", plan="ddp")

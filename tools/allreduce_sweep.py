@@ -69,7 +69,7 @@ def main():
             two = size >= 256 * 1024
             # conv weights (99.85 % of a VGG gradient) publish their bf16 copy only: the swept range is "sharded"
             shard = [0, n] if two else None
-            blocks = big_grid if size >= (4 << 20) else 0
+            blocks = (big_grid if "SWEEP_BLOCKS" in os.environ else -1) if size >= (4 << 20) else 0     # -1: fat CTAs, grid by size
             t_p2p = timed(lambda: arena.sync(nv.P2P_TWOSHOT if two else nv.P2P_ONESHOT, 0, n, 0.1, 0.9, 1e-4,
                                              blocks=blocks, shard=shard), iters, world)
             t_nvls = timed(lambda: arena.sync_nvls(0, n, 0.1, 0.9, 1e-4, blocks=blocks, shard=shard, one_shot=not two),

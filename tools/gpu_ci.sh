@@ -72,6 +72,21 @@ ncufull)
   timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"${NCU_KERNEL:-conv3x3_tc}" -s ${NCU_SKIP:-30} -c ${NCU_COUNT:-3} \
       -o $OUT/prof_${NCU_TAG:-conv} -f python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncufull_run.log 2>&1
   echo "ncufull exit=$?" | tee -a $OUT/summary.log ;;
+ncustep)
+  # ncu --set full over ONE whole eager training step (about 50 launches: every kernel of the step once); the raw
+  # page is exported to CSV on the box and the report itself is dropped when it would not fit the 64 MiB merge limit
+  python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncu_plain.log 2>&1 &&
+  timeout 1200 ncu --set full --clock-control none --kernel-name-base mangled -k regex:ddpb -s ${NCU_SKIP:-150} -c ${NCU_COUNT:-50} \
+      -o $OUT/prof_step -f python bench.py --steps 2 --warmup 3 --no-graph > $OUT/ncustep_run.log 2>&1
+  echo "ncustep exit=$?" | tee -a $OUT/summary.log
+  ncu -i $OUT/prof_step.ncu-rep --page raw --csv > $OUT/ncu_step_raw.csv 2>/dev/null
+  ls -la $OUT/prof_step.ncu-rep | tee -a $OUT/summary.log
+  [ $(stat -c %s $OUT/prof_step.ncu-rep 2>/dev/null || echo 0) -gt 40000000 ] && rm -f $OUT/prof_step.ncu-rep ;;
+benchjson)
+  python bench.py --steps 200 --warmup 20 2>/dev/null | tail -1 > $OUT/bench_n1_ours.json; cut -c1-400 $OUT/bench_n1_ours.json
+  python bench.py --steps 100 --warmup 10 --dtype fp32 2>/dev/null | tail -1 > $OUT/bench_n1_ours_fp32.json; cut -c1-400 $OUT/bench_n1_ours_fp32.json
+  python bench.py 2>/dev/null | tail -1 > $OUT/bench_n1_ours_defaults.json; cut -c1-600 $OUT/bench_n1_ours_defaults.json
+  python bench.py --impl reference --steps 40 --warmup 10 2>/dev/null | tail -1 > $OUT/bench_n1_reference.json; cut -c1-400 $OUT/bench_n1_reference.json ;;
 esac
 done
 grep -h "\[num\]\|\[eng\]" $OUT/t_*.log 2>/dev/null | sort | uniq > $OUT/numerics.log

@@ -11,8 +11,8 @@ if [[ $WHAT == tests || $WHAT == all ]]; then
   # the parametrisations of THIS world size (and the un-parametrised 2-rank tests when N == 2)
   K="$N]"; [[ $N == 2 ]] && K="2] or 2-16 or bf16_ddp or checkpoint"
   [[ $N == 4 ]] && K="4] or 4-64 or 4-16"
-  [[ $N == 8 ]] && K="8-32 or nvls_multicast_reduce_matches_nccl_baseline[8] or random_arrival_order[8]"
-  TAILN=6 run t_multi_w$N 1500 python -m pytest tests/test_multigpu.py -x -q -s -p no:cacheprovider -k "$K"
+  [[ $N == 8 ]] && K="8-32 or nvls_multicast_reduce_matches_nccl_baseline[8] or random_arrival_order[8] or after_backward"
+  TAILN=6 run t_multi_w$N 1500 python -m pytest tests/test_multigpu.py -x -q -s -rs -p no:cacheprovider -k "$K"
 fi
 if [[ $WHAT == sweep || $WHAT == all ]]; then
   TAILN=14 CUT=200 run sweep_w$N 900 $TR --master-port 29541 tools/allreduce_sweep.py
@@ -20,7 +20,7 @@ fi
 if [[ $WHAT == bench || $WHAT == all ]]; then
   p=29600
   for part in ${PARTS:-3 2a 2b}; do
-    for impl in ours reference; do
+    for impl in ${IMPLS:-ours reference}; do
       p=$((p+1))
       CUT=1500 TAILN=1 run bench_w${N}_p${part}_${impl} 600 $TR --master-port $p bench.py --gpus $N --steps ${STEPS:-50} --warmup 10 --part $part --impl $impl
     done
