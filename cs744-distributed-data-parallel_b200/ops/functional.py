@@ -238,6 +238,15 @@ def conv_wgrad_tc(dy, x, split_k: int = 0, out: Optional[torch.Tensor] = None):
     return dw
 
 
+def conv_wgrad_tc_range(dy, x, co_lo: int, co_n: int, out: torch.Tensor, split_k: int = 0):
+    """Weight gradient of output channels [co_lo, co_lo + co_n) only, accumulated into rows co_lo.. of ``out``."""
+    b, h, w_, cout = dy.shape
+    cin = x.shape[3]
+    check(lib().ddpb_conv3x3_wgrad_tc_range(ptr(dy), ptr(x), ptr(out), b, h, w_, cin, cout, co_lo, co_n, split_k,
+                                            stream_handle()), "conv_wgrad_tc_range")
+    return out
+
+
 def first_layer_fwd_tc(x, w_bf16, bias, want_stats: bool = False, generic_kernel: bool = False):
     """conv3x3(3 -> Cout) on the tensor cores: im2col to [pixels][64], then a 1x1 convolution.
     Returns (y, stats | None, cols) - ``cols`` is what the weight gradient needs later."""

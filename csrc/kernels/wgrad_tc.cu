@@ -223,8 +223,9 @@ using namespace ddpb;
 
 // dw (fp32 [Cout,3,3,Cin], KRSC) += dy^T * shifted(x).  dw is ACCUMULATED into (split-K partials
 // and the caller's zeroed gradient arena).  split_k = 0 picks a split that fills ~148 SMs.
-extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
-                                     int Cout, int split_k, cudaStream_t stream) {
+// `dy` points at the first of the `Cout` output channels handled here; dy_pitch = channels per pixel of the dY tensor
+static int wgrad_tc_launch(const void* dy, int dy_pitch, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                           int split_k, cudaStream_t stream) {
   DDPB_REQUIRE(B > 0 && H == W && (H == 32 || H == 16 || H == 8 || H == 4 || H == 2),
                "wgrad_tc: unsupported spatial size %dx%d", H, W);
   DDPB_REQUIRE(Cin % 64 == 0 && Cout % 128 == 0, "wgrad_tc: need Cin %% 64 == 0 and Cout %% 128 == 0 (got %d, %d)",
@@ -234,7 +235,7 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
   CUtensorMap tmDY, tmX, tmW;
   int rc = make_tmap_2d_f32(&tmW, dw, Cout, 9LL * Cin, 32, WG_M);
   if (rc) return rc;
-  rc = make_tmap_nhwc_bf16(&tmDY, dy, B, H, W, Cout, 64, bw, bh, bn);
+  rc = make_tmap_nhwc_bf16(&tmDY, dy, B, H, W, Cout, 64, bw, bh, bn, dy_pitch);
   if (rc) return rc;
   rc = make_tmap_nhwc_bf16(&tmX, x, B, H, W, Cin, 64, bw, bh, bn);
   if (rc) return rc;
@@ -292,6 +293,21 @@ extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, i
 #undef DDPB_WGRAD_LAUNCH
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
+}
+
+extern "C" int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
+                                     int Cout, int split_k, cudaStream_t stream) {
+  return wgrad_tc_launch(dy, Cout, x, dw, B, H, W, Cin, Cout, split_k, stream);
+}
+
+// The same for the output channels [co_lo, co_lo + co_n) only (multiples of 128): rows co_lo.. of dw.  The engine
+// launches a large layer's weight gradient as two such halves so that the first half of the layer's bucket can be
+// reduced across the GPUs while the second half is still being computed (sub-bucket hand-off).
+extern "C" int ddpb_conv3x3_wgrad_tc_range(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
+                                           int Cout, int co_lo, int co_n, int split_k, cudaStream_t stream) {
+  DDPB_REQUIRE(co_lo >= 0 && co_n > 0 && co_lo % 128 == 0 && co_n % 128 == 0 && co_lo + co_n <= Cout,
+               "wgrad_tc_range: bad channel range [%d, %d) of %d", co_lo, co_lo + co_n, Cout);
+  return wgrad_tc_launch((const bf16*)dy + co_lo, Cout, x, dw + (size_t)co_lo * 9 * Cin, B, H, W, Cin, co_n, split_k, stream);
 }
 
 // dw (fp32 [64][ld], columns < cols) += dy[pixels][64]^T * x[pixels][64]: the first layer's weight

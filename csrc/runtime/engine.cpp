@@ -48,7 +48,10 @@ struct Block {
   void* win = nullptr;   // pooling blocks, bf16 tensor-core path: conv output that won each pool window (NaN = none)
 };
 
-struct Bucket { long long off, numel; int last_block; int mode; };   // last_block: -1 = classifier
+struct Bucket {
+  long long off, numel; int last_block; int mode;   // last_block: -1 = classifier
+  int part, parts;       // sub-bucket hand-off: this is part `part` of `parts` of its layer (output-channel ranges of the conv weight)
+};
 
 typedef std::map<std::string, long long> NameCounts;
 struct Graph { cudaGraphExec_t exec = nullptr; long long launches = 0; NameCounts by_name; };
@@ -83,6 +86,10 @@ struct Engine {
   std::vector<Bucket> buckets;
   std::vector<long long> shard;          // [lo, hi) arena ranges of the conv weights: fp32 master stays with its owner
   bool shard_master = true;              // DDPB_SHARD_MASTER=0: publish the fp32 master of every element
+  int sub_buckets = 1;                   // DDPB_SUB_BUCKETS=2|4: split the large layers' buckets by output-channel range
+  long long sub_bucket_min = 1 << 20;    // ... layers with at least this many weight elements (DDPB_SUB_BUCKET_MIN)
+  bool sub_bucket_force = false;         // DDPB_SUB_BUCKETS_FORCE=1: also on one GPU (tests)
+  std::vector<cudaEvent_t> ev_part;      // [block][part] weight-gradient part complete
   bool nvls_after_bwd = true;            // Parts 2a / 2b on a multicast arena: in-switch reduction (DDPB_NVLS_AFTER_BWD=0: unicast)
   bool fat_after_bwd = true;             // Parts 2a / 2b: 512-thread CTAs, grid by size (DDPB_FAT_AFTER_BWD=0: the in-step shape)
   bool zero_async = true;                // DDPB_ZERO_ASYNC=0: clear the gradients at the start of backward, on its stream
@@ -214,7 +221,7 @@ static void plan_buckets(Engine* e) {
     add(b.bn_w, i); add(b.bn_b, i); add(b.conv_w, i); add(b.conv_b, i);
   }
   e->buckets.clear();
-  auto close = [&](long long off, long long end, int last) { e->buckets.push_back({off, end - off, last, 0}); };
+  auto close = [&](long long off, long long end, int last) { e->buckets.push_back({off, end - off, last, 0, 0, 1}); };
   if (c.bucket_plan == 2) {
     close(0, e->arena_elems, 0);
   } else if (c.bucket_plan == 1) {
@@ -240,6 +247,29 @@ static void plan_buckets(Engine* e) {
         start = items[i].end; acc = 0; limit = c.bucket_cap_mb * mib;
       }
     }
+  }
+  // Sub-bucket hand-off (per-layer plan): a large layer's bucket is cut at output-channel boundaries of its conv
+  // weight ([co][3][3][ci] in the arena, so a channel range is contiguous); backward() launches that layer's
+  // weight gradient once per range and hands each part to the communication streams as soon as it exists, so the
+  // reduce of the first half runs while the second half is still being computed (DDP cannot go below a bucket).
+  if (c.bucket_plan == 1 && e->sub_buckets > 1 && (c.world > 1 || e->sub_bucket_force)) {
+    std::vector<Bucket> out;
+    for (const Bucket& bk : e->buckets) {
+      const int S = e->sub_buckets;
+      const Block* blk = bk.last_block >= 0 ? &e->blocks[bk.last_block] : nullptr;
+      const bool ok = blk && c.dtype == DDPB_BF16 && c.use_tc && blk->cin % 64 == 0 && blk->cout % (128 * S) == 0 &&
+                      blk->conv_w.numel >= e->sub_bucket_min && blk->conv_w.off >= bk.off &&
+                      blk->conv_w.off + blk->conv_w.numel <= bk.off + bk.numel;
+      if (!ok) { out.push_back(bk); continue; }
+      const long long per = blk->conv_w.numel / S;
+      long long lo = bk.off;
+      for (int p = 0; p < S; ++p) {
+        const long long hi = p + 1 == S ? bk.off + bk.numel : blk->conv_w.off + per * (p + 1);
+        out.push_back({lo, hi - lo, bk.last_block, 0, p, S});
+        lo = hi;
+      }
+    }
+    e->buckets.swap(out);
   }
   for (auto& b : e->buckets)
     b.mode = (c.world > 1 && b.numel * 4 >= 256 * 1024) ? DDPB_P2P_TWOSHOT : DDPB_P2P_ONESHOT;
@@ -368,6 +398,8 @@ static int alloc_all(Engine* e) {
     DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->ev_dg[i], cudaEventDisableTiming));
     DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->ev_wg[i], cudaEventDisableTiming));
   }
+  e->ev_part.resize((size_t)c.num_blocks * 4);
+  for (auto& ev : e->ev_part) DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   e->bucket_ev.resize(e->buckets.size());
   for (auto& ev : e->bucket_ev) DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   DDPB_CUDA_CHECK(cudaEventCreateWithFlags(&e->join_ev, cudaEventDisableTiming));
@@ -586,13 +618,21 @@ static bool overlapped(const Engine* e) {
   return c.strategy == 3 || c.world == 1;
 }
 
+// into how many output-channel parts backward() cuts the weight gradient of block `blk` (see plan_buckets)
+static int layer_parts(const Engine* e, int blk) {
+  for (const Bucket& b : e->buckets)
+    if (b.last_block == blk) return b.parts;
+  return 1;
+}
+
 // Block `blk` (-1 = classifier) is complete: its gradients have been produced (event ev_a) and every
 // reader of its current weights has run (event ev_b).  Hand each bucket that ends with this block to
 // the communication stream, where its fused reduce + optimizer kernel overlaps the rest of backward.
-static int buckets_ready(Engine* e, int blk, cudaEvent_t ev_a, cudaEvent_t ev_b) {
+static int buckets_ready(Engine* e, int blk, cudaEvent_t ev_a, cudaEvent_t ev_b, int part = -1) {
   if (!overlapped(e)) return DDPB_OK;
   for (size_t i = 0; i < e->buckets.size(); ++i) {
     if (e->buckets[i].last_block != blk) continue;
+    if (part >= 0 && e->buckets[i].part != part) continue;
     // Multi-GPU: a bucket kernel is mostly NVLink latency (cross-rank barrier, first loads), so two of
     // them in flight on alternating streams overlap their latencies.  Each stream's last kernel carries the
     // closing barrier for the buckets of its stream (launch_bucket); the step joins both streams at its end.
@@ -682,6 +722,19 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
     }
     DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[i], s));
     DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->ev_dy[i], 0));
+    const int parts = overlapped(e) ? layer_parts(e, i) : 1;
+    if (parts > 1 && use_tc_wgrad(e, b)) {
+      // sub-bucket hand-off: one launch per output-channel range, each part's bucket leaves as soon as it exists
+      const int cn = b.cout / parts;
+      for (int p = 0; p < parts; ++p) {
+        LAUNCH(e, e->wg, ddpb_conv3x3_wgrad_tc_range(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, p * cn,
+                                                     cn, 0, e->wg));
+        cudaEvent_t ev = p + 1 == parts ? e->ev_wg[i] : e->ev_part[(size_t)i * 4 + p];
+        DDPB_CUDA_CHECK(cudaEventRecord(ev, e->wg));
+        ECHECK(buckets_ready(e, i, ev, e->ev_dg[i], p));
+      }
+      continue;
+    }
     if (use_tc_wgrad(e, b))
       LAUNCH(e, e->wg, ddpb_conv3x3_wgrad_tc(dy, x_in, e->grad + b.conv_w.off, B, b.hw, b.hw, b.cin, b.cout, 0, e->wg));
     else if (use_tf32(e, b) && b.cout % 128 == 0)
@@ -859,6 +912,9 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   if (const char* f0 = getenv("DDPB_FUSE_FIRST_BWD")) e->fuse_first_bwd = f0[0] != '0';
   if (const char* tf = getenv("DDPB_TF32")) e->tf32 = tf[0] != '0';
   if (const char* sm = getenv("DDPB_SHARD_MASTER")) e->shard_master = sm[0] != '0';
+  if (const char* v = getenv("DDPB_SUB_BUCKETS")) { const int n = atoi(v); e->sub_buckets = (n == 2 || n == 4) ? n : 1; }
+  if (const char* v = getenv("DDPB_SUB_BUCKET_MIN")) { const long long n = atoll(v); if (n > 0) e->sub_bucket_min = n; }
+  if (const char* v = getenv("DDPB_SUB_BUCKETS_FORCE")) e->sub_bucket_force = v[0] == '1';
   if (const char* v = getenv("DDPB_NVLS_AFTER_BWD")) e->nvls_after_bwd = v[0] != '0';
   if (const char* v = getenv("DDPB_FAT_AFTER_BWD")) e->fat_after_bwd = v[0] != '0';
   if (const char* za = getenv("DDPB_ZERO_ASYNC")) e->zero_async = za[0] != '0';
@@ -892,6 +948,7 @@ extern "C" int ddpb_engine_destroy(void* handle) {
   for (auto& ev : e->ev_dy) cudaEventDestroy(ev);
   for (auto& ev : e->ev_dg) cudaEventDestroy(ev);
   for (auto& ev : e->ev_wg) cudaEventDestroy(ev);
+  for (auto& ev : e->ev_part) cudaEventDestroy(ev);
   if (e->comm) cudaStreamDestroy(e->comm);
   if (e->comm2) cudaStreamDestroy(e->comm2);
   if (e->wg) cudaStreamDestroy(e->wg);

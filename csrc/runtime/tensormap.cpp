@@ -126,13 +126,14 @@ static int encode(CUtensorMap* out, const void* ptr, int rank, const cuuint64_t*
 }
 
 int make_tmap_nhwc_bf16(CUtensorMap* out, const void* ptr, int N, int H, int W, int C, int box_c, int box_w,
-                        int box_h, int box_n) {
-  if (box_c != 64 || C % 64 != 0) {
-    set_last_error("tensor map: channel box must be 64 and C a multiple of 64 (C=%d box=%d)", C, box_c);
+                        int box_h, int box_n, int c_pitch) {
+  if (c_pitch <= 0) c_pitch = C;          // c_pitch > C: a channel range [ptr .. ptr + C) of a wider tensor
+  if (box_c != 64 || C % 64 != 0 || c_pitch % 8 != 0 || c_pitch < C) {
+    set_last_error("tensor map: channel box must be 64 and C a multiple of 64 (C=%d box=%d pitch=%d)", C, box_c, c_pitch);
     return DDPB_ERR_ARG;
   }
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint64_t strides[3] = {(cuuint64_t)c_pitch * 2, (cuuint64_t)W * c_pitch * 2, (cuuint64_t)H * W * c_pitch * 2};
   cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)box_w, (cuuint32_t)box_h, (cuuint32_t)box_n};
   return encode(out, ptr, 4, dims, strides, box);
 }

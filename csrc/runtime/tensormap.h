@@ -9,7 +9,7 @@ namespace ddpb {
 // NHWC bf16 activation tensor seen as 4-D (C, W, H, N); box = (box_c, box_w, box_h, box_n) elements,
 // 128-byte swizzle (box_c must be 64), out-of-bounds elements read as zero.
 int make_tmap_nhwc_bf16(CUtensorMap* out, const void* ptr, int N, int H, int W, int C, int box_c, int box_w,
-                        int box_h, int box_n);
+                        int box_h, int box_n, int c_pitch = 0);      // c_pitch: elements between pixels (0 = C)
 
 // Row-major bf16 matrix [rows][cols]; box = box_cols (must be 64) x box_rows, 128-byte swizzle.
 int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, long long rows, long long cols, int box_cols,

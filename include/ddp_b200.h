@@ -170,6 +170,11 @@ int ddpb_conv3x3_dgrad_bnred_tc(const void* dy, const void* w_bf16, void* dx, in
 /* dw (fp32 KRSC) accumulates. */
 int ddpb_conv3x3_wgrad_tc(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
                           int split_k, cudaStream_t stream);
+/* The same for the output channels [co_lo, co_lo + co_n) only (both multiples of 128): rows co_lo.. of dw.  Lets a
+ * caller hand the first part of a layer's gradient to the communication stream while the rest is still being
+ * computed (the engine's sub-bucket hand-off; DDP has no counterpart below bucket granularity). */
+int ddpb_conv3x3_wgrad_tc_range(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                                int co_lo, int co_n, int split_k, cudaStream_t stream);
 
 /* First layer (Cin = 3) on the tensor cores: its 3x3x3 patches are laid out as a [B*H*W][64] bf16
  * matrix (27 real columns), after which forward is a 1x1 convolution and the weight gradient a plain

@@ -288,6 +288,27 @@ def test_conv_tc_wgrad(F, R, b, hw, cin, cout, split_k):
     _report(f"tc_wgrad hw{hw} {cin}->{cout} b{b} s{split_k}", dw, R.conv_wgrad(dy, x), 2e-3)
 
 
+@pytest.mark.parametrize("hw,cin,cout", [(4, 256, 512), (2, 512, 512), (8, 128, 256)])
+def test_conv_tc_wgrad_by_channel_range(F, R, hw, cin, cout):
+    """The engine's sub-bucket hand-off computes a layer's weight gradient as output-channel halves: the halves
+    must fill disjoint rows of dW and together equal the one-launch result (fp64 reference)."""
+    torch.manual_seed(6)
+    b = 16
+    dy = torch.randn(b, hw, hw, cout, device=DEV).to(torch.bfloat16)
+    x = torch.randn(b, hw, hw, cin, device=DEV).to(torch.bfloat16)
+    dw = torch.zeros((cout, 3, 3, cin), dtype=torch.float32, device=DEV)
+    half = cout // 2
+    F.conv_wgrad_tc_range(dy, x, 0, half, dw)
+    torch.cuda.synchronize()
+    assert dw[half:].abs().max().item() == 0                      # the second half's rows are untouched so far
+    _report(f"tc_wgrad range lo hw{hw} {cin}->{cout}", dw[:half], R.conv_wgrad(dy, x)[:half], 2e-3)
+    F.conv_wgrad_tc_range(dy, x, half, half, dw)
+    torch.cuda.synchronize()
+    _report(f"tc_wgrad range all hw{hw} {cin}->{cout}", dw, R.conv_wgrad(dy, x), 2e-3)
+    with pytest.raises(Exception):
+        F.conv_wgrad_tc_range(dy, x, 64, half, dw)                # not a multiple of 128
+
+
 @pytest.mark.parametrize("b", [16, 5, 37])
 @pytest.mark.parametrize("cout", [64, 128])
 @pytest.mark.parametrize("generic", [False, True])
