@@ -268,6 +268,21 @@ def first_layer_fwd_tc(x, w_bf16, bias, want_stats: bool = False, generic_kernel
     return y, stats, cols
 
 
+def im2col3x3_c3(x, w_bf16, zero_pad: bool = True, cols: Optional[torch.Tensor] = None):
+    """Patch matrix [pixels][64] (27 real columns) of a 3-channel NHWC image and the zero-padded [Cout][64] weight
+    matrix.  ``zero_pad=False`` leaves columns 32..63 alone (the engine's mode: it clears them once; a 32 x 32 image
+    then takes the eight-rows-per-CTA kernel) - pass a ``cols`` buffer whose upper half is already zero."""
+    b, h, w_, cin = x.shape
+    assert cin == 3 and x.dtype == torch.bfloat16
+    cout = w_bf16.shape[0]
+    if cols is None:
+        cols = (torch.empty if zero_pad else torch.zeros)((b, h, w_, 64), dtype=torch.bfloat16, device=x.device)
+    w_pad = torch.empty((cout, 64), dtype=torch.bfloat16, device=x.device)
+    check(lib().ddpb_im2col3x3_c3(ptr(x), ptr(w_bf16), ptr(cols), ptr(w_pad), b, h, w_, cout, 1 if zero_pad else 0,
+                                  stream_handle()), "im2col3x3_c3")
+    return cols, w_pad
+
+
 def first_layer_wgrad_tc(dy, cols, split_k: int = 0):
     b, h, w_, cout = dy.shape
     dw = torch.zeros((cout, 3, 3, 3), dtype=torch.float32, device=dy.device)

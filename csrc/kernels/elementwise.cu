@@ -191,6 +191,56 @@ im2col3x3_c3_row32_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w
   ktrace_end(pdl);
 }
 
+// W == 32, H % 8 == 0, columns 32..63 already zero: one block = EIGHT image rows.  Ten input rows are staged with
+// 4-byte loads, then all 256 threads write four 16-byte segments each (the one-row kernel above starts 8192 CTAs of
+// which half the threads exit at once; per-CTA staging and the barrier dominated its 15 us).
+constexpr int IM2_ROWS = 8;
+constexpr int IM2_PITCH = 104;          // 1 pad + pixel -1 (3) + 32 pixels (96) + pixel 32 (3) + 1: rows stay 4-byte aligned
+__global__ void __launch_bounds__(256)
+im2col3x3_c3_rows8_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ cols,
+                          bf16* __restrict__ w_pad, int H, int Cout, int pdl) {
+  ktrace_begin(pdl);
+  if (pdl & 1) pdl_launch_dependents();     // launched normally itself (it follows the scratch memset)
+  __shared__ __align__(16) unsigned short rows[IM2_ROWS + 2][IM2_PITCH];
+  const int tid = threadIdx.x;
+  const long long gi = (long long)blockIdx.x * 256 + tid;
+  if (gi < (long long)Cout * 8) {
+    const int co = (int)(gi >> 3), seg = (int)(gi & 7);
+    const unsigned short* ws = reinterpret_cast<const unsigned short*>(w) + co * 27;
+    unsigned short v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { const int k = seg * 8 + j; v[j] = k < 27 ? ws[k] : (unsigned short)0; }
+    reinterpret_cast<uint4*>(w_pad)[gi] = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+  }
+  const long long row0 = (long long)blockIdx.x * IM2_ROWS;          // (n, h0): first of this block's image rows
+  const int h0 = (int)(row0 & (long long)(H - 1));
+  const uint32_t* x32 = reinterpret_cast<const uint32_t*>(x);        // one image row = 96 bf16 = 48 words
+  for (int i = tid; i < (IM2_ROWS + 2) * 48; i += 256) {
+    const int r = i / 48, e = i - r * 48;
+    const int yy = h0 + r - 1;
+    const uint32_t v = (yy >= 0 && yy < H) ? x32[(row0 + r - 1) * 48 + e] : 0u;
+    *reinterpret_cast<uint32_t*>(&rows[r][4 + 2 * e]) = v;           // pixel p, channel c at [4 + 3 p + c]
+  }
+  if (tid < (IM2_ROWS + 2) * 6) { const int r = tid / 6, e = tid - r * 6; rows[r][e < 3 ? 1 + e : 100 + (e - 3)] = 0; }   // pixels -1 and 32
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < IM2_ROWS * 32 * 4 / 256; ++it) {
+    const int item = it * 256 + tid;
+    const int seg = item & 3, wx = (item >> 2) & 31, rl = item >> 7;
+    unsigned short v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = seg * 8 + j;
+      const int tap = k / 3, c = k - tap * 3;
+      const int r = tap / 3, s2 = tap - r * 3;
+      v[j] = k < 27 ? rows[rl + r][1 + (wx + s2) * 3 + c] : (unsigned short)0;
+    }
+    reinterpret_cast<uint4*>(cols)[((row0 + rl) * 32 + wx) * 8 + seg] =
+        make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+  }
+  ktrace_end(pdl);
+}
+
 static int grid_for(long long n, int block, int cap = 0) {
   if (cap <= 0) cap = sm_count() * 16;
   long long g = (n + block - 1) / block;
@@ -273,6 +323,13 @@ extern "C" int ddpb_im2col3x3_c3(const void* x, const void* w_bf16, void* cols, 
   while ((1 << w_shift) < W) ++w_shift;
   DDPB_REQUIRE(n_seg >= (long long)Cout * 8, "im2col3x3_c3: fewer pixels than output channels");
   const long long blocks = (n_seg + 255) / 256;
+  static const bool rows8 = !(getenv("DDPB_IM2COL_ROWS8") && atoi(getenv("DDPB_IM2COL_ROWS8")) == 0);
+  if (W == 32 && !zero_pad && rows8 && H % IM2_ROWS == 0 && (long long)B * H / IM2_ROWS * 256 >= (long long)Cout * 8) {
+    im2col3x3_c3_rows8_kernel<<<(unsigned)((long long)B * H / IM2_ROWS), 256, 0, stream>>>(
+        (const bf16*)x, (const bf16*)w_bf16, (bf16*)cols, (bf16*)w_pad, H, Cout, kernel_flags(stream, 64));
+    DDPB_LAUNCH_CHECK();
+    return DDPB_OK;
+  }
   if (W == 32) {
     im2col3x3_c3_row32_kernel<<<(unsigned)((long long)B * H), 256, 0, stream>>>((const bf16*)x, (const bf16*)w_bf16, (bf16*)cols,
                                                                                (bf16*)w_pad, H, h_shift, Cout, zero_pad, kernel_flags(stream, 64));

@@ -288,6 +288,27 @@ def test_conv_tc_wgrad(F, R, b, hw, cin, cout, split_k):
     _report(f"tc_wgrad hw{hw} {cin}->{cout} b{b} s{split_k}", dw, R.conv_wgrad(dy, x), 2e-3)
 
 
+@pytest.mark.parametrize("b", [1, 5, 16, 37])
+def test_im2col_eight_rows_per_cta_matches_the_one_row_kernel(F, b):
+    """The engine's im2col (columns 32..63 pre-cleared, eight image rows per CTA) against the zero-padding one-row
+    kernel: bit-identical patch matrix and weight matrix, and against an unfold of the image."""
+    torch.manual_seed(21)
+    x = torch.randn(b, 32, 32, 3, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(64, 3, 3, 3, device=DEV) * 0.2).to(torch.bfloat16)
+    ref_cols, ref_w = F.im2col3x3_c3(x, w, zero_pad=True)
+    cols, w_pad = F.im2col3x3_c3(x, w, zero_pad=False)
+    torch.cuda.synchronize()
+    assert torch.equal(cols, ref_cols) and torch.equal(w_pad, ref_w)
+    # independent oracle: column k = (r * 3 + s) * 3 + c holds x[n, h + r - 1, w + s - 1, c]
+    pad = torch.nn.functional.pad(x.float().permute(0, 3, 1, 2), (1, 1, 1, 1))
+    for r in range(3):
+        for s_ in range(3):
+            want = pad[:, :, r:r + 32, s_:s_ + 32].permute(0, 2, 3, 1)
+            k = (r * 3 + s_) * 3
+            assert torch.equal(cols[..., k:k + 3].float(), want), (r, s_)
+    assert cols[..., 27:].abs().max().item() == 0
+
+
 @pytest.mark.parametrize("hw,cin,cout", [(4, 256, 512), (2, 512, 512), (8, 128, 256)])
 def test_conv_tc_wgrad_by_channel_range(F, R, hw, cin, cout):
     """The engine's sub-bucket hand-off computes a layer's weight gradient as output-channel halves: the halves
