@@ -356,7 +356,16 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const vo
                "r"(smem_u32(smem)), "r"(c0), "r"(c1)
                : "memory");
 }
+// global[0 .. bytes) += smem[0 .. bytes) as ONE bulk operation (fp32 adds performed in L2); both addresses 16-byte
+// aligned, bytes a multiple of 16.  Replaces bytes / 4 separate RED instructions.
+__device__ __forceinline__ void bulk_reduce_add_f32(float* gmem, const void* smem, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gmem), "r"(smem_u32(smem)),
+               "r"(bytes)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// wait until the bulk stores / reductions of this thread are complete (not only their shared-memory reads)
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // wait until the bulk stores of this thread have finished READING shared memory
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 

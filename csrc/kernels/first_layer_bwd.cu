@@ -41,7 +41,8 @@ struct FirstBwdParams {
   const float *mean, *invstd, *gamma, *beta, *sums;
   float *dw, *dgamma, *dbeta, *dbias;
   int ld, cols;            // dw row pitch and number of real patch columns (27)
-  int flags;               // launch flags (common.cuh): bit 0 programmatic launch, bits 1.. trace id
+  int flags;               // launch flags (common.cuh): bits 0-1 programmatic launch trigger, bits 2.. trace id
+  int bulk_add;            // 1: dw is contiguous (ld == cols), 16-byte aligned: one bulk reduce-add per CTA
 };
 
 __global__ void __launch_bounds__(192)
@@ -193,7 +194,24 @@ first_layer_bwd_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_con
       float acc[32];
       tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16), acc);
       tmem_ld_wait();
-      if (lane < 16) {
+      if (prm.bulk_add) {
+        // the 64 x cols partial result goes to the gradient arena as ONE bulk reduce-add from shared memory (every
+        // stage of the ring is free by now: the accumulator barrier follows the last MMA) instead of 64 x cols
+        // RED instructions per CTA - 296 CTAs x 1728 atomics on the same 54 lines throttled the LSU
+        float* stg = reinterpret_cast<float*>(smem);
+        if (lane < 16) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < prm.cols) stg[(q * 16 + lane) * prm.cols + j] = acc[j];
+        }
+        fence_async_proxy();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (t == 0) {
+          bulk_reduce_add_f32(prm.dw, stg, (uint32_t)(FL_C * prm.cols * 4));
+          tma_store_commit();
+          tma_store_wait_all();
+        }
+      } else if (lane < 16) {
         float* dst = prm.dw + (size_t)(q * 16 + lane) * prm.ld;
 #pragma unroll
         for (int j = 0; j < 32; ++j)
@@ -239,6 +257,8 @@ extern "C" int ddpb_first_layer_bwd_fused(const void* dout, const void* y, const
   prm.mean = save_mean; prm.invstd = save_invstd; prm.gamma = gamma; prm.beta = beta; prm.sums = sums;
   prm.dw = dw; prm.dgamma = dgamma; prm.dbeta = dbeta; prm.dbias = dbias;
   prm.ld = ld; prm.cols = cols;
+  static const bool bulk_ok = !(getenv("DDPB_FL_BULK") && atoi(getenv("DDPB_FL_BULK")) == 0);
+  prm.bulk_add = (bulk_ok && ld == cols && (FL_C * cols * 4) % 16 == 0 && reinterpret_cast<uintptr_t>(dw) % 16 == 0) ? 1 : 0;
   // everything streams from HBM once: two CTAs per SM keep ~140 KB of loads in flight per SM
   if (ctas <= 0) ctas = 2 * sm_count();
   if (ctas > prm.chunks) ctas = (int)prm.chunks;
