@@ -10,7 +10,7 @@
 // it back, and sat one after the other at the very end of the step, where nothing overlaps them.  Here dY
 // never leaves the SM:
 //   warp 0      TMA: per chunk of 64 pixels (two image rows = 16 complete pool windows) the conv output y,
-//               the pooled incoming gradient and the patch-matrix tile, 4 stages deep
+//               the pooled incoming gradient and the patch-matrix tile, 2 stages deep (template parameter)
 //   warps 2-5   one thread per (pool window, 8 channels): recomputes the ReLU / arg-max routing from y,
 //               applies dy = sc * dz + cb - cy * y and writes the 64 x 64 bf16 tile straight into shared
 //               memory in the 128-byte-swizzled MN-major layout tcgen05.mma reads (what TMA would have
@@ -27,7 +27,7 @@ namespace ddpb {
 constexpr int FL_C = 64;                 // channels of block 0
 constexpr int FL_PIX = 64;               // pixels per chunk: two rows of a 32-wide image
 constexpr int FL_WIN = 16;               // pool windows per chunk
-constexpr int FL_STAGES = 4;
+constexpr int FL_STAGES_DEFAULT = 2;     // pipeline depth ST of the kernel template (DDPB_FL_STAGES = 2 | 3 | 4)
 constexpr int FL_Y = FL_PIX * 128;       // y tile: 64 rows x 128 B
 constexpr int FL_D = FL_WIN * 128;       // pooled gradient tile: 16 rows x 128 B
 constexpr int FL_X = FL_PIX * 128;       // patch tile: 64 rows x 128 B
@@ -45,6 +45,7 @@ struct FirstBwdParams {
   int bulk_add;            // 1: dw is contiguous (ld == cols), 16-byte aligned: one bulk reduce-add per CTA
 };
 
+template <int FL_STAGES>
 __global__ void __launch_bounds__(192)
 first_layer_bwd_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmD,
                        const __grid_constant__ CUtensorMap tmX, const FirstBwdParams prm) {
@@ -259,19 +260,38 @@ extern "C" int ddpb_first_layer_bwd_fused(const void* dout, const void* y, const
   prm.ld = ld; prm.cols = cols;
   static const bool bulk_ok = !(getenv("DDPB_FL_BULK") && atoi(getenv("DDPB_FL_BULK")) == 0);
   prm.bulk_add = (bulk_ok && ld == cols && (FL_C * cols * 4) % 16 == 0 && reinterpret_cast<uintptr_t>(dw) % 16 == 0) ? 1 : 0;
-  // everything streams from HBM once: two CTAs per SM keep ~140 KB of loads in flight per SM
-  if (ctas <= 0) ctas = 2 * sm_count();
-  if (ctas > prm.chunks) ctas = (int)prm.chunks;
-  constexpr int smem = FL_STAGES * FL_STAGE + FL_ABUF * FL_A + (2 * FL_STAGES + 2 * FL_ABUF + 1) * 8 + 16 +
-                       FL_WIN * FL_C * 4 + 1024;
-  static unsigned long long configured = 0;
-  if (first_on_device(&configured)) {
-    DDPB_CUDA_CHECK(cudaFuncSetAttribute(first_layer_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    DDPB_CUDA_CHECK(cudaFuncSetAttribute(first_layer_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                         cudaSharedmemCarveoutMaxShared));
+  // Everything streams from HBM once.  Measured in the step (bench.py, 200 steps; stages x CTAs per SM): 4 x 2
+  // 0.5111 ms, 3 x 2 0.5109, 2 x 2 0.5080, 2 x 3 0.5092, 2 x 4 0.5065 - the transform warps, not the loads, are the
+  // bottleneck, so more (smaller) CTAs win: two stages (58 KB, three CTAs resident per SM) and a grid of 4 per SM.
+  // DDPB_FL_STAGES / DDPB_FL_PER_SM override.
+  static int stages = 0, per_sm = 0;
+  if (!stages) {
+    const char* e = getenv("DDPB_FL_STAGES");
+    stages = e ? atoi(e) : FL_STAGES_DEFAULT;
+    if (stages < 2 || stages > 4) stages = FL_STAGES_DEFAULT;
+    const char* q = getenv("DDPB_FL_PER_SM");
+    per_sm = q ? atoi(q) : 4;
+    if (per_sm < 1 || per_sm > 4) per_sm = 4;
   }
+  if (ctas <= 0) ctas = per_sm * sm_count();
+  if (ctas > prm.chunks) ctas = (int)prm.chunks;
   prm.flags = kernel_flags(stream, 16);
-  DDPB_CUDA_CHECK(launch_ex(first_layer_bwd_kernel, dim3(ctas), dim3(192), smem, stream, dim3(1, 1, 1), 16, tmY, tmD, tmX, prm));
+#define DDPB_FL_LAUNCH(ST)                                                                                            \
+  do {                                                                                                                \
+    constexpr int smem = ST * FL_STAGE + FL_ABUF * FL_A + (2 * ST + 2 * FL_ABUF + 1) * 8 + 16 + FL_WIN * FL_C * 4 + 1024; \
+    static unsigned long long configured = 0;                                                                         \
+    if (first_on_device(&configured)) {                                                                               \
+      DDPB_CUDA_CHECK(cudaFuncSetAttribute(first_layer_bwd_kernel<ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+      DDPB_CUDA_CHECK(cudaFuncSetAttribute(first_layer_bwd_kernel<ST>, cudaFuncAttributePreferredSharedMemoryCarveout,     \
+                                           cudaSharedmemCarveoutMaxShared));                                          \
+    }                                                                                                                 \
+    DDPB_CUDA_CHECK(launch_ex(first_layer_bwd_kernel<ST>, dim3(ctas), dim3(192), smem, stream, dim3(1, 1, 1), 16, tmY, tmD, \
+                              tmX, prm));                                                                             \
+  } while (0)
+  if (stages == 2) DDPB_FL_LAUNCH(2);
+  else if (stages == 3) DDPB_FL_LAUNCH(3);
+  else DDPB_FL_LAUNCH(4);
+#undef DDPB_FL_LAUNCH
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
 }
