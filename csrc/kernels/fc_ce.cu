@@ -15,17 +15,28 @@ constexpr int NCLS = 10;
 constexpr int FEAT = 512;
 constexpr int FC_SLICE = 16;
 
-// One warp per sample, no shared memory: lane l owns features [16 l, 16 l + 16) (two 16-byte activation
-// loads) and reads the matching 16 weights of every class with 16-byte loads (the 20 KB weight matrix
-// stays in L1/L2); the ten partial dot products are then reduced across the warp.
+// One warp per sample: lane l owns features [16 l, 16 l + 16) (two 16-byte activation loads).  The 20 KB weight
+// matrix is staged in shared memory by the whole CTA BEFORE griddepcontrol.wait - it does not depend on the
+// preceding kernel, so the staging overlaps that kernel's tail - in a lane-interleaved layout (float4 index
+// (class * 4 + quarter) * 32 + lane: conflict-free 16-byte reads).  Round 1 read the weights with ten dependent
+// groups of global loads per lane (42 registers: the compiler serialised them): 8.1 us, of which ~5 us were those
+// round trips.
 template <typename T>
 __global__ void __launch_bounds__(128)
 fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ bias,
                  const int64_t* __restrict__ target, float* __restrict__ logits, float* __restrict__ dlogits,
                  float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch, int pdl) {
+  __shared__ float4 ws[NCLS * 4 * 32];
+  __shared__ float bs[NCLS];
   if (pdl & 1) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
+  for (int e = threadIdx.x; e < NCLS * FEAT / 4; e += blockDim.x) {
+    const int j = e / (FEAT / 4), rem = e - j * (FEAT / 4);
+    ws[(j * 4 + (rem & 3)) * 32 + (rem >> 2)] = DDPB_LD_COH(reinterpret_cast<const float4*>(w) + e);
+  }
+  if (threadIdx.x < NCLS) bs[threadIdx.x] = ld_coh(&bias[threadIdx.x]);
   pdl_wait();
   ktrace_begin(pdl);      // stamped once the predecessor has finished: the start of this kernel's own work
+  __syncthreads();
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int b = blockIdx.x * (blockDim.x >> 5) + warp;
   if (b >= batch) return;
@@ -36,15 +47,17 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
   float acc[NCLS];
 #pragma unroll
   for (int j = 0; j < NCLS; ++j) {
-    float wv[16];
-    ld_coh_vec<16>(w + j * FEAT + lane * 16, wv);
     float a = 0.f;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) a = fmaf(av[i], wv[i], a);
+    for (int q = 0; q < 4; ++q) {
+      const float4 wv = ws[(j * 4 + q) * 32 + lane];
+      a = fmaf(av[4 * q], wv.x, a); a = fmaf(av[4 * q + 1], wv.y, a);
+      a = fmaf(av[4 * q + 2], wv.z, a); a = fmaf(av[4 * q + 3], wv.w, a);
+    }
     acc[j] = a;
   }
 #pragma unroll
-  for (int j = 0; j < NCLS; ++j) acc[j] = warp_sum(acc[j]) + ld_coh(&bias[j]);
+  for (int j = 0; j < NCLS; ++j) acc[j] = warp_sum(acc[j]) + bs[j];
   // every lane now holds all ten logits
   float mx = acc[0];
   int arg = 0;
