@@ -93,7 +93,9 @@ while True:
             key = ids[device_index] if device_index < len(ids) and ids[device_index].isdigit() else str(device_index)
         self.proc = subprocess.Popen([sys.executable, "-c", self.CHILD, key], stdout=subprocess.PIPE,
                                      stderr=subprocess.DEVNULL, text=True)
-        first = self.proc.stdout.readline().split()
+        import select
+        ok, _, _ = select.select([self.proc.stdout], [], [], 20.0)          # never block the benchmark on the sampler
+        first = self.proc.stdout.readline().split() if ok else []
         if len(first) != 2 or first[0] != "ready":
             self.proc.kill()
             raise RuntimeError("NVML sampler child did not start")
