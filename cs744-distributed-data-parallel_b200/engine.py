@@ -320,15 +320,17 @@ class NativeBackend:
             with self.on_stream():
                 cur = torch.cuda.current_stream(self.device)
                 cur.wait_event(slot["ready"])
-                F.augment(batch.images, None, batch.crop_xy, batch.flip, self.dtype, out=self.input, batch=n)
-                self.target[:n].copy_(batch.labels, non_blocking=True)
+                F.augment(batch.images, None, batch.crop_xy, batch.flip, self.dtype, out=self.input, batch=n,
+                          labels=(batch.labels, self.target))           # images and targets in one launch
                 slot["consumed"] = torch.cuda.Event()
                 slot["consumed"].record(cur)
             return self.input[:n], self.target[:n]
         with self.on_stream():
             b = batch.to(self.device)
-            F.augment(b.images, None, b.crop_xy, b.flip, self.dtype, out=self.input, batch=n)
-            self.target[:n].copy_(b.labels, non_blocking=True)
+            F.augment(b.images, None, b.crop_xy, b.flip, self.dtype, out=self.input, batch=n,
+                      labels=(b.labels.contiguous(), self.target) if b.labels.dtype == torch.int64 else None)
+            if b.labels.dtype != torch.int64:
+                self.target[:n].copy_(b.labels, non_blocking=True)
         return self.input[:n], self.target[:n]
 
     def _stage(self, data: torch.Tensor, target: torch.Tensor) -> int:

@@ -22,12 +22,19 @@ BN_MOMENTUM = 0.1
 # ---- data / optimizer ---------------------------------------------------------------------
 def augment(images_u8: torch.Tensor, index: Optional[torch.Tensor], crop_xy: Optional[torch.Tensor],
             flip: Optional[torch.Tensor], dtype: torch.dtype, out: Optional[torch.Tensor] = None,
-            batch: Optional[int] = None) -> torch.Tensor:
+            batch: Optional[int] = None, labels: Optional[Tuple[torch.Tensor, torch.Tensor]] = None) -> torch.Tensor:
+    """``labels=(src, dst)``: the batch's int64 targets are copied by the same kernel."""
     b = batch if batch is not None else (index.numel() if index is not None else images_u8.shape[0])
     if out is None:
         out = torch.empty((b, 32, 32, 3), dtype=dtype, device=images_u8.device)
     mean = (ctypes.c_float * 3)(*CIFAR_MEAN)
     std = (ctypes.c_float * 3)(*CIFAR_STD)
+    if labels is not None:
+        src, dst = labels
+        assert src.dtype == torch.int64 and dst.dtype == torch.int64 and src.numel() >= b and dst.numel() >= b
+        check(lib().ddpb_augment_labels(ptr(images_u8), ptr(index), ptr(crop_xy), ptr(flip), ptr(out), ptr(src), ptr(dst), b,
+                                        dtype_code(dtype), mean, std, stream_handle()), "augment_labels")
+        return out
     check(lib().ddpb_augment(ptr(images_u8), ptr(index), ptr(crop_xy), ptr(flip), ptr(out), b,
                              dtype_code(dtype), mean, std, stream_handle()), "augment")
     return out

@@ -19,9 +19,11 @@ __global__ void augment_kernel(const uint8_t* __restrict__ images,   // [N,32,32
                                const int32_t* __restrict__ crop_xy,  // [B,2] in [0,8], or null
                                const uint8_t* __restrict__ flip,     // [B], or null
                                T* __restrict__ out,                  // [B,32,32,3]
+                               const int64_t* __restrict__ labels_src, int64_t* __restrict__ labels_dst,   // [B] each, or null
                                int batch, float m0, float m1, float m2, float s0, float s1, float s2) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= batch * 1024) return;
+  if (labels_dst && t < batch) labels_dst[t] = labels_src[t];       // the batch's targets ride along: one launch less per step
   int b = t >> 10, h = (t >> 5) & 31, w = t & 31;
   long long src = index ? index[b] : b;
   int ox = crop_xy ? crop_xy[2 * b] - 4 : 0;
@@ -253,22 +255,33 @@ DDPB_KTRACE_SETTER(elementwise)
 
 using namespace ddpb;
 
-extern "C" int ddpb_augment(const void* images, const void* index, const void* crop_xy, const void* flip,
-                            void* out, int batch, int out_dtype, const float* mean3, const float* std3,
-                            cudaStream_t stream) {
+// labels_src / labels_dst (int64 [batch], nullable): the batch's targets are copied by the same kernel, so a staged
+// batch reaches the engine's input and target buffers in ONE launch (ddpb_augment = without labels).
+extern "C" int ddpb_augment_labels(const void* images, const void* index, const void* crop_xy, const void* flip,
+                                   void* out, const void* labels_src, void* labels_dst, int batch, int out_dtype,
+                                   const float* mean3, const float* std3, cudaStream_t stream) {
   DDPB_REQUIRE(batch > 0, "augment: batch must be positive");
+  DDPB_REQUIRE((labels_src == nullptr) == (labels_dst == nullptr), "augment: labels_src and labels_dst go together");
   int threads = 256, blocks = ceil_div((long long)batch * 1024, threads);
   if (out_dtype == DDPB_BF16) {
     augment_kernel<bf16><<<blocks, threads, 0, stream>>>(
         (const uint8_t*)images, (const int64_t*)index, (const int32_t*)crop_xy, (const uint8_t*)flip,
-        (bf16*)out, batch, mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2]);
+        (bf16*)out, (const int64_t*)labels_src, (int64_t*)labels_dst, batch, mean3[0], mean3[1], mean3[2], std3[0],
+        std3[1], std3[2]);
   } else {
     augment_kernel<float><<<blocks, threads, 0, stream>>>(
         (const uint8_t*)images, (const int64_t*)index, (const int32_t*)crop_xy, (const uint8_t*)flip,
-        (float*)out, batch, mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2]);
+        (float*)out, (const int64_t*)labels_src, (int64_t*)labels_dst, batch, mean3[0], mean3[1], mean3[2], std3[0],
+        std3[1], std3[2]);
   }
   DDPB_LAUNCH_CHECK();
   return DDPB_OK;
+}
+
+extern "C" int ddpb_augment(const void* images, const void* index, const void* crop_xy, const void* flip,
+                            void* out, int batch, int out_dtype, const float* mean3, const float* std3,
+                            cudaStream_t stream) {
+  return ddpb_augment_labels(images, index, crop_xy, flip, out, nullptr, nullptr, batch, out_dtype, mean3, std3, stream);
 }
 
 extern "C" int ddpb_sgd_step(float* param, float* mom, const float* grad, void* shadow_bf16, long long n,

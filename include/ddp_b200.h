@@ -43,6 +43,10 @@ const char* ddpb_last_error(void);
  * (null: none), /255 and per-channel normalisation; write NHWC.  ref Part 1/main.py:82-93. */
 int ddpb_augment(const void* images_u8, const void* index_i64, const void* crop_xy_i32, const void* flip_u8,
                  void* out, int batch, int out_dtype, const float* mean3, const float* std3, cudaStream_t stream);
+/* The same, and the batch's int64 targets are copied labels_src -> labels_dst by the same kernel (both nullable). */
+int ddpb_augment_labels(const void* images_u8, const void* index_i64, const void* crop_xy_i32, const void* flip_u8,
+                        void* out, const void* labels_src_i64, void* labels_dst_i64, int batch, int out_dtype,
+                        const float* mean3, const float* std3, cudaStream_t stream);
 
 /* SGD with momentum and weight decay over a flat range (torch.optim.SGD semantics, dampening 0,
  * no Nesterov; ref Part 1/main.py:114-115): g = grad*grad_scale + wd*p; m = momentum*m + g;

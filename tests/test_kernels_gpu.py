@@ -55,6 +55,11 @@ def test_augment_matches_torch_pipeline(F):
     plain = F.augment(split.images, None, None, None, torch.float32, batch=64)
     ref2 = transform_batch(RawBatch(split.images, split.labels, None, None), layout="nhwc")
     assert torch.allclose(plain, ref2, atol=1e-6)
+    # the targets of the batch ride along in the same launch (the engine's staged-batch path)
+    dst = torch.full((80,), -1, dtype=torch.int64, device=DEV)
+    lab = split.labels[idx].contiguous()
+    out2 = F.augment(split.images, idx, crop, flip, torch.float32, labels=(lab, dst))
+    assert torch.equal(out2, out) and torch.equal(dst[:40], lab) and bool((dst[40:] == -1).all())
 
 
 def test_sgd_matches_torch_optim(F):
