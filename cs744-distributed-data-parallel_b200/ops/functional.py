@@ -139,9 +139,22 @@ def fc_ce_fwd(act: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, target: to
     return logits, dlogits, loss, correct
 
 
-def fc_bwd(act: torch.Tensor, w: torch.Tensor, dlogits: torch.Tensor):
+def fc_ce_fwd_dact(act: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, target: torch.Tensor):
+    """Loss kernel that also writes the gradient of its input (what ``fc_bwd`` returns as ``dact``)."""
     b = act.shape[0]
+    dev = act.device
+    logits = torch.empty((b, 10), dtype=torch.float32, device=dev)
+    dlogits = torch.empty((b, 10), dtype=torch.float32, device=dev)
+    loss = torch.zeros(1, dtype=torch.float32, device=dev)
     dact = torch.empty_like(act)
+    check(lib().ddpb_fc_ce_fwd_dact(ptr(act), ptr(w), ptr(bias), ptr(target), ptr(logits), ptr(dlogits), ptr(loss), None,
+                                    ptr(dact), b, b, dtype_code(act.dtype), stream_handle()), "fc_ce_fwd_dact")
+    return logits, dlogits, loss, dact
+
+
+def fc_bwd(act: torch.Tensor, w: torch.Tensor, dlogits: torch.Tensor, want_dact: bool = True):
+    b = act.shape[0]
+    dact = torch.empty_like(act) if want_dact else None
     dw = torch.zeros((10, 512), dtype=torch.float32, device=act.device)
     db = torch.zeros(10, dtype=torch.float32, device=act.device)
     check(lib().ddpb_fc_bwd(ptr(act), ptr(w), ptr(dlogits), ptr(dact), ptr(dw), ptr(db), b,

@@ -25,7 +25,8 @@ template <typename T>
 __global__ void __launch_bounds__(128)
 fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const float* __restrict__ bias,
                  const int64_t* __restrict__ target, float* __restrict__ logits, float* __restrict__ dlogits,
-                 float* __restrict__ loss, int* __restrict__ correct, int batch, float inv_batch, int pdl) {
+                 float* __restrict__ loss, int* __restrict__ correct, T* __restrict__ dact, int batch, float inv_batch,
+                 int pdl) {
   __shared__ float4 ws[NCLS * 4 * 32];
   __shared__ float bs[NCLS];
   if (pdl & 1) pdl_launch_dependents();     // programmatic dependent launch: see common.cuh
@@ -69,17 +70,37 @@ fc_ce_fwd_kernel(const T* __restrict__ act, const float* __restrict__ w, const f
   for (int j = 0; j < NCLS; ++j) se += expf(acc[j] - mx);
   float lse = mx + logf(se);
   int t = (int)DDPB_LD_COH(reinterpret_cast<const long long*>(&target[b]));
+  float dl[NCLS];                 // every lane: the sample's logit gradient (identical values in all lanes)
+#pragma unroll
+  for (int j = 0; j < NCLS; ++j) dl[j] = (expf(acc[j] - lse) - (j == t ? 1.f : 0.f)) * inv_batch;
   if (lane == 0) {
     float lt = 0.f;
 #pragma unroll
     for (int j = 0; j < NCLS; ++j) {
-      float p = expf(acc[j] - lse);
       if (logits) logits[b * NCLS + j] = acc[j];
-      if (dlogits) dlogits[b * NCLS + j] = (p - (j == t ? 1.f : 0.f)) * inv_batch;
+      if (dlogits) dlogits[b * NCLS + j] = dl[j];
       if (j == t) lt = acc[j];
     }
     atomicAdd(loss, (lse - lt) * inv_batch);
     if (correct && arg == t) atomicAdd(correct, 1);
+  }
+  if (dact) {
+    // the gradient of the classifier's input, dA[b, k] = sum_j dlogits[b, j] W[j, k], from the staged weights: the
+    // backward pass then starts with the last block's BatchNorm backward and the classifier's weight gradient
+    // leaves the critical path (same summation order as fc_bwd_kernel: bit-identical)
+    float o[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) o[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < NCLS; ++j)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 wv = ws[(j * 4 + q) * 32 + lane];
+        o[4 * q] = fmaf(dl[j], wv.x, o[4 * q]); o[4 * q + 1] = fmaf(dl[j], wv.y, o[4 * q + 1]);
+        o[4 * q + 2] = fmaf(dl[j], wv.z, o[4 * q + 2]); o[4 * q + 3] = fmaf(dl[j], wv.w, o[4 * q + 3]);
+      }
+#pragma unroll
+    for (int i = 0; i < 16; i += V) store_vec<T>(dact + (size_t)b * FEAT + lane * 16 + i, o + i);
   }
   ktrace_end(pdl);
 }
@@ -128,27 +149,36 @@ DDPB_KTRACE_SETTER(fc_ce)
 using namespace ddpb;
 
 // `loss` (1 float) and `correct` (1 int, may be null) are ACCUMULATED into: zero them first.
-extern "C" int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias, const void* target_i64,
-                              float* logits, float* dlogits, float* loss, int* correct, int batch,
-                              int loss_divisor, int dtype, cudaStream_t stream) {
+// dact (nullable, same dtype as act, [batch, 512]): also write the gradient of the classifier's input, which
+// ddpb_fc_bwd would otherwise compute (call that with dact = null then: weight and bias gradients only).
+extern "C" int ddpb_fc_ce_fwd_dact(const void* act, const float* w, const float* bias, const void* target_i64,
+                                   float* logits, float* dlogits, float* loss, int* correct, void* dact, int batch,
+                                   int loss_divisor, int dtype, cudaStream_t stream) {
   DDPB_REQUIRE(batch > 0 && loss_divisor > 0, "fc_ce_fwd: bad batch");
   int blocks = ceil_div(batch, 4);
   float inv = 1.f / (float)loss_divisor;
   if (dtype == DDPB_BF16)
     DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<bf16>, dim3(blocks), dim3(128), 0, stream, dim3(1, 1, 1), 32,
                               (const bf16*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
-                              batch, inv, kernel_flags(stream, 32)));
+                              (bf16*)dact, batch, inv, kernel_flags(stream, 32)));
   else
     DDPB_CUDA_CHECK(launch_ex(fc_ce_fwd_kernel<float>, dim3(blocks), dim3(128), 0, stream, dim3(1, 1, 1), 32,
                               (const float*)act, w, bias, (const int64_t*)target_i64, logits, dlogits, loss, correct,
-                              batch, inv, kernel_flags(stream, 32)));
+                              (float*)dact, batch, inv, kernel_flags(stream, 32)));
   return DDPB_OK;
+}
+
+extern "C" int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias, const void* target_i64,
+                              float* logits, float* dlogits, float* loss, int* correct, int batch,
+                              int loss_divisor, int dtype, cudaStream_t stream) {
+  return ddpb_fc_ce_fwd_dact(act, w, bias, target_i64, logits, dlogits, loss, correct, nullptr, batch, loss_divisor, dtype,
+                             stream);
 }
 
 // dw [10*512] and db [10] are ACCUMULATED into (they live in the zeroed gradient arena).
 extern "C" int ddpb_fc_bwd(const void* act, const float* w, const float* dlogits, void* dact, float* dw,
                            float* db, int batch, int dtype, cudaStream_t stream) {
-  int blocks_da = ceil_div((long long)batch * FEAT, 256);
+  int blocks_da = dact ? ceil_div((long long)batch * FEAT, 256) : 0;     // dact = null: weight / bias gradients only
   int blocks_dw = ceil_div(NCLS * FEAT + NCLS, 256) * ceil_div(batch, FC_SLICE);
   if (dtype == DDPB_BF16)
     fc_bwd_kernel<bf16><<<blocks_da + blocks_dw, 256, 0, stream>>>((const bf16*)act, w, dlogits, (bf16*)dact, dw,

@@ -85,6 +85,7 @@ struct Engine {
   void *x0cols = nullptr, *w0pad = nullptr;   // first layer as a GEMM: patch matrix [B*1024][64], weights [64][64]
   std::vector<Bucket> buckets;
   std::vector<long long> shard;          // [lo, hi) arena ranges of the conv weights: fp32 master stays with its owner
+  bool fuse_fc_da = false;               // DDPB_FUSE_FC_DA=1: the loss kernel also produces the classifier's input gradient
   bool shard_master = true;              // DDPB_SHARD_MASTER=0: publish the fp32 master of every element
   int sub_buckets = 1;                   // DDPB_SUB_BUCKETS=2|4: split the large layers' buckets by output-channel range
   long long sub_bucket_min = 1 << 20;    // ... layers with at least this many weight elements (DDPB_SUB_BUCKET_MIN)
@@ -494,9 +495,11 @@ static int forward(Engine* e, int B, int training, cudaStream_t s, bool zero_gra
 
 static int loss_fwd(Engine* e, int B, int training, cudaStream_t s) {
   const Block& last = e->blocks.back();
-  LAUNCH(e, s, ddpb_fc_ce_fwd(last.act, e->master + e->fc_w.off, e->master + e->fc_b.off, e->target, e->logits,
-                           training ? e->dlogits : nullptr, training ? e->loss : e->eval_loss,
-                           training ? nullptr : e->correct, B, B, e->cfg.dtype, s));
+  // training: the loss kernel also produces the gradient of the classifier's input (DDPB_FUSE_FC_DA=0: fc_bwd does)
+  LAUNCH(e, s, ddpb_fc_ce_fwd_dact(last.act, e->master + e->fc_w.off, e->master + e->fc_b.off, e->target, e->logits,
+                                training ? e->dlogits : nullptr, training ? e->loss : e->eval_loss,
+                                training ? nullptr : e->correct, (training && e->fuse_fc_da) ? e->dact : nullptr, B, B,
+                                e->cfg.dtype, s));
   return DDPB_OK;
 }
 
@@ -661,9 +664,21 @@ static int backward(Engine* e, int B, cudaStream_t s, bool grads_zeroed = false)
   if (grads_zeroed) DDPB_CUDA_CHECK(cudaStreamWaitEvent(s, e->zero_ev, 0));    // cleared during forward(), on wg
   else DDPB_CUDA_CHECK(cudaMemsetAsync(e->grad, 0, e->arena_elems * 4, s));
   const Block& last = e->blocks.back();
-  LAUNCH(e, s, ddpb_fc_bwd(last.act, e->master + e->fc_w.off, e->dlogits, e->dact, e->grad + e->fc_w.off,
-                        e->grad + e->fc_b.off, B, dt, s));
-  DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[L], s));
+  if (e->fuse_fc_da && grads_zeroed) {
+    // dA came with the loss kernel: the classifier's weight / bias gradient is all that is left of its backward,
+    // and it runs on the weight-gradient stream, off the critical path.  (Only in the whole-step graph, where the
+    // gradient arena was cleared on that stream: when the memset sits on `s` right above, a normally launched kernel
+    // has to follow it - a programmatic launch cannot depend on a memset node - and fc_bwd is that kernel.)
+    DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dy[L], s));                 // the loss kernel has run, the gradient arena is zero
+    DDPB_CUDA_CHECK(cudaStreamWaitEvent(e->wg, e->ev_dy[L], 0));
+    LAUNCH(e, e->wg, ddpb_fc_bwd(last.act, e->master + e->fc_w.off, e->dlogits, nullptr, e->grad + e->fc_w.off,
+                              e->grad + e->fc_b.off, B, dt, e->wg));
+    DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[L], e->wg));
+  } else {
+    LAUNCH(e, s, ddpb_fc_bwd(last.act, e->master + e->fc_w.off, e->dlogits, e->fuse_fc_da ? nullptr : e->dact,
+                          e->grad + e->fc_w.off, e->grad + e->fc_b.off, B, dt, s));
+    DDPB_CUDA_CHECK(cudaEventRecord(e->ev_dg[L], s));
+  }
   ECHECK(buckets_ready(e, -1, e->ev_dg[L], nullptr));
   bool reduced_by_dgrad = false;
   for (int i = L - 1; i >= 0; --i) {
@@ -912,6 +927,7 @@ extern "C" int ddpb_engine_create(const ddpb_engine_config* cfg, void** handle) 
   if (const char* f0 = getenv("DDPB_FUSE_FIRST_BWD")) e->fuse_first_bwd = f0[0] != '0';
   if (const char* tf = getenv("DDPB_TF32")) e->tf32 = tf[0] != '0';
   if (const char* sm = getenv("DDPB_SHARD_MASTER")) e->shard_master = sm[0] != '0';
+  if (const char* v = getenv("DDPB_FUSE_FC_DA")) e->fuse_fc_da = v[0] != '0';
   if (const char* v = getenv("DDPB_SUB_BUCKETS")) { const int n = atoi(v); e->sub_buckets = (n == 2 || n == 4) ? n : 1; }
   if (const char* v = getenv("DDPB_SUB_BUCKET_MIN")) { const long long n = atoll(v); if (n > 0) e->sub_bucket_min = n; }
   if (const char* v = getenv("DDPB_SUB_BUCKETS_FORCE")) e->sub_bucket_force = v[0] == '1';

@@ -123,7 +123,13 @@ int ddpb_fc_ce_fwd(const void* act, const float* w, const float* bias, const voi
                    float* dlogits, float* loss, int* correct, int batch, int loss_divisor, int dtype,
                    cudaStream_t stream);
 
-/* dact [batch,512] is written; dw [10,512] and db [10] accumulate. */
+/* The same, and when dact ([batch,512], dtype of act) is non-null the kernel also writes the gradient of the
+ * classifier's input (what ddpb_fc_bwd computes as dact), so that backward can start with the last block at once. */
+int ddpb_fc_ce_fwd_dact(const void* act, const float* w, const float* bias, const void* target_i64, float* logits,
+                        float* dlogits, float* loss, int* correct, void* dact, int batch, int loss_divisor, int dtype,
+                        cudaStream_t stream);
+
+/* dact [batch,512] is written (null: skipped - weight and bias gradients only); dw [10,512] and db [10] accumulate. */
 int ddpb_fc_bwd(const void* act, const float* w, const float* dlogits, void* dact, float* dw, float* db,
                 int batch, int dtype, cudaStream_t stream);
 

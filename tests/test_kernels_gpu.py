@@ -146,6 +146,15 @@ def test_fc_cross_entropy(F, R, dtype, b):
     _report("fc_dact", dact, rda, tol)
     _report("fc_dw", dw, rdw, 1e-4)
     _report("fc_db", db, rdb, 1e-4)
+    # the loss kernel can produce dact itself (the engine's path: backward then starts with the last conv block):
+    # same values as fc_bwd's, and fc_bwd without dact leaves the weight / bias gradients unchanged
+    logits2, dlogits2, loss2, dact2 = F.fc_ce_fwd_dact(act, w, bias, tgt)
+    assert torch.equal(logits2, logits) and torch.equal(dlogits2, dlogits)
+    assert torch.equal(dact2, dact)
+    none, dw2, db2 = F.fc_bwd(act, w, dlogits, want_dact=False)
+    assert none is None
+    _report("fc_dw (no dact)", dw2, rdw, 1e-4)
+    _report("fc_db (no dact)", db2, rdb, 1e-4)
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
