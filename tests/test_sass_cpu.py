@@ -86,3 +86,10 @@ def test_pair_tiles_issue_the_two_cta_mma(sass):
         body = text.split("Function : " + name, 1)[1].split("Function :", 1)[0]
         assert re.search(r"UTCHMMA\.2CTA", body), name
         assert re.search(r"UTCBAR\.2CTA\.MULTICAST", body), name
+
+
+def test_block0_backward_ends_with_one_bulk_reduce_add(sass):
+    """The 64 x 27 partial weight gradient leaves each CTA through cp.reduce.async.bulk (UBLKRED), the RED loop is the
+    fall-back for non-contiguous destinations only."""
+    ks = _with(sass, "first_layer_bwd_kernel")
+    assert ks and all("UBLKRED" in ops for ops in ks.values()), {k: sorted(v & {"UBLKRED", "REDG"}) for k, v in ks.items()}
